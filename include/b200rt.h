@@ -1,0 +1,197 @@
+/* b200rt.h — C ABI of the B200-native render hot path.
+ *
+ * The reference (clayne/CPU-Raytracer) has no plugin / FFI interface: its hot path is
+ * reached by a direct C++ call from worker threads,
+ *     params.raytracer->render_tile(*params.window, x, y, w, h, *params.stats)   WorkerThread.cpp:63
+ * driven once per frame by Main.cpp:54-59:
+ *     scene.update(dt); wake_up_worker_threads(tiles); wait_on_worker_threads(); window.draw_quad();
+ * The seam is therefore "one frame". b200rt_render_frame() replaces
+ * wake_up_worker_threads + wait_on_worker_threads + draw_quad (Main.cpp:56-59): every tile
+ * of the frame is ray traced (Raytracer.cpp:3-400) and the FXAA + gamma pass of
+ * Data/Shaders/fragment_fxaa.glsl is applied, on the GPU. Scene::update (Scene.cpp:139-171,
+ * including the per-frame TopLevelBVH rebuild) stays on the host, exactly where the
+ * reference has it; its results are handed over in b200rt_frame.
+ *
+ * Plain C: POD structs, raw pointers, sizes. No C++ or torch types cross this boundary.
+ * All arrays are borrowed for the duration of the call and copied; the context owns every
+ * device allocation. A context is single-caller (not re-entrant), like the reference's
+ * frame loop. Every function returns 0 on success, < 0 on error (the reference abort()s:
+ * Texture.cpp:43-47, Sky.cpp:11, BottomLevelBVH.cpp:153,174); b200rt_last_error() gives text.
+ */
+#ifndef B200RT_H
+#define B200RT_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---------------------------------------------------------------- data layouts ------ */
+/* Byte-for-byte the reference's structs, so that a host that holds the
+ * reference's objects can pass them without conversion.                                  */
+
+/* BVHNode, BVHNode.h:10-16. count bits 30-31 = split axis + 1 (inner node), bits 0-29 =
+ * primitive count (> 0 => leaf). Inner: children at left, left+1. Root = node 0.          */
+typedef struct { float aabb_min[3]; float aabb_max[3]; int32_t left_or_first; int32_t count; } b200rt_bvh_node;
+
+/* BottomLevelBVH::TriangleHot, BottomLevelBVH.h:6-10 (edges pre-subtracted).              */
+typedef struct { float position_0[3]; float position_edge_1[3]; float position_edge_2[3]; } b200rt_triangle_hot;
+
+/* BottomLevelBVH::TriangleCold, BottomLevelBVH.h:12-22. material_id is mesh-local.        */
+typedef struct {
+	float tex_coord_0[2], tex_coord_edge_1[2], tex_coord_edge_2[2];
+	float normal_0[3], normal_edge_1[3], normal_edge_2[3];
+	int32_t material_id;
+} b200rt_triangle_cold;
+
+/* One BottomLevelBVH in the concatenated static arrays. Triangles are FLATTENED (leaf
+ * order, BottomLevelBVH.cpp:196-212): a leaf's `first` indexes triangles directly.         */
+typedef struct {
+	int32_t node_offset, node_count;       /* into static_scene.nodes                       */
+	int32_t triangle_offset, triangle_count; /* into static_scene.triangles_hot/_cold        */
+	int32_t material_offset;                /* BottomLevelBVH::material_offset               */
+} b200rt_blas;
+
+/* Material, Material.h:7-14, re-packed: the texture pointer becomes an index (-1 = none). */
+typedef struct {
+	float   diffuse[3];
+	int32_t texture;
+	float   reflection[3];
+	float   index_of_refraction;
+	float   transmittance[3];
+	int32_t reserved;
+} b200rt_material;
+
+/* Texture, Texture.h:8-18: linear-space float RGB texels, all mip levels contiguous.      */
+#define B200RT_MAX_MIP_LEVELS 16
+typedef struct {
+	int64_t texel_offset;                  /* first texel of level 0 in static_scene.texels */
+	int32_t width, height;
+	int32_t mipmapped;                     /* Texture::mipmapped                            */
+	int32_t mip_levels;                    /* 1 when not mip-mapped                         */
+	int32_t mip_offsets[B200RT_MAX_MIP_LEVELS]; /* in texels, relative to texel_offset       */
+} b200rt_texture;
+
+/* Everything that does not change between frames (Scene members Scene.h:20-39 that are
+ * loaded once; MaterialBuffer::materials Material.h:28-30; Sky Sky.h:4-12).                */
+typedef struct {
+	const b200rt_bvh_node      * nodes;          int32_t node_count;
+	const b200rt_triangle_hot  * triangles_hot;
+	const b200rt_triangle_cold * triangles_cold; int32_t triangle_count;
+	const b200rt_blas          * blas;           int32_t blas_count;
+	const b200rt_material      * materials;      int32_t material_count;  /* <= 256, Config.h:18 */
+	const b200rt_texture       * textures;       int32_t texture_count;
+	const float                * texels;         int64_t texel_count;     /* float[texel_count][3] */
+	const float                * sky;            int32_t sky_size;        /* float[size*size (+1)][3], Sky.cpp:13-25 */
+} b200rt_static_scene;
+
+/* Mesh, Mesh.h:8-16: instance of a BLAS. Matrices are the reference's Matrix4 (column-major
+ * cells[i + 4j], Matrix4.h:19-28): world = Transform::world_matrix, inverse = Mesh::transform_inv. */
+typedef struct { float world[16]; float inverse[16]; int32_t blas; int32_t reserved[3]; } b200rt_instance;
+
+/* Sphere.h:8-22 after update: centre = transform.position.                                */
+typedef struct { float center[3]; float radius_squared; float radius_inv; int32_t material_id; int32_t reserved[2]; } b200rt_sphere;
+
+/* Plane.h:8-22 after Plane::update (Plane.cpp:3-11).                                      */
+typedef struct { float normal[3]; float distance; float u_axis[3]; int32_t material_id; float v_axis[3]; int32_t reserved; } b200rt_plane;
+
+/* PointLight.h / SpotLight.h / DirectionalLight.h. kind: 0 point, 1 spot, 2 directional.
+ * Lights are evaluated in the reference's order: all point, then spot, then directional
+ * (Raytracer.cpp:155-198); the array must be sorted by kind.                              */
+typedef struct {
+	int32_t kind;
+	float   colour[3];
+	float   position[3];           /* point, spot                                          */
+	float   negative_direction[3]; /* spot, directional (= -direction)                     */
+	float   inner_cutoff, outer_cutoff; /* spot: cos of the half angles, SpotLight.h:13-14 */
+} b200rt_light;
+
+/* Camera.h:12-23 after Camera::update: position + rotated view pyramid.                   */
+typedef struct { float position[3]; float top_left_corner[3]; float x_axis[3]; float y_axis[3]; } b200rt_camera;
+
+/* What Scene::update (Scene.cpp:139-171) produces each frame.                             */
+typedef struct {
+	b200rt_camera camera;
+	float         ambient[3];                                   /* Scene::ambient_lighting  */
+	const b200rt_instance * instances;   int32_t instance_count; /* TopLevelBVH::primitives  */
+	const b200rt_bvh_node * tlas_nodes;  int32_t tlas_node_count; /* TopLevelBVH::nodes       */
+	const int32_t         * tlas_indices;                        /* TopLevelBVH::indices [instance_count] */
+	const b200rt_sphere   * spheres;     int32_t sphere_count;
+	const b200rt_plane    * planes;      int32_t plane_count;
+	const b200rt_light    * lights;      int32_t light_count;
+} b200rt_frame;
+
+/* Run-time mirror of the compile-time switches in Config.h:1-55.                          */
+enum { B200RT_FILTER_TRILINEAR = 0, B200RT_FILTER_ANISOTROPIC = 1, B200RT_FILTER_EWA = 2 }; /* MIPMAP_FILTER */
+typedef struct {
+	int32_t width, height;        /* SCREEN_WIDTH / SCREEN_HEIGHT                            */
+	int32_t bounces;              /* NUMBER_OF_BOUNCES (0..8)                                */
+	int32_t mipmap_filter;        /* MIPMAP_FILTER                                           */
+	float   max_anisotropy;       /* MAX_ANISOTROPY                                          */
+	int32_t enable_fxaa;          /* ENABLE_FXAA: 1 = fragment_fxaa.glsl, 0 = fragment_identity.glsl */
+	int32_t device;               /* CUDA device ordinal                                     */
+	/* Multi-GPU tile partition: this context renders the 32x32 tiles whose
+	 * row-major id t satisfies t % tile_stride == tile_phase. 1 / 0 = the whole frame.       */
+	int32_t tile_stride, tile_phase;
+} b200rt_config;
+
+/* Counters of one frame. Rays are ACTIVE rays (one per traced ray), which is what the
+ * reference's lane-1 build counts (Raytracer.cpp:61,163,180,192,265,320).                  */
+typedef struct {
+	uint64_t primary_rays, shadow_rays, reflection_rays, refraction_rays;
+	uint64_t nodes_visited;        /* TLAS + BLAS nodes whose box was tested                 */
+	uint64_t triangles_tested;
+	uint64_t texels_fetched;
+	float    device_ms_render;     /* CUDA-event time of the ray tracing kernel(s)           */
+	float    device_ms_fxaa;       /* CUDA-event time of the FXAA kernel                     */
+	float    device_ms_total;      /* uploads + kernels + downloads on the context's stream  */
+} b200rt_stats;
+
+/* Host buffers to fill; any pointer may be NULL to skip that output.                      */
+typedef struct {
+	uint32_t * frame_buffer;   /* [height][width] 0x00RRGGBB, linear colour, Window::plot (Window.h:56-65) */
+	uint8_t  * presented_rgb8; /* [height][width][3] after gamma + FXAA (fragment_fxaa.glsl)  */
+	float    * colour_float;   /* [height][width][3] un-quantised linear colour (diagnostic)  */
+	int32_t  * primary_ids;    /* [height][width][2] (instance, flattened triangle); miss = (-1,-1);
+	                              sphere k = (-2,k); plane k = (-3,k)                          */
+	float    * primary_hit;    /* [height][width][4] (distance, material id, u, v)            */
+	b200rt_stats * stats;
+} b200rt_outputs;
+
+typedef struct b200rt_ctx b200rt_ctx;
+
+/* ---------------------------------------------------------------- device path ------- */
+int  b200rt_create(const b200rt_config * config, b200rt_ctx ** ctx);
+void b200rt_destroy(b200rt_ctx * ctx);
+const char * b200rt_last_error(const b200rt_ctx * ctx); /* ctx may be NULL: error of b200rt_create */
+
+/* Replaces the one-off construction of Scene / BottomLevelBVH::load / Texture::load /
+ * MaterialBuffer / Sky (Main.cpp:26-41): copies and re-packs the static arrays into HBM.   */
+int b200rt_upload_static(b200rt_ctx * ctx, const b200rt_static_scene * scene);
+
+/* Replaces Main.cpp:56-59 for one frame. Host buffers in, host buffers out: uploads the
+ * per-frame data, renders, applies FXAA, downloads the requested outputs.                  */
+int b200rt_render_frame(b200rt_ctx * ctx, const b200rt_frame * frame, const b200rt_outputs * outputs);
+
+/* Same, but leaves the results in device memory (for callers that keep the image on the
+ * GPU, e.g. the multi-GPU gather over NCCL): frame_buffer_dev is uint32 [height][width]
+ * (only this context's tiles are written), presented_dev is uint8 [height][width][3] or 0. */
+int b200rt_render_frame_device(b200rt_ctx * ctx, const b200rt_frame * frame,
+                               uint64_t frame_buffer_dev, b200rt_stats * stats);
+
+/* FXAA + gamma over a full pre-FXAA frame that is already in device memory (after the
+ * multi-GPU gather): in uint32 [height][width], out uint8 [height][width][3].              */
+int b200rt_present_device(b200rt_ctx * ctx, uint64_t frame_buffer_dev, uint64_t presented_dev, float * device_ms);
+
+/* Re-times the last frame without host<->device traffic: `repeat` back-to-back launches of
+ * the render (+FXAA) kernels on resident inputs; returns the average per-frame device time. */
+int b200rt_time_resident(b200rt_ctx * ctx, int repeat, float * ms_render, float * ms_fxaa);
+
+/* The CUDA stream (cudaStream_t as integer) all work of this context is issued on.        */
+uint64_t b200rt_stream(const b200rt_ctx * ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200RT_H */
