@@ -2,11 +2,16 @@
 // SDL2/OpenGL/ImGui window). Same frame loop as Main.cpp:51-59 without the presentation:
 //   scene.update(dt) -> wake worker threads over all tiles -> wait.
 // Adds: scene description file input, raw dumps of the frame buffer, timing, and (in the
-// ORACLE_IDS build, lane size 1 only) a primary-ray pass that records the closest-hit
+// ORACLE_IDS build) a primary-ray pass that records the closest-hit
 // record per pixel through the reference's own Scene::trace_primitives.
 //
 // usage: ref_<variant> scene.txt --out PREFIX [--frames N] [--dt SECONDS] [--dump a,b,c]
-//                      [--width W --height H] [--quiet]
+//                      [--width W --height H] [--quiet] [--per-ray]
+// --per-ray: instead of render_tile's 4x2 pixel packets (Raytracer.cpp:28-42) every pixel gets a
+//   packet whose lanes all carry the SAME ray (primary ray expressions of Raytracer.cpp:45-59),
+//   pushed through the reference's own Raytracer::bounce; lane 0 is plotted. Arithmetic is the
+//   SIMD build's (fused madd, SVML->libmvec), but traversal order and every all/any early-out
+//   depend on that one ray only — the semantics a one-ray-per-thread GPU renderer has.
 // dumps (little-endian raw):  PREFIX.fNNNN.u32   uint32 [H][W]   0x00RRGGBB (Window::plot)
 //                             PREFIX.fNNNN.rgbf  float  [H][W][3] un-quantised colour
 //                             PREFIX.fNNNN.ids   int32  [H][W][2] (instance, triangle)   ORACLE_IDS
@@ -16,9 +21,24 @@
 #include <vector>
 #include <algorithm>
 
+#include <thread>
+#include <atomic>
+#include <map>
+#include <unordered_map>
+#include <filesystem>
+#include <fstream>
+#include <sstream>
+
 #include "SceneFile.h"
 
+#include "Scene.h"
+
+// `Raytracer::bounce` is private (Raytracer.h:16-17). The per-ray mode below has to call it with a
+// ray of its own, so the access specifier is lifted for this one header — layout and code of the
+// reference class are untouched.
+#define private public
 #include "Raytracer.h"
+#undef private
 #include "WorkerThread.h"
 
 #ifdef ORACLE_IDS
@@ -34,41 +54,104 @@ static void write_file(const std::string & name, const void * data, size_t bytes
 	fclose(f);
 }
 
-#ifdef ORACLE_IDS
-// Primary-ray closest hits through the reference's own trace_primitives. The ray is built
-// with the same SIMD expressions as Raytracer.cpp:45-59 (lane size 1).
-static void dump_primary_hits(const Scene & scene, int width, int height, const std::string & prefix) {
-	static_assert(SIMD_LANE_SIZE == 1, "the id dump is a lane-1 build");
+// Primary ray for pixel (i, j), all lanes identical: the expressions of Raytracer.cpp:45-59.
+static Ray primary_ray(const Scene & scene, int i, int j) {
+	Ray ray;
+	ray.origin = SIMD_Vector3(scene.camera.position);
+#if RAY_DIFFERENTIALS_ENABLED
+	ray.dO_dx  = SIMD_Vector3(0.0f);
+	ray.dO_dy  = SIMD_Vector3(0.0f);
+#endif
+	SIMD_float is{float(i)};
+	SIMD_float js{float(j)};
 
+	SIMD_Vector3 direction = SIMD_Vector3::madd(scene.camera.rotated_x_axis, is,
+		SIMD_Vector3::madd(scene.camera.rotated_y_axis, js, scene.camera.rotated_top_left_corner));
+
+	SIMD_float d_dot_d  = SIMD_Vector3::dot(direction, direction);
+	SIMD_float inv_sqrt = SIMD_float::inv_sqrt(d_dot_d);
+	SIMD_float denom    = inv_sqrt / d_dot_d;
+#if RAY_DIFFERENTIALS_ENABLED
+	ray.dD_dx = (d_dot_d * scene.camera.rotated_x_axis - SIMD_Vector3::dot(direction, scene.camera.rotated_x_axis) * direction) * denom;
+	ray.dD_dy = (d_dot_d * scene.camera.rotated_y_axis - SIMD_Vector3::dot(direction, scene.camera.rotated_y_axis) * direction) * denom;
+#endif
+	ray.direction = direction * inv_sqrt;
+	return ray;
+}
+
+static PerformanceStats g_per_ray_stats = { 0, 0, 0, 0 };
+
+// One identical-lane packet per pixel through the reference's bounce(); rows are handed out
+// by an atomic counter to `threads` std::threads.
+static void render_per_ray(const Raytracer & raytracer, const Scene & scene, const Window & window, int threads) {
+	std::atomic<int> next_row(0);
+	std::vector<PerformanceStats> stats(threads, PerformanceStats { 0, 0, 0, 0 });
+	auto work = [&](int id) {
+		for (int j = next_row.fetch_add(1); j < window.height; j = next_row.fetch_add(1)) {
+			for (int i = 0; i < window.width; i++) {
+				Ray ray = primary_ray(scene, i, j);
+				stats[id].num_primary_rays++;
+				SIMD_float distance;
+				SIMD_Vector3 colour = raytracer.bounce(ray, NUMBER_OF_BOUNCES, distance, stats[id]);
+				window.plot(i, j, Vector3(colour.x[0], colour.y[0], colour.z[0]));
+			}
+		}
+	};
+	std::vector<std::thread> pool;
+	for (int t = 1; t < threads; t++) pool.emplace_back(work, t);
+	work(0);
+	for (auto & t : pool) t.join();
+
+	g_per_ray_stats = PerformanceStats { 0, 0, 0, 0 };
+	for (const auto & s : stats) {
+		g_per_ray_stats.num_primary_rays    += s.num_primary_rays;
+		g_per_ray_stats.num_shadow_rays     += s.num_shadow_rays;
+		g_per_ray_stats.num_reflection_rays += s.num_reflection_rays;
+		g_per_ray_stats.num_refraction_rays += s.num_refraction_rays;
+	}
+}
+
+// What Scene::update produced for this frame, for checking the host library against the
+// reference: PREFIX.fNNNN.frame = int32 instance_count, node_count; per instance float world[16],
+// inverse[16], aabb[6]; BVHNode nodes[node_count]; int32 indices[instance_count]; float camera[12].
+static void dump_frame_inputs(const Scene & scene, const std::string & prefix) {
+	FILE * f = fopen((prefix + ".frame").c_str(), "wb");
+	if (!f) return;
+	const TopLevelBVH & tlas = scene.top_level_bvh;
+	int counts[2] = { tlas.primitive_count, tlas.node_count };
+	fwrite(counts, sizeof(int), 2, f);
+	for (int i = 0; i < tlas.primitive_count; i++) {
+		fwrite(tlas.primitives[i].transform.world_matrix.cells, sizeof(float), 16, f);
+		fwrite(tlas.primitives[i].transform_inv.cells,          sizeof(float), 16, f);
+		fwrite(&tlas.primitives[i].aabb, sizeof(float), 6, f);
+	}
+	fwrite(tlas.nodes,   sizeof(BVHNode), tlas.node_count, f);
+	fwrite(tlas.indices, sizeof(int), tlas.primitive_count, f);
+	float camera[12] = {
+		scene.camera.position.x, scene.camera.position.y, scene.camera.position.z,
+		scene.camera.rotated_top_left_corner.x[0], scene.camera.rotated_top_left_corner.y[0], scene.camera.rotated_top_left_corner.z[0],
+		scene.camera.rotated_x_axis.x[0], scene.camera.rotated_x_axis.y[0], scene.camera.rotated_x_axis.z[0],
+		scene.camera.rotated_y_axis.x[0], scene.camera.rotated_y_axis.y[0], scene.camera.rotated_y_axis.z[0] };
+	fwrite(camera, sizeof(float), 12, f);
+	fclose(f);
+}
+
+#ifdef ORACLE_IDS
+// Primary-ray closest hits through the reference's own trace_primitives (identical-lane packet,
+// lane 0 read back).
+static void dump_primary_hits(const Scene & scene, int width, int height, const std::string & prefix) {
 	std::vector<int>   ids(size_t(width) * height * 2);
 	std::vector<float> hits(size_t(width) * height * 4);
 
 	for (int j = 0; j < height; j++) {
 		for (int i = 0; i < width; i++) {
-			Ray ray;
-			ray.origin = SIMD_Vector3(scene.camera.position);
-			ray.dO_dx  = SIMD_Vector3(0.0f);
-			ray.dO_dy  = SIMD_Vector3(0.0f);
-
-			SIMD_float is{float(i)};
-			SIMD_float js{float(j)};
-
-			SIMD_Vector3 direction = SIMD_Vector3::madd(scene.camera.rotated_x_axis, is,
-				SIMD_Vector3::madd(scene.camera.rotated_y_axis, js, scene.camera.rotated_top_left_corner));
-
-			SIMD_float d_dot_d  = SIMD_Vector3::dot(direction, direction);
-			SIMD_float inv_sqrt = SIMD_float::inv_sqrt(d_dot_d);
-			SIMD_float denom    = inv_sqrt / d_dot_d;
-
-			ray.dD_dx = (d_dot_d * scene.camera.rotated_x_axis - SIMD_Vector3::dot(direction, scene.camera.rotated_x_axis) * direction) * denom;
-			ray.dD_dy = (d_dot_d * scene.camera.rotated_y_axis - SIMD_Vector3::dot(direction, scene.camera.rotated_y_axis) * direction) * denom;
-			ray.direction = direction * inv_sqrt;
+			Ray ray = primary_ray(scene, i, j);
 
 			RayHit hit;
 			scene.trace_primitives(ray, hit);
 
 			size_t p = size_t(i) + size_t(width) * j;
-			bool is_hit = SIMD_float::mask(hit.hit) != 0;
+			bool is_hit = (SIMD_float::mask(hit.hit) & 1) != 0;
 
 			int instance = -1, triangle = -1;
 			if (is_hit) {
@@ -101,6 +184,7 @@ int main(int argc, char ** argv) {
 	float dt = 0.0f;
 	int   width = -1, height = -1;
 	bool  quiet = false;
+	bool  per_ray = false;
 	std::vector<int> dump_frames;
 
 	for (int a = 2; a < argc; a++) {
@@ -112,6 +196,7 @@ int main(int argc, char ** argv) {
 		else if (arg == "--width")  width  = atoi(next());
 		else if (arg == "--height") height = atoi(next());
 		else if (arg == "--quiet")  quiet = true;
+		else if (arg == "--per-ray") per_ray = true;
 		else if (arg == "--dump") {
 			std::string list(next());
 			size_t pos = 0;
@@ -134,8 +219,6 @@ int main(int argc, char ** argv) {
 	Texture::init();
 	MaterialBuffer::init();
 
-	FILE * saved_stdout = nullptr; (void)saved_stdout;
-
 	Scene * scene = new Scene(); // leaked on purpose, see SceneFromFile.cpp
 	scene->camera.resize(width, height);
 
@@ -154,15 +237,19 @@ int main(int argc, char ** argv) {
 
 		auto t1 = std::chrono::steady_clock::now();
 
-		WorkerThreads::wake_up_worker_threads(window.tile_count_x * window.tile_count_y);
-		WorkerThreads::wait_on_worker_threads();
+		if (per_ray) {
+			render_per_ray(raytracer, *scene, window, WorkerThreads_thread_count());
+		} else {
+			WorkerThreads::wake_up_worker_threads(window.tile_count_x * window.tile_count_y);
+			WorkerThreads::wait_on_worker_threads();
+		}
 
 		auto t2 = std::chrono::steady_clock::now();
 
 		ms_total .push_back(std::chrono::duration<double, std::milli>(t2 - t0).count());
 		ms_render.push_back(std::chrono::duration<double, std::milli>(t2 - t1).count());
 
-		last_stats = WorkerThreads::sum_performance_stats();
+		last_stats = per_ray ? g_per_ray_stats : WorkerThreads::sum_performance_stats();
 
 		if (!out_prefix.empty() && std::find(dump_frames.begin(), dump_frames.end(), frame) != dump_frames.end()) {
 			char tag[32]; snprintf(tag, sizeof(tag), ".f%04d", frame);
@@ -172,13 +259,14 @@ int main(int argc, char ** argv) {
 #ifdef ORACLE_IDS
 			dump_primary_hits(*scene, width, height, prefix);
 #endif
+			dump_frame_inputs(*scene, prefix);
 		}
 	}
 
 	if (!quiet) {
-		printf("{\"impl\": \"reference\", \"lanes\": %d, \"bounces\": %d, \"threads\": %d, \"width\": %d, \"height\": %d, \"frames\": %d, ",
-			SIMD_LANE_SIZE, NUMBER_OF_BOUNCES, WorkerThreads_thread_count(), width, height, frames);
-		printf("\"rays_packet_convention\": {\"primary\": %d, \"shadow\": %d, \"reflection\": %d, \"refraction\": %d}, ",
+		printf("{\"impl\": \"reference\", \"mode\": \"%s\", \"lanes\": %d, \"bounces\": %d, \"threads\": %d, \"width\": %d, \"height\": %d, \"frames\": %d, ",
+			per_ray ? "per-ray" : "packet", SIMD_LANE_SIZE, NUMBER_OF_BOUNCES, WorkerThreads_thread_count(), width, height, frames);
+		printf("\"rays\": {\"primary\": %d, \"shadow\": %d, \"reflection\": %d, \"refraction\": %d}, ",
 			last_stats.num_primary_rays, last_stats.num_shadow_rays, last_stats.num_reflection_rays, last_stats.num_refraction_rays);
 		printf("\"ms_total\": [");
 		for (size_t i = 0; i < ms_total.size(); i++) printf("%s%.4f", i ? ", " : "", ms_total[i]);
