@@ -1,0 +1,491 @@
+// b200rt.cu — the C ABI of include/b200rt.h over the sm_100a kernels (kernels.cuh).
+//
+// There is no CPU fallback in this library: every entry point either runs the CUDA path or
+// returns an error.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "kernels.cuh"
+
+using namespace rt;
+
+namespace {
+
+std::string g_create_error;
+
+struct DeviceBuffer {
+	void * ptr = nullptr; size_t bytes = 0;
+	cudaError_t ensure(size_t n) {
+		if (n <= bytes) return cudaSuccess;
+		if (ptr) cudaFree(ptr);
+		ptr = nullptr; bytes = 0;
+		cudaError_t e = cudaMalloc(&ptr, n ? n : 16);
+		if (e == cudaSuccess) bytes = n;
+		return e;
+	}
+	void release() { if (ptr) cudaFree(ptr); ptr = nullptr; bytes = 0; }
+};
+
+} // namespace
+
+struct b200rt_ctx {
+	b200rt_config config;
+	std::string   error;
+	cudaStream_t  stream = nullptr;
+	cudaEvent_t   ev[4] = { nullptr, nullptr, nullptr, nullptr }; // total begin, render begin, render end / fxaa begin, fxaa end
+
+	// static scene in HBM
+	DeviceBuffer nodes, hot, cold, materials, textures, texels, sky, gamma;
+	int sky_size = 0;
+	bool have_static = false;
+	std::vector<b200rt_blas> blas;
+
+	// per-frame data: one pinned staging block + one device block, sub-allocated
+	DeviceBuffer frame_block;
+	void * frame_staging = nullptr; size_t frame_staging_bytes = 0;
+
+	// outputs
+	DeviceBuffer frame_buffer, presented, colour_float, ids, hits, counters;
+	void * pinned_out = nullptr; size_t pinned_out_bytes = 0;
+	FrameCounters * pinned_counters = nullptr;
+
+	SceneParams params;      // last frame's parameters (for b200rt_time_resident)
+	bool have_frame = false;
+	int  num_sms = 0, blocks_per_sm = 0;
+};
+
+#define CHECK_CUDA(ctx, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { (ctx)->error = std::string(#call) + ": " + cudaGetErrorString(e_); return -1; } } while (0)
+
+static int fail(b200rt_ctx * ctx, const std::string & message) { ctx->error = message; return -1; }
+
+extern "C" const char * b200rt_last_error(const b200rt_ctx * ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
+
+extern "C" uint64_t b200rt_stream(const b200rt_ctx * ctx) { return ctx ? uint64_t(reinterpret_cast<uintptr_t>(ctx->stream)) : 0; }
+
+extern "C" int b200rt_create(const b200rt_config * config, b200rt_ctx ** out) {
+	if (!config || !out) { g_create_error = "null argument"; return -1; }
+	*out = nullptr;
+	if (config->width <= 0 || config->height <= 0) { g_create_error = "bad resolution"; return -1; }
+	if (config->bounces < 0 || config->bounces > RT_MAX_BOUNCES) { g_create_error = "bounces must be in 0..8"; return -1; }
+	if (config->mipmap_filter < 0 || config->mipmap_filter > 2) { g_create_error = "bad mipmap_filter"; return -1; }
+	if (config->tile_stride < 1 || config->tile_phase < 0 || config->tile_phase >= config->tile_stride) { g_create_error = "bad tile partition"; return -1; }
+
+	int device_count = 0;
+	cudaError_t e = cudaGetDeviceCount(&device_count);
+	if (e != cudaSuccess || device_count == 0) { g_create_error = std::string("no CUDA device: ") + cudaGetErrorString(e); return -1; }
+	if (config->device < 0 || config->device >= device_count) { g_create_error = "bad device ordinal"; return -1; }
+	if ((e = cudaSetDevice(config->device)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); return -1; }
+
+	b200rt_ctx * ctx = new b200rt_ctx();
+	ctx->config = *config;
+	memset(&ctx->params, 0, sizeof(ctx->params));
+
+	auto bail = [&](const char * what, cudaError_t err) { g_create_error = std::string(what) + ": " + cudaGetErrorString(err); b200rt_destroy(ctx); return -1; };
+
+	if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
+	for (auto & ev : ctx->ev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) return bail("cudaEventCreate", e);
+
+	cudaDeviceProp prop;
+	if ((e = cudaGetDeviceProperties(&prop, config->device)) != cudaSuccess) return bail("cudaGetDeviceProperties", e);
+	ctx->num_sms = prop.multiProcessorCount;
+	if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->blocks_per_sm, render_kernel<false>, RT_BLOCK_THREADS, 0)) != cudaSuccess) return bail("occupancy query (is this an sm_100a device?)", e);
+	if (ctx->blocks_per_sm < 1) ctx->blocks_per_sm = 1;
+
+	// Texture::init (Texture.h:53-62) and the gamma table of get_screen() (fragment_fxaa.glsl:16-18)
+	float ewa[128];
+	{
+		const float alpha = 2.0f, denom = 1.0f / 127.0f, exp_neg_alpha = expf(-alpha);
+		for (int i = 0; i < 128; i++) ewa[i] = expf(-alpha * (float(i) * denom)) - exp_neg_alpha;
+	}
+	if ((e = cudaMemcpyToSymbol(c_ewa_weight_table, ewa, sizeof(ewa))) != cudaSuccess) return bail("cudaMemcpyToSymbol", e);
+
+	float gamma[256];
+	for (int i = 0; i < 256; i++) gamma[i] = powf(float(i) / 255.0f, 1.0f / 2.2f);
+	if ((e = ctx->gamma.ensure(sizeof(gamma))) != cudaSuccess) return bail("cudaMalloc", e);
+	if ((e = cudaMemcpy(ctx->gamma.ptr, gamma, sizeof(gamma), cudaMemcpyHostToDevice)) != cudaSuccess) return bail("cudaMemcpy", e);
+
+	const size_t pixels = size_t(config->width) * config->height;
+	if ((e = ctx->frame_buffer.ensure(pixels * 4)) != cudaSuccess) return bail("cudaMalloc", e);
+	if ((e = ctx->presented.ensure(pixels * 3 + 16)) != cudaSuccess) return bail("cudaMalloc", e);
+	if ((e = ctx->counters.ensure(sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMalloc", e);
+	if ((e = cudaMemset(ctx->frame_buffer.ptr, 0, pixels * 4)) != cudaSuccess) return bail("cudaMemset", e);
+	if ((e = cudaMallocHost(reinterpret_cast<void **>(&ctx->pinned_counters), sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMallocHost", e);
+
+	*out = ctx;
+	return 0;
+}
+
+extern "C" void b200rt_destroy(b200rt_ctx * ctx) {
+	if (!ctx) return;
+	cudaSetDevice(ctx->config.device);
+	if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+	for (DeviceBuffer * b : { &ctx->nodes, &ctx->hot, &ctx->cold, &ctx->materials, &ctx->textures, &ctx->texels, &ctx->sky, &ctx->gamma,
+	                          &ctx->frame_block, &ctx->frame_buffer, &ctx->presented, &ctx->colour_float, &ctx->ids, &ctx->hits, &ctx->counters }) b->release();
+	if (ctx->frame_staging) cudaFreeHost(ctx->frame_staging);
+	if (ctx->pinned_out) cudaFreeHost(ctx->pinned_out);
+	if (ctx->pinned_counters) cudaFreeHost(ctx->pinned_counters);
+	for (auto & ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+	if (ctx->stream) cudaStreamDestroy(ctx->stream);
+	delete ctx;
+}
+
+// ------------------------------------------------------------------------ static upload ---
+static int upload(b200rt_ctx * ctx, DeviceBuffer & buffer, const void * host, size_t bytes) {
+	CHECK_CUDA(ctx, buffer.ensure(bytes));
+	if (bytes) CHECK_CUDA(ctx, cudaMemcpy(buffer.ptr, host, bytes, cudaMemcpyHostToDevice));
+	return 0;
+}
+
+extern "C" int b200rt_upload_static(b200rt_ctx * ctx, const b200rt_static_scene * s) {
+	if (!ctx) return -1;
+	if (!s) return fail(ctx, "null scene");
+	CHECK_CUDA(ctx, cudaSetDevice(ctx->config.device));
+
+	if (s->node_count <= 0 || s->triangle_count <= 0 || s->blas_count <= 0 || !s->nodes || !s->triangles_hot || !s->triangles_cold || !s->blas) return fail(ctx, "static scene needs at least one BLAS with nodes and triangles");
+	if (s->material_count <= 0 || s->material_count > 256 || !s->materials) return fail(ctx, "material_count must be in 1..256 (MAX_MATERIALS, Config.h:18)");
+	if (s->sky_size <= 0 || !s->sky) return fail(ctx, "a sky probe is required (Sky.cpp:11)");
+	if (s->texture_count < 0 || (s->texture_count > 0 && (!s->textures || !s->texels))) return fail(ctx, "bad texture arrays");
+
+	// validate indices: the kernels trust them
+	for (int b = 0; b < s->blas_count; b++) {
+		const b200rt_blas & d = s->blas[b];
+		if (d.node_offset < 0 || d.node_count <= 0 || d.node_offset + d.node_count > s->node_count || d.triangle_offset < 0 || d.triangle_count < 0 || d.triangle_offset + d.triangle_count > s->triangle_count) return fail(ctx, "BLAS range out of bounds");
+		for (int n = 0; n < d.node_count; n++) {
+			const b200rt_bvh_node & node = s->nodes[d.node_offset + n];
+			const int count = node.count & 0x3FFFFFFF;
+			if (count > 0) { if (node.left_or_first < 0 || node.left_or_first + count > d.triangle_count) return fail(ctx, "BLAS leaf range out of bounds"); }
+			else if ((unsigned(node.count) >> 30) != 0 && (node.left_or_first < 0 || node.left_or_first + 1 >= d.node_count)) return fail(ctx, "BLAS child index out of bounds");
+		}
+		for (int t = 0; t < d.triangle_count; t++) {
+			const int m = d.material_offset + s->triangles_cold[d.triangle_offset + t].material_id;
+			if (m < 0 || m >= s->material_count) return fail(ctx, "triangle material id out of range");
+		}
+	}
+	for (int m = 0; m < s->material_count; m++) if (s->materials[m].texture >= s->texture_count) return fail(ctx, "material texture index out of range");
+	for (int t = 0; t < s->texture_count; t++) {
+		const b200rt_texture & tex = s->textures[t];
+		if (tex.width <= 0 || tex.height <= 0 || tex.mip_levels < 1 || tex.mip_levels > B200RT_MAX_MIP_LEVELS || tex.texel_offset < 0) return fail(ctx, "bad texture descriptor");
+		const int last = tex.mip_levels - 1;
+		const int64_t end = tex.texel_offset + tex.mip_offsets[last] + int64_t(std::max(tex.width >> last, 1)) * std::max(tex.height >> last, 1);
+		if (end > s->texel_count) return fail(ctx, "texture pyramid exceeds the texel pool");
+	}
+
+	// BVH nodes: same 32 bytes, viewed as two float4
+	if (upload(ctx, ctx->nodes, s->nodes, size_t(s->node_count) * sizeof(b200rt_bvh_node))) return -1;
+
+	{ // TriangleHot 36 B -> 48 B (three aligned float4)
+		std::vector<float> packed(size_t(s->triangle_count) * 12, 0.0f);
+		for (int i = 0; i < s->triangle_count; i++) memcpy(&packed[size_t(i) * 12], &s->triangles_hot[i], sizeof(b200rt_triangle_hot));
+		if (upload(ctx, ctx->hot, packed.data(), packed.size() * sizeof(float))) return -1;
+	}
+	if (upload(ctx, ctx->cold, s->triangles_cold, size_t(s->triangle_count) * sizeof(b200rt_triangle_cold))) return -1;
+
+	{ // Material -> three float4
+		std::vector<DeviceMaterial> packed(s->material_count);
+		for (int i = 0; i < s->material_count; i++) {
+			const b200rt_material & m = s->materials[i];
+			int texture = m.texture < 0 ? -1 : m.texture;
+			float texture_bits; memcpy(&texture_bits, &texture, 4);
+			packed[i].diffuse_texture = make_float4(m.diffuse[0], m.diffuse[1], m.diffuse[2], texture_bits);
+			packed[i].reflection_ior  = make_float4(m.reflection[0], m.reflection[1], m.reflection[2], m.index_of_refraction);
+			packed[i].transmittance   = make_float4(m.transmittance[0], m.transmittance[1], m.transmittance[2], 0.0f);
+		}
+		if (upload(ctx, ctx->materials, packed.data(), packed.size() * sizeof(DeviceMaterial))) return -1;
+	}
+	{
+		std::vector<DeviceTexture> packed(std::max(s->texture_count, 1));
+		memset(packed.data(), 0, packed.size() * sizeof(DeviceTexture));
+		for (int i = 0; i < s->texture_count; i++) {
+			const b200rt_texture & t = s->textures[i];
+			packed[i].texel_offset = t.texel_offset; packed[i].width = t.width; packed[i].height = t.height;
+			packed[i].mipmapped = t.mipmapped; packed[i].mip_levels = t.mip_levels;
+			memcpy(packed[i].mip_offsets, t.mip_offsets, sizeof(t.mip_offsets));
+		}
+		if (upload(ctx, ctx->textures, packed.data(), packed.size() * sizeof(DeviceTexture))) return -1;
+	}
+	{ // texels and sky: float3 -> float4, in chunks to bound the host staging memory
+		auto upload_rgb = [&](DeviceBuffer & buffer, const float * rgb, size_t count) -> int {
+			CHECK_CUDA(ctx, buffer.ensure(std::max<size_t>(count, 1) * sizeof(float4)));
+			const size_t chunk = size_t(1) << 22;
+			std::vector<float4> staging(std::min(count, chunk));
+			for (size_t base = 0; base < count; base += chunk) {
+				const size_t n = std::min(chunk, count - base);
+				for (size_t i = 0; i < n; i++) staging[i] = make_float4(rgb[(base + i) * 3], rgb[(base + i) * 3 + 1], rgb[(base + i) * 3 + 2], 0.0f);
+				CHECK_CUDA(ctx, cudaMemcpy(static_cast<float4 *>(buffer.ptr) + base, staging.data(), n * sizeof(float4), cudaMemcpyHostToDevice));
+			}
+			return 0;
+		};
+		if (upload_rgb(ctx->texels, s->texels, size_t(s->texel_count))) return -1;
+		if (upload_rgb(ctx->sky, s->sky, size_t(s->sky_size) * s->sky_size + 1)) return -1; // + the pad texel (Sky.cpp:45)
+	}
+	ctx->sky_size = s->sky_size;
+	ctx->blas.assign(s->blas, s->blas + s->blas_count);
+	ctx->have_static = true;
+	ctx->have_frame = false;
+	return 0;
+}
+
+// ------------------------------------------------------------------------- per frame ---
+static size_t align16(size_t n) { return (n + 15) & ~size_t(15); }
+
+// Validates the frame, packs it into the pinned staging block and issues ONE host->device copy.
+static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
+	if (!ctx->have_static) return fail(ctx, "b200rt_upload_static has not been called");
+	if (!f) return fail(ctx, "null frame");
+	if (f->instance_count <= 0 || !f->instances || !f->tlas_nodes || !f->tlas_indices || f->tlas_node_count <= 0) return fail(ctx, "frame needs at least one instance and a TLAS (TopLevelBVH.cpp:6)");
+	if (f->sphere_count < 0 || f->plane_count < 0 || f->light_count < 0) return fail(ctx, "negative count");
+
+	const int material_count = int(ctx->materials.bytes / sizeof(DeviceMaterial));
+	for (int i = 0; i < f->instance_count; i++) {
+		if (f->instances[i].blas < 0 || f->instances[i].blas >= int(ctx->blas.size())) return fail(ctx, "instance BLAS index out of range");
+		if (f->tlas_indices[i] < 0 || f->tlas_indices[i] >= f->instance_count) return fail(ctx, "TLAS primitive index out of range");
+	}
+	for (int n = 0; n < f->tlas_node_count; n++) {
+		const b200rt_bvh_node & node = f->tlas_nodes[n];
+		const int count = node.count & 0x3FFFFFFF;
+		if (count > 0) { if (node.left_or_first < 0 || node.left_or_first + count > f->instance_count) return fail(ctx, "TLAS leaf range out of bounds"); }
+		else if ((unsigned(node.count) >> 30) != 0 && (node.left_or_first < 0 || node.left_or_first + 1 >= f->tlas_node_count)) return fail(ctx, "TLAS child index out of bounds");
+	}
+	for (int i = 0; i < f->sphere_count; i++) if (f->spheres[i].material_id < 0 || f->spheres[i].material_id >= material_count) return fail(ctx, "sphere material id out of range");
+	for (int i = 0; i < f->plane_count;  i++) if (f->planes[i].material_id  < 0 || f->planes[i].material_id  >= material_count) return fail(ctx, "plane material id out of range");
+	for (int i = 0; i < f->light_count; i++) {
+		if (f->lights[i].kind < 0 || f->lights[i].kind > 2) return fail(ctx, "bad light kind");
+		if (i > 0 && f->lights[i].kind < f->lights[i - 1].kind) return fail(ctx, "lights must be ordered point, spot, directional (Raytracer.cpp:155-198)");
+	}
+
+	const size_t off_nodes     = 0;
+	const size_t off_indices   = off_nodes     + align16(size_t(f->tlas_node_count) * sizeof(b200rt_bvh_node));
+	const size_t off_instances = off_indices   + align16(size_t(f->instance_count) * sizeof(int));
+	const size_t off_spheres   = off_instances + size_t(f->instance_count) * sizeof(DeviceInstance);
+	const size_t off_planes    = off_spheres   + size_t(f->sphere_count) * sizeof(DeviceSphere);
+	const size_t off_lights    = off_planes    + size_t(f->plane_count) * sizeof(DevicePlane);
+	const size_t total         = off_lights    + size_t(f->light_count) * sizeof(DeviceLight);
+
+	if (total > ctx->frame_staging_bytes) {
+		if (ctx->frame_staging) cudaFreeHost(ctx->frame_staging);
+		ctx->frame_staging = nullptr; ctx->frame_staging_bytes = 0;
+		CHECK_CUDA(ctx, cudaMallocHost(&ctx->frame_staging, total * 2));
+		ctx->frame_staging_bytes = total * 2;
+	}
+	CHECK_CUDA(ctx, ctx->frame_block.ensure(total));
+
+	char * base = static_cast<char *>(ctx->frame_staging);
+	memcpy(base + off_nodes,   f->tlas_nodes,   size_t(f->tlas_node_count) * sizeof(b200rt_bvh_node));
+	memcpy(base + off_indices, f->tlas_indices, size_t(f->instance_count) * sizeof(int));
+
+	auto as_float = [](int v) { float r; memcpy(&r, &v, 4); return r; };
+
+	DeviceInstance * instances = reinterpret_cast<DeviceInstance *>(base + off_instances);
+	for (int i = 0; i < f->instance_count; i++) {
+		const b200rt_instance & in = f->instances[i];
+		const b200rt_blas & blas = ctx->blas[in.blas];
+		// Matrix4 cells[i + 4j]: the first twelve floats are the three rows the transforms use (Matrix4.h:39-85)
+		memcpy(&instances[i].inverse, in.inverse, 12 * sizeof(float));
+		memcpy(&instances[i].world,   in.world,   12 * sizeof(float));
+		instances[i].node_offset = blas.node_offset; instances[i].triangle_offset = blas.triangle_offset;
+		instances[i].material_offset = blas.material_offset; instances[i].pad = 0;
+		memset(instances[i].reserved, 0, sizeof(instances[i].reserved));
+	}
+	DeviceSphere * spheres = reinterpret_cast<DeviceSphere *>(base + off_spheres);
+	for (int i = 0; i < f->sphere_count; i++) {
+		const b200rt_sphere & s = f->spheres[i];
+		spheres[i].center_r2 = make_float4(s.center[0], s.center[1], s.center[2], s.radius_squared);
+		spheres[i].rinv_mat  = make_float4(s.radius_inv, as_float(s.material_id), 0.0f, 0.0f);
+	}
+	DevicePlane * planes = reinterpret_cast<DevicePlane *>(base + off_planes);
+	for (int i = 0; i < f->plane_count; i++) {
+		const b200rt_plane & p = f->planes[i];
+		planes[i].normal_d   = make_float4(p.normal[0], p.normal[1], p.normal[2], p.distance);
+		planes[i].u_axis_mat = make_float4(p.u_axis[0], p.u_axis[1], p.u_axis[2], as_float(p.material_id));
+		planes[i].v_axis     = make_float4(p.v_axis[0], p.v_axis[1], p.v_axis[2], 0.0f);
+	}
+	DeviceLight * lights = reinterpret_cast<DeviceLight *>(base + off_lights);
+	for (int i = 0; i < f->light_count; i++) {
+		const b200rt_light & l = f->lights[i];
+		lights[i].colour_kind    = make_float4(l.colour[0], l.colour[1], l.colour[2], as_float(l.kind));
+		lights[i].position_inner = make_float4(l.position[0], l.position[1], l.position[2], l.inner_cutoff);
+		lights[i].negdir_outer   = make_float4(l.negative_direction[0], l.negative_direction[1], l.negative_direction[2], l.outer_cutoff);
+	}
+
+	CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->frame_block.ptr, base, total, cudaMemcpyHostToDevice, ctx->stream));
+
+	const char * dev = static_cast<const char *>(ctx->frame_block.ptr);
+	SceneParams & P = ctx->params;
+	P.nodes = static_cast<const float4 *>(ctx->nodes.ptr);
+	P.triangles_hot = static_cast<const float4 *>(ctx->hot.ptr);
+	P.triangles_cold = static_cast<const float4 *>(ctx->cold.ptr);
+	P.materials = static_cast<const DeviceMaterial *>(ctx->materials.ptr);
+	P.textures = static_cast<const DeviceTexture *>(ctx->textures.ptr);
+	P.texels = static_cast<const float4 *>(ctx->texels.ptr);
+	P.sky = static_cast<const float4 *>(ctx->sky.ptr);
+	P.sky_size = ctx->sky_size;
+	P.tlas_nodes   = reinterpret_cast<const float4 *>(dev + off_nodes);
+	P.tlas_indices = reinterpret_cast<const int *>(dev + off_indices);
+	P.instances    = reinterpret_cast<const DeviceInstance *>(dev + off_instances);
+	P.spheres      = reinterpret_cast<const DeviceSphere *>(dev + off_spheres);
+	P.planes       = reinterpret_cast<const DevicePlane *>(dev + off_planes);
+	P.lights       = reinterpret_cast<const DeviceLight *>(dev + off_lights);
+	P.sphere_count = f->sphere_count; P.plane_count = f->plane_count; P.light_count = f->light_count;
+	for (int c = 0; c < 3; c++) {
+		P.cam_position[c] = f->camera.position[c]; P.cam_top_left[c] = f->camera.top_left_corner[c];
+		P.cam_x_axis[c] = f->camera.x_axis[c];     P.cam_y_axis[c] = f->camera.y_axis[c];
+		P.ambient[c] = f->ambient[c];
+	}
+	const b200rt_config & c = ctx->config;
+	P.width = c.width; P.height = c.height; P.bounces = c.bounces; P.mipmap_filter = c.mipmap_filter; P.max_anisotropy = c.max_anisotropy;
+	P.tiles_x = (c.width + 31) / 32; P.tiles_y = (c.height + 31) / 32; // Window.cpp:11-12
+	P.tile_stride = c.tile_stride; P.tile_phase = c.tile_phase;
+	const int tiles = P.tiles_x * P.tiles_y;
+	P.tile_count_mine = tiles > c.tile_phase ? (tiles - c.tile_phase + c.tile_stride - 1) / c.tile_stride : 0;
+
+	ctx->have_frame = true;
+	return 0;
+}
+
+// Launches the render kernel over this context's tiles. frame_buffer is a device pointer.
+static int launch_render(b200rt_ctx * ctx, unsigned * frame_buffer, float * colour_float, bool count) {
+	CHECK_CUDA(ctx, cudaMemsetAsync(ctx->counters.ptr, 0, sizeof(FrameCounters), ctx->stream));
+	const unsigned total_warps = unsigned(ctx->params.tile_count_mine) * 32u;
+	if (total_warps == 0) return 0;
+	// persistent grid: every SM filled to the occupancy limit, never more warps than units
+	unsigned blocks = unsigned(ctx->num_sms) * unsigned(ctx->blocks_per_sm);
+	const unsigned needed = (total_warps + RT_BLOCK_THREADS / 32 - 1) / (RT_BLOCK_THREADS / 32);
+	if (blocks > needed) blocks = needed;
+	FrameCounters * counters = static_cast<FrameCounters *>(ctx->counters.ptr);
+	if (count) render_kernel<true ><<<blocks, RT_BLOCK_THREADS, 0, ctx->stream>>>(ctx->params, frame_buffer, colour_float, counters);
+	else       render_kernel<false><<<blocks, RT_BLOCK_THREADS, 0, ctx->stream>>>(ctx->params, frame_buffer, colour_float, counters);
+	CHECK_CUDA(ctx, cudaGetLastError());
+	return 0;
+}
+
+static int launch_fxaa(b200rt_ctx * ctx, const unsigned * frame_buffer, unsigned char * presented) {
+	const dim3 block(FXAA_TILE_W, FXAA_TILE_H);
+	const dim3 grid((ctx->config.width + FXAA_TILE_W - 1) / FXAA_TILE_W, (ctx->config.height + FXAA_TILE_H - 1) / FXAA_TILE_H);
+	fxaa_kernel<<<grid, block, 0, ctx->stream>>>(frame_buffer, presented, static_cast<const float *>(ctx->gamma.ptr), ctx->config.width, ctx->config.height, ctx->config.enable_fxaa);
+	CHECK_CUDA(ctx, cudaGetLastError());
+	return 0;
+}
+
+static void fill_stats(b200rt_ctx * ctx, b200rt_stats * stats) {
+	const FrameCounters & c = *ctx->pinned_counters;
+	stats->primary_rays = c.primary; stats->shadow_rays = c.shadow; stats->reflection_rays = c.reflection; stats->refraction_rays = c.refraction;
+	stats->nodes_visited = c.nodes; stats->triangles_tested = c.triangles; stats->texels_fetched = c.texels;
+	stats->device_ms_render = stats->device_ms_fxaa = stats->device_ms_total = 0.0f;
+	cudaEventElapsedTime(&stats->device_ms_render, ctx->ev[1], ctx->ev[2]);
+	cudaEventElapsedTime(&stats->device_ms_fxaa,   ctx->ev[2], ctx->ev[3]);
+}
+
+extern "C" int b200rt_render_frame(b200rt_ctx * ctx, const b200rt_frame * frame, const b200rt_outputs * out) {
+	if (!ctx) return -1;
+	if (!out) return fail(ctx, "null outputs");
+	CHECK_CUDA(ctx, cudaSetDevice(ctx->config.device));
+
+	const size_t pixels = size_t(ctx->config.width) * ctx->config.height;
+	const size_t off_fb = 0, off_rgb = align16(pixels * 4), pinned_total = off_rgb + align16(pixels * 3);
+	if (pinned_total > ctx->pinned_out_bytes) {
+		if (ctx->pinned_out) cudaFreeHost(ctx->pinned_out);
+		ctx->pinned_out = nullptr; ctx->pinned_out_bytes = 0;
+		CHECK_CUDA(ctx, cudaMallocHost(&ctx->pinned_out, pinned_total));
+		ctx->pinned_out_bytes = pinned_total;
+	}
+	if (out->colour_float) CHECK_CUDA(ctx, ctx->colour_float.ensure(pixels * 12));
+	if (out->primary_ids)  CHECK_CUDA(ctx, ctx->ids.ensure(pixels * 8));
+	if (out->primary_hit)  CHECK_CUDA(ctx, ctx->hits.ensure(pixels * 16));
+
+	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
+	if (stage_frame(ctx, frame)) return -1;
+
+	unsigned * fb = static_cast<unsigned *>(ctx->frame_buffer.ptr);
+	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+	if (launch_render(ctx, fb, out->colour_float ? static_cast<float *>(ctx->colour_float.ptr) : nullptr, ctx->config.count_traversal != 0)) return -1;
+	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
+	if (out->presented_rgb8 && launch_fxaa(ctx, fb, static_cast<unsigned char *>(ctx->presented.ptr))) return -1;
+	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));
+
+	if (out->primary_ids || out->primary_hit) {
+		const dim3 grid((ctx->config.width + 31) / 32, (ctx->config.height + 7) / 8);
+		primary_hits_kernel<<<grid, RT_BLOCK_THREADS, 0, ctx->stream>>>(ctx->params, out->primary_ids ? static_cast<int *>(ctx->ids.ptr) : nullptr, out->primary_hit ? static_cast<float *>(ctx->hits.ptr) : nullptr);
+		CHECK_CUDA(ctx, cudaGetLastError());
+	}
+
+	// device -> pinned host, then one synchronisation
+	char * pinned = static_cast<char *>(ctx->pinned_out);
+	if (out->frame_buffer)   CHECK_CUDA(ctx, cudaMemcpyAsync(pinned + off_fb,  fb, pixels * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (out->presented_rgb8) CHECK_CUDA(ctx, cudaMemcpyAsync(pinned + off_rgb, ctx->presented.ptr, pixels * 3, cudaMemcpyDeviceToHost, ctx->stream));
+	CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->pinned_counters, ctx->counters.ptr, sizeof(FrameCounters), cudaMemcpyDeviceToHost, ctx->stream));
+	if (out->colour_float) CHECK_CUDA(ctx, cudaMemcpyAsync(out->colour_float, ctx->colour_float.ptr, pixels * 12, cudaMemcpyDeviceToHost, ctx->stream));
+	if (out->primary_ids)  CHECK_CUDA(ctx, cudaMemcpyAsync(out->primary_ids, ctx->ids.ptr, pixels * 8, cudaMemcpyDeviceToHost, ctx->stream));
+	if (out->primary_hit)  CHECK_CUDA(ctx, cudaMemcpyAsync(out->primary_hit, ctx->hits.ptr, pixels * 16, cudaMemcpyDeviceToHost, ctx->stream));
+	cudaEvent_t end = ctx->ev[0]; // reuse: total = ev[0] .. now, measured with a fresh record on a temp event
+	cudaEvent_t total_end;
+	CHECK_CUDA(ctx, cudaEventCreate(&total_end));
+	CHECK_CUDA(ctx, cudaEventRecord(total_end, ctx->stream));
+	cudaError_t sync = cudaStreamSynchronize(ctx->stream);
+	if (sync != cudaSuccess) { cudaEventDestroy(total_end); ctx->error = std::string("render failed: ") + cudaGetErrorString(sync); return -1; }
+
+	if (out->frame_buffer)   memcpy(out->frame_buffer,   pinned + off_fb,  pixels * 4);
+	if (out->presented_rgb8) memcpy(out->presented_rgb8, pinned + off_rgb, pixels * 3);
+	if (out->stats) {
+		fill_stats(ctx, out->stats);
+		cudaEventElapsedTime(&out->stats->device_ms_total, end, total_end);
+	}
+	cudaEventDestroy(total_end);
+	return 0;
+}
+
+extern "C" int b200rt_render_frame_device(b200rt_ctx * ctx, const b200rt_frame * frame, uint64_t frame_buffer_dev, b200rt_stats * stats) {
+	if (!ctx) return -1;
+	if (!frame_buffer_dev) return fail(ctx, "null device frame buffer");
+	CHECK_CUDA(ctx, cudaSetDevice(ctx->config.device));
+	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
+	if (stage_frame(ctx, frame)) return -1;
+	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+	if (launch_render(ctx, reinterpret_cast<unsigned *>(uintptr_t(frame_buffer_dev)), nullptr, false)) return -1;
+	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
+	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));
+	CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->pinned_counters, ctx->counters.ptr, sizeof(FrameCounters), cudaMemcpyDeviceToHost, ctx->stream));
+	CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	if (stats) { fill_stats(ctx, stats); cudaEventElapsedTime(&stats->device_ms_total, ctx->ev[0], ctx->ev[3]); }
+	return 0;
+}
+
+extern "C" int b200rt_present_device(b200rt_ctx * ctx, uint64_t frame_buffer_dev, uint64_t presented_dev, float * device_ms) {
+	if (!ctx) return -1;
+	if (!frame_buffer_dev || !presented_dev) return fail(ctx, "null device pointer");
+	CHECK_CUDA(ctx, cudaSetDevice(ctx->config.device));
+	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
+	if (launch_fxaa(ctx, reinterpret_cast<const unsigned *>(uintptr_t(frame_buffer_dev)), reinterpret_cast<unsigned char *>(uintptr_t(presented_dev)))) return -1;
+	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));
+	CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	if (device_ms) cudaEventElapsedTime(device_ms, ctx->ev[2], ctx->ev[3]);
+	return 0;
+}
+
+extern "C" int b200rt_time_resident(b200rt_ctx * ctx, int repeat, float * ms_render, float * ms_fxaa) {
+	if (!ctx) return -1;
+	if (!ctx->have_frame) return fail(ctx, "no frame has been rendered yet");
+	if (repeat < 1) repeat = 1;
+	CHECK_CUDA(ctx, cudaSetDevice(ctx->config.device));
+	unsigned * fb = static_cast<unsigned *>(ctx->frame_buffer.ptr);
+	float total_render = 0.0f, total_fxaa = 0.0f;
+	for (int i = 0; i < repeat; i++) {
+		CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+		if (launch_render(ctx, fb, nullptr, false)) return -1;
+		CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
+		if (launch_fxaa(ctx, fb, static_cast<unsigned char *>(ctx->presented.ptr))) return -1;
+		CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));
+		CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+		float a = 0.0f, b = 0.0f;
+		cudaEventElapsedTime(&a, ctx->ev[1], ctx->ev[2]);
+		cudaEventElapsedTime(&b, ctx->ev[2], ctx->ev[3]);
+		total_render += a; total_fxaa += b;
+	}
+	if (ms_render) *ms_render = total_render / float(repeat);
+	if (ms_fxaa)   *ms_fxaa   = total_fxaa / float(repeat);
+	return 0;
+}

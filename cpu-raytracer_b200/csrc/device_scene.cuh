@@ -1,0 +1,76 @@
+// device_scene.cuh — how the scene lies in HBM.
+//
+// Everything a ray touches is stored as 16-byte aligned records read with LDG.128:
+//   BVH node      32 B = 2 x float4   {min.xyz, max.x} {max.yz, left_or_first, count}   (BVHNode.h:10-16, same bytes)
+//   TriangleHot   48 B = 3 x float4   {p0.xyz, e1.x} {e1.yz, e2.xy} {e2.z, -, -, -}      (36 B of payload, BottomLevelBVH.h:6-10)
+//   TriangleCold  64 B = 4 x float4   same bytes as BottomLevelBVH.h:12-22
+//   texel         16 B = float4       linear RGB + pad                                   (12 B of payload, Texture.cpp:146)
+//   instance     128 B = 8 x float4   inverse rows 0-2, world rows 0-2, {node_offset, triangle_offset, material_offset, -}
+// The child pair of an inner node (left, left + 1) is one aligned 64-byte line, as in the
+// reference (root 0, node 1 unused, BottomLevelBVH.cpp:92,132).
+#pragma once
+#include "rt_math.cuh"
+#include "../../include/b200rt.h"
+
+namespace rt {
+
+struct DeviceInstance {
+	Affine inverse;   // Mesh::transform_inv
+	Affine world;     // Transform::world_matrix
+	int node_offset, triangle_offset, material_offset, pad;
+	int reserved[4];    // keeps the record at 128 bytes (one L2 line)
+};
+static_assert(sizeof(DeviceInstance) == 128, "instance record is 128 bytes");
+
+struct DeviceTexture {   // Texture.h:8-18
+	long long texel_offset;
+	int width, height;
+	int mipmapped, mip_levels;
+	int mip_offsets[B200RT_MAX_MIP_LEVELS];
+};
+
+struct DeviceMaterial {  // Material.h:7-14, 48 bytes
+	float4 diffuse_texture;      // diffuse.xyz, as_float(texture index)
+	float4 reflection_ior;       // reflection.xyz, index_of_refraction
+	float4 transmittance;        // transmittance.xyz, -
+};
+
+struct DeviceSphere { float4 center_r2; float4 rinv_mat; };                  // centre.xyz, radius^2 | 1/radius, as_float(material id)
+struct DevicePlane  { float4 normal_d; float4 u_axis_mat; float4 v_axis; };  // normal.xyz, distance | u.xyz, as_float(material id) | v.xyz
+struct DeviceLight  { float4 colour_kind; float4 position_inner; float4 negdir_outer; }; // colour.xyz, as_float(kind) | position.xyz, inner_cutoff | -direction.xyz, outer_cutoff
+
+// Per-frame + static pointers, passed to the kernels by value (kernel parameter space).
+struct SceneParams {
+	// static (uploaded once)
+	const float4 * __restrict__ nodes;          // all BLAS, concatenated
+	const float4 * __restrict__ triangles_hot;
+	const float4 * __restrict__ triangles_cold;
+	const DeviceMaterial * __restrict__ materials;
+	const DeviceTexture  * __restrict__ textures;
+	const float4 * __restrict__ texels;
+	const float4 * __restrict__ sky;
+	int sky_size;
+	// per frame
+	const float4 * __restrict__ tlas_nodes;
+	const int    * __restrict__ tlas_indices;
+	const DeviceInstance * __restrict__ instances;
+	const DeviceSphere   * __restrict__ spheres;
+	const DevicePlane    * __restrict__ planes;
+	const DeviceLight    * __restrict__ lights;
+	int sphere_count, plane_count, light_count;
+	float cam_position[3], cam_top_left[3], cam_x_axis[3], cam_y_axis[3];
+	float ambient[3];
+	// configuration (Config.h mirror)
+	int width, height, bounces, mipmap_filter;
+	float max_anisotropy;
+	int tiles_x, tiles_y, tile_stride, tile_phase, tile_count_mine;
+};
+
+struct FrameCounters {   // accumulated with one atomicAdd per warp
+	unsigned long long primary, shadow, reflection, refraction;
+	unsigned long long nodes, triangles, texels;
+	unsigned int next_unit;      // work-stealing cursor (WorkerThread.cpp:53-54)
+	unsigned int pad;
+};
+
+} // namespace rt

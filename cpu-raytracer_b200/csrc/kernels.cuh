@@ -1,0 +1,193 @@
+// kernels.cuh — __global__ entry points.
+#pragma once
+#include "render.cuh"
+
+namespace rt {
+
+__device__ __forceinline__ unsigned warp_sum(unsigned v) {
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+	return v;
+}
+
+// Maps a work unit to a pixel. The frame is cut into the reference's 32x32 tiles (Window.h:32-33,
+// Window.cpp:11-12); this GPU owns the tiles t with t % tile_stride == tile_phase (SURVEY.md
+// 8(e)); a unit is one warp-sized 8x4 pixel block, 32 units per tile, numbered tile-major so that
+// consecutive units (taken by neighbouring warps) stay in one tile.
+__device__ __forceinline__ bool unit_pixel(const SceneParams & P, unsigned unit, int lane, int & px, int & py) {
+	const int tile = P.tile_phase + int(unit >> 5) * P.tile_stride;
+	const int sub  = int(unit & 31);
+	px = (tile % P.tiles_x) * 32 + (sub & 3) * 8 + (lane & 7);
+	py = (tile / P.tiles_x) * 32 + (sub >> 2) * 4 + (lane >> 3);
+	return px < P.width && py < P.height; // edge tiles are clipped, WorkerThread.cpp:60-61
+}
+
+// Persistent warps pull units off one device-side counter — the GPU form of the reference's
+// InterlockedDecrement tile countdown (WorkerThread.cpp:53-65).
+template<bool COUNT>
+__global__ void __launch_bounds__(RT_BLOCK_THREADS)
+render_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, float * __restrict__ colour_float, FrameCounters * __restrict__ counters) {
+	const int lane = threadIdx.x & 31;
+	const unsigned total_units = unsigned(P.tile_count_mine) * 32u;
+
+	Counters cnt = { 0, 0, 0, 0, 0, 0 };
+	unsigned primary = 0;
+
+	for (;;) {
+		unsigned unit = 0;
+		if (lane == 0) unit = atomicAdd(&counters->next_unit, 1u);
+		unit = __shfl_sync(0xffffffffu, unit, 0);
+		if (unit >= total_units) break;
+
+		int px, py;
+		if (unit_pixel(P, unit, lane, px, py)) {
+			const Ray ray = primary_ray(P, px, py);
+			primary++;
+			const v3 colour = shade_pixel<COUNT>(P, ray, cnt);
+
+			const size_t p = size_t(px) + size_t(P.width) * py;
+			frame_buffer[p] = plot_colour(colour);
+			if (colour_float) { colour_float[3 * p] = colour.x; colour_float[3 * p + 1] = colour.y; colour_float[3 * p + 2] = colour.z; }
+		}
+		__syncwarp();
+	}
+
+	// one atomic per warp and counter
+	const unsigned s_primary = warp_sum(primary), s_shadow = warp_sum(cnt.shadow), s_refl = warp_sum(cnt.reflection), s_refr = warp_sum(cnt.refraction);
+	if (lane == 0) {
+		atomicAdd(&counters->primary, (unsigned long long)s_primary);
+		atomicAdd(&counters->shadow, (unsigned long long)s_shadow);
+		atomicAdd(&counters->reflection, (unsigned long long)s_refl);
+		atomicAdd(&counters->refraction, (unsigned long long)s_refr);
+	}
+	if (COUNT) {
+		const unsigned s_nodes = warp_sum(cnt.nodes), s_tris = warp_sum(cnt.triangles), s_texels = warp_sum(cnt.texels);
+		if (lane == 0) {
+			atomicAdd(&counters->nodes, (unsigned long long)s_nodes);
+			atomicAdd(&counters->triangles, (unsigned long long)s_tris);
+			atomicAdd(&counters->texels, (unsigned long long)s_texels);
+		}
+	}
+}
+
+// Closest-hit record of the primary ray per pixel: (instance, flattened triangle) and
+// (distance, material id, u, v) — what the id-instrumented reference build dumps. Test output only.
+__global__ void __launch_bounds__(RT_BLOCK_THREADS)
+primary_hits_kernel(const SceneParams P, int * __restrict__ ids, float * __restrict__ hits) {
+	const int px = blockIdx.x * 32 + (threadIdx.x & 31);
+	const int py = blockIdx.y * 8 + (threadIdx.x >> 5);
+	if (px >= P.width || py >= P.height) return;
+
+	const Ray ray = primary_ray(P, px, py);
+	Counters cnt = { 0, 0, 0, 0, 0, 0 };
+	Candidate best;
+	trace_closest<false>(P, ray.origin, ray.direction, best, cnt);
+
+	const size_t p = size_t(px) + size_t(P.width) * py;
+	const bool is_hit = best.instance != HIT_NONE;
+	if (ids) { ids[2 * p] = is_hit ? best.instance : -1; ids[2 * p + 1] = is_hit ? best.primitive : -1; }
+	if (hits) {
+		float material = -1.0f, u = 0.0f, v = 0.0f;
+		if (is_hit) {
+			HitRecord hit;
+			build_record(P, ray, best, hit);
+			material = float(hit.material_id); u = hit.u; v = hit.v;
+		}
+		hits[4 * p] = best.t; hits[4 * p + 1] = material; hits[4 * p + 2] = u; hits[4 * p + 3] = v;
+	}
+}
+
+// ------------------------------------------------------------------------------ FXAA ---
+// Data/Shaders/fragment_fxaa.glsl:11-74 (+ fragment_identity.glsl) as a compute kernel. Sampler
+// state of Window.cpp:48-50: NEAREST, GL_REPEAT, RGBA8; uv of pixel (px, py) = ((px+.5)/W,
+// (py+.5)/H) (vertex.glsl:7-11). get_screen() = pow(texel, 1/2.2) of an 8-bit value = a 256-entry
+// table, computed on the host with powf and kept in shared memory.
+#define FXAA_TILE_W 64
+#define FXAA_TILE_H 4
+
+__device__ __forceinline__ v3 fxaa_screen(const unsigned * __restrict__ fb, const float * gamma, int W, int H, float fx, float fy) {
+	const int x = positive_mod(int(floorf(fx)), W);
+	const int y = positive_mod(int(floorf(fy)), H);
+	const unsigned c = __ldg(fb + size_t(x) + size_t(W) * y);
+	return V(gamma[(c >> 16) & 255], gamma[(c >> 8) & 255], gamma[c & 255]);
+}
+__device__ __forceinline__ float fxaa_luma(v3 c) { return (0.299f * c.x + 0.587f * c.y) + 0.114f * c.z; }
+__device__ __forceinline__ unsigned fxaa_unorm8(float c) {
+	if (!(c > 0.0f)) c = 0.0f;
+	if (c > 1.0f) c = 1.0f;
+	return unsigned(__float2int_rn(c * 255.0f));
+}
+
+__global__ void __launch_bounds__(FXAA_TILE_W * FXAA_TILE_H)
+fxaa_kernel(const unsigned * __restrict__ fb, unsigned char * __restrict__ rgb8, const float * __restrict__ gamma_table, int W, int H, int enable_fxaa) {
+	__shared__ float gamma[256];
+	__shared__ __align__(16) unsigned char staged[FXAA_TILE_H][FXAA_TILE_W * 3];
+
+	const int tid = threadIdx.y * FXAA_TILE_W + threadIdx.x;
+	gamma[tid] = gamma_table[tid]; // 256 threads, 256 entries
+	__syncthreads();
+
+	const int px = blockIdx.x * FXAA_TILE_W + threadIdx.x;
+	const int py = blockIdx.y * FXAA_TILE_H + threadIdx.y;
+
+	if (px < W && py < H) {
+		const float cx = float(px) + 0.5f, cy = float(py) + 0.5f;
+		v3 out;
+		if (!enable_fxaa) {
+			out = fxaa_screen(fb, gamma, W, H, cx, cy);
+		} else {
+			// vec2(+-inv.x, +-inv_screen_size) takes .x for both components (fragment_fxaa.glsl:25-28):
+			// +-1 px in x, +-H/W px in y
+			const float diag_y = float(H) / float(W);
+			const float luma_tl = fxaa_luma(fxaa_screen(fb, gamma, W, H, cx - 1.0f, cy - diag_y));
+			const float luma_tr = fxaa_luma(fxaa_screen(fb, gamma, W, H, cx + 1.0f, cy - diag_y));
+			const float luma_bl = fxaa_luma(fxaa_screen(fb, gamma, W, H, cx - 1.0f, cy + diag_y));
+			const float luma_br = fxaa_luma(fxaa_screen(fb, gamma, W, H, cx + 1.0f, cy + diag_y));
+			const float luma_m  = fxaa_luma(fxaa_screen(fb, gamma, W, H, cx, cy));
+
+			const float luma_min = fminf(fminf(fminf(luma_tl, luma_tr), fminf(luma_bl, luma_br)), luma_m);
+			const float luma_max = fmaxf(fmaxf(fmaxf(luma_tl, luma_tr), fmaxf(luma_bl, luma_br)), luma_m);
+
+			float dir_x = (luma_bl + luma_br) - (luma_tl + luma_tr);
+			float dir_y = (luma_tl + luma_bl) - (luma_tr + luma_br);
+
+			const float reduce = fmaxf(1.0f / 128.0f, (luma_tl + luma_tr + luma_bl + luma_br) * 0.25f * (1.0f / 8.0f));
+			const float adjust = 1.0f / (fminf(fabsf(dir_x), fabsf(dir_y)) + reduce);
+
+			dir_x = fminf(fmaxf(dir_x * adjust, -8.0f), 8.0f); // in pixels: * inv_screen_size * screen_size
+			dir_y = fminf(fmaxf(dir_y * adjust, -8.0f), 8.0f);
+
+			const float k1 = 1.0f / 3.0f - 0.5f, k2 = 2.0f / 3.0f - 0.5f;
+			const v3 a0 = fxaa_screen(fb, gamma, W, H, cx + dir_x * k1, cy + dir_y * k1);
+			const v3 a1 = fxaa_screen(fb, gamma, W, H, cx + dir_x * k2, cy + dir_y * k2);
+			const v3 b0 = fxaa_screen(fb, gamma, W, H, cx + dir_x * -0.5f, cy + dir_y * -0.5f);
+			const v3 b1 = fxaa_screen(fb, gamma, W, H, cx + dir_x * 0.5f,  cy + dir_y * 0.5f);
+
+			const v3 result_a = (a0 + a1) * 0.5f;
+			const v3 result_b = (b0 + b1) * 0.5f;
+			const v3 result   = (result_a + result_b) * 0.5f;
+
+			const float luma_result = fxaa_luma(result);
+			out = (luma_result < luma_min || luma_result > luma_max) ? result_a : result;
+		}
+		staged[threadIdx.y][threadIdx.x * 3]     = (unsigned char)fxaa_unorm8(out.x);
+		staged[threadIdx.y][threadIdx.x * 3 + 1] = (unsigned char)fxaa_unorm8(out.y);
+		staged[threadIdx.y][threadIdx.x * 3 + 2] = (unsigned char)fxaa_unorm8(out.z);
+	}
+	__syncthreads();
+
+	// 64 pixels x 3 bytes = 48 aligned 32-bit words per row: coalesced word stores
+	const int row_px0 = blockIdx.x * FXAA_TILE_W;
+	if (py < H && threadIdx.x < 48) {
+		const int valid_bytes = min(FXAA_TILE_W, W - row_px0) * 3;
+		const size_t row_base = (size_t(py) * W + row_px0) * 3; // multiple of 4 when W % 4 == 0 or row_px0 * 3 aligned
+		const int b = threadIdx.x * 4;
+		if ((row_base & 3) == 0 && b + 4 <= valid_bytes) {
+			*reinterpret_cast<unsigned *>(rgb8 + row_base + b) = *reinterpret_cast<const unsigned *>(&staged[threadIdx.y][b]);
+		} else {
+			for (int k = b; k < b + 4 && k < valid_bytes; k++) rgb8[row_base + k] = staged[threadIdx.y][k];
+		}
+	}
+}
+
+} // namespace rt

@@ -1,0 +1,75 @@
+// rt_math.cuh — per-thread FP32 vector math with the reference's association order.
+//
+// One CUDA thread carries one ray, which is one lane of the reference's SIMD packet
+// (SIMD_Vector3.h, SIMD_floats.h). A multiply-add is fused exactly where the reference calls
+// madd / msub (SIMD_floats.h:223-224 -> _mm256_fmadd_ps / _mm256_fmsub_ps; used by dot, cross
+// and the matrix transforms, SIMD_Vector3.h:53-63, Matrix4.h:39-85) and nowhere else: the file
+// is compiled with -fmad=false and spells every fused operation as __fmaf_rn. Division and
+// square root are IEEE (nvcc defaults -prec-div=true -prec-sqrt=true; no --use_fast_math).
+#pragma once
+#include <cuda_runtime.h>
+#include <math_constants.h>
+#include <stdint.h>
+
+namespace rt {
+
+#define RT_EPSILON 0.005f               // Ray::EPSILON, Ray.h:5
+#define RT_ONE_OVER_PI     0.31830988618f // Util.h:9
+#define RT_ONE_OVER_TWO_PI 0.15915494309f // Util.h:12
+
+struct v3 { float x, y, z; };
+
+__device__ __forceinline__ v3 V(float x, float y, float z) { v3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ v3 V(float4 a) { return V(a.x, a.y, a.z); }
+__device__ __forceinline__ v3 operator+(v3 a, v3 b) { return V(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ v3 operator-(v3 a, v3 b) { return V(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ v3 operator*(v3 a, v3 b) { return V(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ v3 operator*(v3 a, float f) { return V(a.x * f, a.y * f, a.z * f); }   // v * f and f * v (SIMD_Vector3.h:150-158)
+__device__ __forceinline__ v3 addf(v3 a, float f) { return V(a.x + f, a.y + f, a.z + f); }        // f + v
+__device__ __forceinline__ v3 neg(v3 a) { return V(0.0f - a.x, 0.0f - a.y, 0.0f - a.z); }          // SIMD_Vector3.h:138-141
+
+__device__ __forceinline__ float dot(v3 a, v3 b) { return __fmaf_rn(a.x, b.x, __fmaf_rn(a.y, b.y, a.z * b.z)); } // :53-55
+__device__ __forceinline__ v3 cross(v3 a, v3 b) {                                                               // :57-63
+	return V(__fmaf_rn(a.y, b.z, -(a.z * b.y)), __fmaf_rn(a.z, b.x, -(a.x * b.z)), __fmaf_rn(a.x, b.y, -(a.y * b.x)));
+}
+__device__ __forceinline__ v3 madd(v3 a, float b, v3 c) { return V(__fmaf_rn(a.x, b, c.x), __fmaf_rn(a.y, b, c.y), __fmaf_rn(a.z, b, c.z)); } // :107-113
+__device__ __forceinline__ float inv_sqrt(float x) { return 1.0f / sqrtf(x); }
+__device__ __forceinline__ v3 normalize(v3 a) { return a * inv_sqrt(dot(a, a)); }            // :44-51
+__device__ __forceinline__ v3 divf(v3 a, float f) { return a * (1.0f / f); }                 // v / f = v * rcp(f), :153
+
+// x86 MINPS/MAXPS semantics: the second operand comes back when either one is NaN.
+__device__ __forceinline__ float sse_min(float a, float b) { return a < b ? a : b; }
+__device__ __forceinline__ float sse_max(float a, float b) { return a > b ? a : b; }
+
+// std::max / std::min as the scalar texture code uses them (Texture.cpp)
+__device__ __forceinline__ float std_max(float a, float b) { return a < b ? b : a; }
+__device__ __forceinline__ float std_min(float a, float b) { return b < a ? b : a; }
+
+// Util::float_to_int (cvtss2si, Util.h:39-41) and _mm256_cvtps_epi32: round to nearest even;
+// NaN and out-of-range give 0x80000000 (CUDA's cvt.rni saturates and maps NaN to 0 instead).
+__device__ __forceinline__ int float_to_int(float x) {
+	return (x >= -2147483648.0f && x < 2147483648.0f) ? __float2int_rn(x) : (int)0x80000000u;
+}
+
+__device__ __forceinline__ int positive_mod(int value, int modulus) { // Math::mod, Math.h:46-53
+	int r = value % modulus;
+	return r < 0 ? r + modulus : r;
+}
+
+// Row-major 3x4 affine matrix (three float4 rows): row i = (m(0,i), m(1,i), m(2,i), m(3,i)) of the
+// reference's column-major Matrix4, so the nested fused multiply-adds of Matrix4.h:39-85 read
+// x' = fma(r.x, p.x, fma(r.y, p.y, fma(r.z, p.z, r.w))).
+struct Affine { float4 r0, r1, r2; };
+
+__device__ __forceinline__ v3 transform_position(const Affine & m, v3 p) {
+	return V(__fmaf_rn(m.r0.x, p.x, __fmaf_rn(m.r0.y, p.y, __fmaf_rn(m.r0.z, p.z, m.r0.w))),
+	         __fmaf_rn(m.r1.x, p.x, __fmaf_rn(m.r1.y, p.y, __fmaf_rn(m.r1.z, p.z, m.r1.w))),
+	         __fmaf_rn(m.r2.x, p.x, __fmaf_rn(m.r2.y, p.y, __fmaf_rn(m.r2.z, p.z, m.r2.w))));
+}
+__device__ __forceinline__ v3 transform_direction(const Affine & m, v3 d) {
+	return V(__fmaf_rn(m.r0.x, d.x, __fmaf_rn(m.r0.y, d.y, m.r0.z * d.z)),
+	         __fmaf_rn(m.r1.x, d.x, __fmaf_rn(m.r1.y, d.y, m.r1.z * d.z)),
+	         __fmaf_rn(m.r2.x, d.x, __fmaf_rn(m.r2.y, d.y, m.r2.z * d.z)));
+}
+
+} // namespace rt

@@ -1,0 +1,295 @@
+// traverse.cuh — two-level BVH traversal and primitive intersection, one ray per thread.
+//
+// Reference: Scene::trace_primitives / intersect_primitives (Scene.cpp:173-190) ->
+// PrimitiveList (PrimitiveList.h:29-45) -> Sphere (Sphere.cpp:9-112), Plane (Plane.cpp:13-79),
+// TopLevelBVH::trace / intersect (TopLevelBVH.cpp:53-129) -> Mesh (Mesh.cpp:17-40) ->
+// BottomLevelBVH::trace / intersect (BottomLevelBVH.cpp:355-437) -> triangle_trace /
+// triangle_intersect (:214-346), AABB::intersect (AABB.cpp:38-52), BVHNode.h:30-40.
+//
+// What is kept from the reference because it decides the RESULT: the slab test's operation
+// order and x86 NaN behaviour, strict inequalities of the triangle test, t shared across the
+// rigid instance transform, leaf/near-far visiting order (ties between equidistant hits).
+// What is restructured for the GPU: a closest-hit query only records (t, u, v, primitive,
+// instance); the full hit record is computed once, after traversal, for the winner
+// (shade.cuh) — the reference recomputes it on every accepted candidate
+// (BottomLevelBVH.cpp:254-308), a pure function of the same inputs.
+#pragma once
+#include "device_scene.cuh"
+
+namespace rt {
+
+#define RT_STACK_SIZE 64   // BVH_TRAVERSAL_STACK_SIZE, Config.h:25
+
+struct Ray {               // Ray.h:7-16
+	v3 origin, direction;
+	v3 dO_dx, dO_dy, dD_dx, dD_dy;
+};
+
+enum { HIT_NONE = -1, HIT_SPHERE = -2, HIT_PLANE = -3 }; // instance >= 0: mesh instance
+
+struct Candidate {         // closest hit so far
+	float t, u, v;
+	int instance;          // HIT_* or TopLevelBVH primitive index
+	int primitive;         // flattened triangle index within its BLAS, or sphere / plane index
+};
+
+struct Counters { unsigned nodes, triangles, texels, shadow, reflection, refraction; };
+
+// AABB::intersect, AABB.cpp:38-52. MINPS/MAXPS NaN semantics matter: a ray with a zero
+// direction component lying exactly on a slab plane produces 0 * inf = NaN.
+__device__ __forceinline__ bool aabb_intersect(float4 n0, float4 n1, v3 o, v3 inv_d, float max_distance) {
+	float t0x = (n0.x - o.x) * inv_d.x, t1x = (n0.w - o.x) * inv_d.x;
+	float t0y = (n0.y - o.y) * inv_d.y, t1y = (n1.x - o.y) * inv_d.y;
+	float t0z = (n0.z - o.z) * inv_d.z, t1z = (n1.y - o.z) * inv_d.z;
+
+	float tminx = sse_min(t0x, t1x), tmaxx = sse_max(t0x, t1x);
+	float tminy = sse_min(t0y, t1y), tmaxy = sse_max(t0y, t1y);
+	float tminz = sse_min(t0z, t1z), tmaxz = sse_max(t0z, t1z);
+
+	float t_near = sse_max(sse_max(RT_EPSILON,   tminx), sse_max(tminy, tminz));
+	float t_far  = sse_min(sse_min(max_distance, tmaxx), sse_min(tmaxy, tmaxz));
+	return t_near < t_far;
+}
+
+// BVHNode::should_visit_left_first, BVHNode.h:30-40 (axis in the top two bits of count)
+__device__ __forceinline__ bool visit_left_first(int count, v3 d) {
+	unsigned axis = unsigned(count) >> 30;
+	float c = axis == 1 ? d.x : (axis == 2 ? d.y : d.z);
+	return c > 0.0f;
+}
+
+// Moller-Trumbore with the reference's operation order; all comparisons strict
+// (BottomLevelBVH.cpp:214-252 / :311-346).
+__device__ __forceinline__ bool triangle_test(const float4 * __restrict__ tri, v3 o, v3 d, float max_t, float & t_out, float & u_out, float & v_out) {
+	const float4 a0 = __ldg(tri), a1 = __ldg(tri + 1), a2 = __ldg(tri + 2);
+	const v3 p0 = V(a0.x, a0.y, a0.z), edge_1 = V(a0.w, a1.x, a1.y), edge_2 = V(a1.z, a1.w, a2.x);
+
+	v3    h = cross(d, edge_2);
+	float a = dot(edge_1, h);
+	float f = 1.0f / a;
+	v3    s = o - p0;
+	float u = f * dot(s, h);
+	if (!(u > 0.0f && u < 1.0f)) return false;
+
+	v3    q = cross(s, edge_1);
+	float v = f * dot(d, q);
+	if (!(v > 0.0f && (u + v) < 1.0f)) return false;
+
+	float t = f * dot(edge_2, q);
+	if (!(t > RT_EPSILON && t < max_t)) return false;
+
+	t_out = t; u_out = u; v_out = v;
+	return true;
+}
+
+__device__ __forceinline__ DeviceInstance load_instance_inverse(const DeviceInstance * __restrict__ inst) {
+	const float4 * p = reinterpret_cast<const float4 *>(inst);
+	DeviceInstance r;
+	r.inverse.r0 = __ldg(p); r.inverse.r1 = __ldg(p + 1); r.inverse.r2 = __ldg(p + 2);
+	const int4 o = __ldg(reinterpret_cast<const int4 *>(p + 6));
+	r.node_offset = o.x; r.triangle_offset = o.y; r.material_offset = o.z; r.pad = 0;
+	return r;
+}
+
+// BottomLevelBVH::trace, BottomLevelBVH.cpp:355-396 (object-space ray, shared t)
+template<bool COUNT>
+__device__ __forceinline__ void blas_trace(const float4 * __restrict__ nodes, const float4 * __restrict__ hot, v3 o, v3 d, int instance, Candidate & best, int * stack, Counters & cnt) {
+	const v3 inv_d = V(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+
+	int stack_size = 1;
+	stack[0] = 0;
+
+	while (stack_size > 0) {
+		const int index = stack[--stack_size];
+		const float4 n0 = __ldg(nodes + 2 * index), n1 = __ldg(nodes + 2 * index + 1);
+		if (COUNT) cnt.nodes++;
+
+		if (!aabb_intersect(n0, n1, o, inv_d, best.t)) continue;
+
+		const int left_or_first = __float_as_int(n1.z), count = __float_as_int(n1.w);
+		if ((count & 0x3FFFFFFF) > 0) {
+			for (int i = left_or_first; i < left_or_first + count; i++) {
+				float t, u, v;
+				if (COUNT) cnt.triangles++;
+				if (triangle_test(hot + 3 * size_t(i), o, d, best.t, t, u, v)) {
+					best.t = t; best.u = u; best.v = v; best.instance = instance; best.primitive = i;
+				}
+			}
+		} else if (visit_left_first(count, d)) {
+			stack[stack_size++] = left_or_first + 1;
+			stack[stack_size++] = left_or_first;
+		} else {
+			stack[stack_size++] = left_or_first;
+			stack[stack_size++] = left_or_first + 1;
+		}
+	}
+}
+
+// BottomLevelBVH::intersect, BottomLevelBVH.cpp:398-437
+template<bool COUNT>
+__device__ __forceinline__ bool blas_intersect(const float4 * __restrict__ nodes, const float4 * __restrict__ hot, v3 o, v3 d, float max_distance, int * stack, Counters & cnt) {
+	const v3 inv_d = V(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+
+	int stack_size = 1;
+	stack[0] = 0;
+
+	while (stack_size > 0) {
+		const int index = stack[--stack_size];
+		const float4 n0 = __ldg(nodes + 2 * index), n1 = __ldg(nodes + 2 * index + 1);
+		if (COUNT) cnt.nodes++;
+
+		if (!aabb_intersect(n0, n1, o, inv_d, max_distance)) continue;
+
+		const int left_or_first = __float_as_int(n1.z), count = __float_as_int(n1.w);
+		if ((count & 0x3FFFFFFF) > 0) {
+			for (int i = left_or_first; i < left_or_first + count; i++) {
+				float t, u, v;
+				if (COUNT) cnt.triangles++;
+				if (triangle_test(hot + 3 * size_t(i), o, d, max_distance, t, u, v)) return true;
+			}
+		} else if (visit_left_first(count, d)) {
+			stack[stack_size++] = left_or_first + 1;
+			stack[stack_size++] = left_or_first;
+		} else {
+			stack[stack_size++] = left_or_first;
+			stack[stack_size++] = left_or_first + 1;
+		}
+	}
+	return false;
+}
+
+// Sphere::trace, Sphere.cpp:9-40 — t only; the record is built in shade.cuh
+__device__ __forceinline__ bool sphere_test(const DeviceSphere * __restrict__ sphere, v3 o, v3 d, float max_t, float & t_out) {
+	const float4 c = __ldg(&sphere->center_r2);
+	v3 oc = o - V(c.x, c.y, c.z);
+	float a = dot(d, d);
+	float b = 2.0f * dot(oc, d);
+	float cc = dot(oc, oc) - c.w;
+
+	float disc = b * b - 4.0f * a * cc;
+	if (!(disc >= 0.0f)) return false;
+
+	float sqrt_d    = sqrtf(disc);
+	float inv_denom = 0.0f - 1.0f / (2.0f * a);
+
+	float t0 = (b + sqrt_d) * inv_denom;
+	float t1 = (b - sqrt_d) * inv_denom;
+
+	float t = t0 > RT_EPSILON ? t0 : t1;
+	if (!(t > RT_EPSILON && t < max_t)) return false;
+	t_out = t;
+	return true;
+}
+
+// Sphere::intersect, Sphere.cpp:92-112 (geometric form: not the same arithmetic as trace)
+__device__ __forceinline__ bool sphere_intersect(const DeviceSphere * __restrict__ sphere, v3 o, v3 d, float max_distance) {
+	const float4 c4 = __ldg(&sphere->center_r2);
+	v3    c  = V(c4.x, c4.y, c4.z) - o;
+	float t  = dot(c, d);
+	v3    Q  = c - d * t;
+	float p2 = dot(Q, Q);
+	if (!(p2 < c4.w)) return false;
+	t = t - sqrtf(c4.w - p2);
+	return t > RT_EPSILON && t < max_distance;
+}
+
+// Plane::trace / intersect, Plane.cpp:13-22,71-79
+__device__ __forceinline__ float plane_t(const DevicePlane * __restrict__ plane, v3 o, v3 d) {
+	const float4 n = __ldg(&plane->normal_d);
+	v3 normal = V(n.x, n.y, n.z);
+	return (0.0f - (dot(normal, o) + n.w)) / dot(normal, d);
+}
+
+// Scene::trace_primitives, Scene.cpp:173-177: spheres, planes, then the TLAS, all against one
+// running closest distance.
+template<bool COUNT>
+__device__ __forceinline__ void trace_closest(const SceneParams & P, v3 o, v3 d, Candidate & best, Counters & cnt) {
+	best.t = CUDART_INF_F; best.u = 0.0f; best.v = 0.0f; best.instance = HIT_NONE; best.primitive = -1;
+
+	for (int i = 0; i < P.sphere_count; i++) {
+		float t;
+		if (sphere_test(P.spheres + i, o, d, best.t, t)) { best.t = t; best.instance = HIT_SPHERE; best.primitive = i; }
+	}
+	for (int i = 0; i < P.plane_count; i++) {
+		float t = plane_t(P.planes + i, o, d);
+		if (t > RT_EPSILON && t < best.t) { best.t = t; best.instance = HIT_PLANE; best.primitive = i; }
+	}
+
+	// TopLevelBVH::trace, TopLevelBVH.cpp:53-87
+	int tlas_stack[RT_STACK_SIZE];
+	int blas_stack[RT_STACK_SIZE];
+
+	const v3 inv_d = V(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+	int stack_size = 1;
+	tlas_stack[0] = 0;
+
+	while (stack_size > 0) {
+		const int index = tlas_stack[--stack_size];
+		const float4 n0 = __ldg(P.tlas_nodes + 2 * index), n1 = __ldg(P.tlas_nodes + 2 * index + 1);
+		if (COUNT) cnt.nodes++;
+
+		if (!aabb_intersect(n0, n1, o, inv_d, best.t)) continue;
+
+		const int left_or_first = __float_as_int(n1.z), count = __float_as_int(n1.w);
+		if ((count & 0x3FFFFFFF) > 0) {
+			for (int i = left_or_first; i < left_or_first + count; i++) {
+				const int instance = __ldg(P.tlas_indices + i);
+				const DeviceInstance inst = load_instance_inverse(P.instances + instance);
+				// Mesh::trace, Mesh.cpp:17-31 (the differentials are transformed in shade.cuh, for the winner only)
+				blas_trace<COUNT>(P.nodes + 2 * size_t(inst.node_offset), P.triangles_hot + 3 * size_t(inst.triangle_offset),
+				                  transform_position(inst.inverse, o), transform_direction(inst.inverse, d), instance, best, blas_stack, cnt);
+			}
+		} else if (visit_left_first(count, d)) {
+			tlas_stack[stack_size++] = left_or_first + 1;
+			tlas_stack[stack_size++] = left_or_first;
+		} else {
+			tlas_stack[stack_size++] = left_or_first;
+			tlas_stack[stack_size++] = left_or_first + 1;
+		}
+	}
+}
+
+// Scene::intersect_primitives, Scene.cpp:179-190
+template<bool COUNT>
+__device__ __forceinline__ bool trace_any(const SceneParams & P, v3 o, v3 d, float max_distance, Counters & cnt) {
+	for (int i = 0; i < P.sphere_count; i++) if (sphere_intersect(P.spheres + i, o, d, max_distance)) return true;
+	for (int i = 0; i < P.plane_count; i++) {
+		float t = plane_t(P.planes + i, o, d);
+		if (t > RT_EPSILON && t < max_distance) return true;
+	}
+
+	// TopLevelBVH::intersect, TopLevelBVH.cpp:89-129
+	int tlas_stack[RT_STACK_SIZE];
+	int blas_stack[RT_STACK_SIZE];
+
+	const v3 inv_d = V(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+	int stack_size = 1;
+	tlas_stack[0] = 0;
+
+	while (stack_size > 0) {
+		const int index = tlas_stack[--stack_size];
+		const float4 n0 = __ldg(P.tlas_nodes + 2 * index), n1 = __ldg(P.tlas_nodes + 2 * index + 1);
+		if (COUNT) cnt.nodes++;
+
+		if (!aabb_intersect(n0, n1, o, inv_d, max_distance)) continue;
+
+		const int left_or_first = __float_as_int(n1.z), count = __float_as_int(n1.w);
+		if ((count & 0x3FFFFFFF) > 0) {
+			for (int i = left_or_first; i < left_or_first + count; i++) {
+				const int instance = __ldg(P.tlas_indices + i);
+				const DeviceInstance inst = load_instance_inverse(P.instances + instance);
+				if (blas_intersect<COUNT>(P.nodes + 2 * size_t(inst.node_offset), P.triangles_hot + 3 * size_t(inst.triangle_offset),
+				                          transform_position(inst.inverse, o), transform_direction(inst.inverse, d), max_distance, blas_stack, cnt)) return true;
+			}
+		} else if (visit_left_first(count, d)) {
+			tlas_stack[stack_size++] = left_or_first + 1;
+			tlas_stack[stack_size++] = left_or_first;
+		} else {
+			tlas_stack[stack_size++] = left_or_first;
+			tlas_stack[stack_size++] = left_or_first + 1;
+		}
+	}
+	return false;
+}
+
+} // namespace rt

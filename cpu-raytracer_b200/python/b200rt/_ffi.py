@@ -46,7 +46,7 @@ class Config(C.Structure):
     _fields_ = [
         ("width", C.c_int32), ("height", C.c_int32), ("bounces", C.c_int32), ("mipmap_filter", C.c_int32),
         ("max_anisotropy", C.c_float), ("enable_fxaa", C.c_int32), ("device", C.c_int32),
-        ("tile_stride", C.c_int32), ("tile_phase", C.c_int32),
+        ("tile_stride", C.c_int32), ("tile_phase", C.c_int32), ("count_traversal", C.c_int32),
     ]
 
 
@@ -69,9 +69,9 @@ class Outputs(C.Structure):
 
 
 def make_config(width, height, bounces, mipmap_filter="aniso", max_anisotropy=8.0, enable_fxaa=True, device=0,
-                tile_stride=1, tile_phase=0):
+                tile_stride=1, tile_phase=0, count_traversal=False):
     f = FILTERS[mipmap_filter] if isinstance(mipmap_filter, str) else int(mipmap_filter)
-    return Config(width, height, bounces, f, max_anisotropy, 1 if enable_fxaa else 0, device, tile_stride, tile_phase)
+    return Config(width, height, bounces, f, max_anisotropy, 1 if enable_fxaa else 0, device, tile_stride, tile_phase, 1 if count_traversal else 0)
 
 
 def _load(path):

@@ -1,0 +1,97 @@
+"""Renderer: Python face of libb200rt.so (include/b200rt.h) — the CUDA render path.
+
+    r = Renderer(width, height, bounces=3, mipmap_filter="tri")
+    r.upload_static(pack)                   # BLAS, materials, textures, sky -> HBM (once)
+    out = r.render(pack)                    # per-frame data up, trace + FXAA, images down
+
+There is deliberately no fallback: if the CUDA library or a GPU is missing this raises.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _ffi
+
+
+class DeviceError(RuntimeError):
+    pass
+
+
+class Renderer:
+    def __init__(self, width, height, bounces, mipmap_filter="aniso", max_anisotropy=8.0, enable_fxaa=True, device=0,
+                 tile_stride=1, tile_phase=0, count_traversal=False):
+        self._lib = _ffi.device_lib()
+        self.config = _ffi.make_config(width, height, bounces, mipmap_filter, max_anisotropy, enable_fxaa, device,
+                                       tile_stride, tile_phase, count_traversal)
+        self._h = C.c_void_p()
+        if self._lib.b200rt_create(C.byref(self.config), C.byref(self._h)) != 0:
+            raise DeviceError(self._lib.b200rt_last_error(None).decode())
+        self.width, self.height = width, height
+        self._keep = None
+
+    def close(self):
+        if self._h:
+            self._lib.b200rt_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            raise DeviceError(self._lib.b200rt_last_error(self._h).decode())
+
+    def upload_static(self, pack):
+        view = pack.static_view()
+        self._check(self._lib.b200rt_upload_static(self._h, C.byref(view)))
+
+    def render(self, pack, want_ids=False, want_float=False, want_presented=True, want_frame_buffer=True, out=None):
+        """One frame through b200rt_render_frame (host buffers in, host buffers out)."""
+        h, w = self.height, self.width
+        res = out if out is not None else {}
+        if want_frame_buffer and "frame_buffer" not in res:
+            res["frame_buffer"] = np.zeros((h, w), dtype=np.uint32)
+        if want_presented and "presented" not in res:
+            res["presented"] = np.zeros((h, w, 3), dtype=np.uint8)
+        if want_ids:
+            res["ids"] = np.full((h, w, 2), -1, dtype=np.int32)
+            res["hit"] = np.zeros((h, w, 4), dtype=np.float32)
+        if want_float:
+            res["colour"] = np.zeros((h, w, 3), dtype=np.float32)
+        stats = _ffi.Stats()
+        outputs = _ffi.Outputs(
+            res["frame_buffer"].ctypes.data if want_frame_buffer else None,
+            res["presented"].ctypes.data if want_presented else None,
+            res["colour"].ctypes.data if want_float else None,
+            res["ids"].ctypes.data if want_ids else None,
+            res["hit"].ctypes.data if want_ids else None,
+            C.pointer(stats))
+        frame = pack.frame_view()
+        self._check(self._lib.b200rt_render_frame(self._h, C.byref(frame), C.byref(outputs)))
+        res["stats"] = stats.as_dict()
+        return res
+
+    def render_device(self, pack, frame_buffer_ptr):
+        """Render this context's tiles into a device buffer (uint32 [H][W]) owned by the caller."""
+        stats = _ffi.Stats()
+        frame = pack.frame_view()
+        self._check(self._lib.b200rt_render_frame_device(self._h, C.byref(frame), C.c_uint64(frame_buffer_ptr), C.byref(stats)))
+        return stats.as_dict()
+
+    def present_device(self, frame_buffer_ptr, presented_ptr):
+        ms = C.c_float()
+        self._check(self._lib.b200rt_present_device(self._h, C.c_uint64(frame_buffer_ptr), C.c_uint64(presented_ptr), C.byref(ms)))
+        return ms.value
+
+    def time_resident(self, repeat=1):
+        """Average device time (ms) of render and FXAA kernels over `repeat` launches on resident inputs."""
+        a, b = C.c_float(), C.c_float()
+        self._check(self._lib.b200rt_time_resident(self._h, repeat, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    @property
+    def stream(self):
+        return self._lib.b200rt_stream(self._h)

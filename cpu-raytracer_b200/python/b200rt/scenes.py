@@ -141,18 +141,21 @@ def dynamic(data, out, width=1920, height=1080):
 
 
 def dielectrics_small(data, out, width=1920, height=1080):
-    """Config 4 without the (missing) Sponza hall: Diamond, Magnifier, two glass spheres, a mirror-ish
-    floor. 8 bounces + EWA filter exercise the reflect/refract recursion and the most expensive filter."""
+    """Config 4 without the (missing) Sponza hall: the camera looks through the lens of Magnifier.obj
+    (Kt 1, Ni 1.45, placed as in SCENE_SPONZA, Scene.cpp:75-130) at Diamond.obj (Ni 2.4), two glass
+    spheres (Scene.cpp:8-19), a Monkey, the Concave.obj mirror and a textured floor. 8 bounces and
+    the EWA filter exercise the full reflect / refract recursion and the most expensive filter."""
     s = SceneWriter(width, height)
-    s.camera((0.0, 2.5, -7.0), axis_angle((1, 0, 0), F(0.18)))
+    s.camera((14.0, 19.0, 0.0), (0.0, -0.707107, 0.0, 0.707107))  # looks along -x, like the shipped camera
     s.ambient((0.2, 0.2, 0.2))
     s.sky(os.path.join(data, "sky_256.float"))
-    s.sphere(1.0, (-2.5, 0.0, 2.0), diffuse=(0.2, 0.2, 0.0), reflection=(0.6, 0.6, 0.0), transmittance=(0.6, 0.6, 0.6), ior=1.33)
-    s.sphere(1.0, (+2.5, 0.0, 2.0), diffuse=(0.0, 0.2, 0.2), reflection=(0.0, 0.6, 0.6), transmittance=(0.6, 0.6, 0.6), ior=1.68)
-    s.plane((0.0, -1.0, 0.0), axis_angle((0, 1, 0), F(0.25) * PI), reflection=(0.1, 0.1, 0.1), texture=os.path.join(data, "bricks.png"))
-    s.mesh(os.path.join(data, "Diamond.obj"), (0.0, 0.0, 1.0))
-    s.mesh(os.path.join(data, "Magnifier.obj"), (0.0, 1.0, -3.0), axis_angle((1, 0, 0), F(-1.2)))
-    s.mesh(os.path.join(data, "Monkey.obj"), (0.0, 1.0, 6.0), axis_angle((0, 1, 0), PI))
-    s.point_light((20.0, 20.0, 20.0), (0.0, 6.0, -2.0))
-    s.directional_light((0.5, 0.5, 0.5), (0.3, -1.0, 0.2))
+    s.sphere(2.0, (-7.0, 16.0, -4.5), diffuse=(0.2, 0.2, 0.0), reflection=(0.6, 0.6, 0.0), transmittance=(0.6, 0.6, 0.6), ior=1.33)
+    s.sphere(2.0, (-7.0, 16.0, +4.5), diffuse=(0.0, 0.2, 0.2), reflection=(0.0, 0.6, 0.6), transmittance=(0.6, 0.6, 0.6), ior=1.68)
+    s.plane((0.0, 12.0, 0.0), axis_angle((0, 1, 0), F(0.25) * PI), reflection=(0.1, 0.1, 0.1), texture=os.path.join(data, "bricks.png"))
+    s.mesh(os.path.join(data, "Magnifier.obj"))
+    s.mesh(os.path.join(data, "Diamond.obj"), (-5.0, 20.0, 0.0), axis_angle((0, 0, 1), F(0.6)))
+    s.mesh(os.path.join(data, "Monkey.obj"), (-9.0, 22.5, 3.0), axis_angle((0, 1, 0), F(0.5) * PI))
+    s.mesh(os.path.join(data, "Concave.obj"), (-16.0, 12.0, 0.0), axis_angle((0, 1, 0), PI))
+    s.point_light((400.0, 400.0, 400.0), (6.0, 30.0, 6.0))
+    s.directional_light((0.5, 0.5, 0.5), (-0.3, -1.0, 0.2))
     return s.write(out)

@@ -134,6 +134,9 @@ typedef struct {
 	/* Multi-GPU tile partition: this context renders the 32x32 tiles whose
 	 * row-major id t satisfies t % tile_stride == tile_phase. 1 / 0 = the whole frame.       */
 	int32_t tile_stride, tile_phase;
+	/* 1 = also count BVH nodes visited / triangles tested / texels fetched (b200rt_stats), the
+	 * run-time cousin of BVH_VISUALIZE_HEATMAP (Config.h:23). Costs registers: keep 0 when timing. */
+	int32_t count_traversal;
 } b200rt_config;
 
 /* Counters of one frame. Rays are ACTIVE rays (one per traced ray), which is what the
