@@ -1,0 +1,373 @@
+#!/usr/bin/env python3
+"""bench.py — the headline benchmark of the render hot path (BASELINE.json: Mrays/s and frames/s,
+Sponza 1920x1080, trilinear mip-maps, point + directional light with shadows, 3 bounces).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+One "step" = one frame of the hot path: trace every tile (primary rays, shadow rays, reflection /
+refraction recursion, texture filtering) + the FXAA pass. Prints ONE JSON line on rank 0.
+
+  value   whole-job Mrays/s with every input resident in HBM (kernels only, CUDA events on the
+          launching stream, L2 flushed between steps), rays = active rays of the frame
+  e2e     the same metric through the public per-frame call b200rt_render_frame: host Scene::update,
+          pinned-host -> device copy of the frame data, kernels, device -> host read of both images
+  roofline  render kernel: algorithmic bytes of the frame (DESIGN.md "Algorithmic bytes") / its
+          CUDA-event duration, against the measured HBM copy peak (MEASURED_PEAKS.json)
+  cpu_baseline  the reference's own AVX renderer (oracle/_ref, SIMD_LANE_SIZE 8, all host threads)
+          on a bounded sample of the same workload
+
+Sponza's OBJ is absent from the reference checkout (.MISSING_LARGE_BLOBS) and there is no network:
+the geometry is the deterministic procedural stand-in of cpu-raytracer_b200/python/b200rt/standin.py
+(seed 1234, ~262 k triangles), `data` says so.
+
+--impl reference: times the reference's CPU implementation of the same path on the host cores
+(rank 0 only), same metric / unit / config.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(REPO, "cpu-raytracer_b200", "python"))
+
+WIDTH, HEIGHT, BOUNCES, FILTER = 1920, 1080, 3, "tri"
+REF_VARIANT = "l8_b3_tri"
+METRIC = "Mrays/s, Sponza(stand-in) 1920x1080, trilinear mip-maps, point+directional light with shadows, 3 bounces"
+L2_FLUSH_BYTES = 256 << 20
+
+
+def workload_config(n_gpus):
+    return {
+        "workload": "configs[1]: Sponza 1920x1080 trilinear, point + directional lights with shadows, 3 bounces (stand-in geometry, seed 1234)",
+        "resolution": [WIDTH, HEIGHT], "bounces": BOUNCES, "mipmap_filter": "trilinear", "fxaa": True,
+        "tiles": "32x32, tile t -> GPU t %% %d, device-side work counter per GPU" % n_gpus,
+        "l2": "flushed between timed steps (256 MiB memset, outside the timed region)",
+        "ray_count": "active rays (primary + shadow + reflection + refraction), reference's PerformanceStats per ray",
+    }
+
+
+def load_peaks():
+    path = os.path.join(REPO, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    QUERY = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, device):
+        self.device, self.samples, self.proc = device, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.QUERY, "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append([x.strip() for x in line.split(",")])
+
+    def __exit__(self, *exc):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+
+    def summary(self):
+        sm = [float(s[0]) for s in self.samples if s and s[0].replace(".", "").isdigit()]
+        mx = [float(s[1]) for s in self.samples if len(s) > 1 and s[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for s in self.samples if len(s) >= 6 for i in range(4) if s[2 + i].lower().startswith("active")})
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm)}
+
+
+def build_scene():
+    from b200rt import standin
+    from b200rt.host import HostScene
+    scene_file = standin.sponza_standin(width=WIDTH, height=HEIGHT)
+    scene = HostScene(scene_file)
+    scene.update(0.0, 0)
+    return scene_file, scene
+
+
+def algorithmic_bytes(stats, pixels):
+    """bytes the reference's algorithm moves for this frame (render kernel only)."""
+    return (32 * stats["nodes_visited"] + 36 * stats["triangles_tested"] + (64 + 64) * stats["hits_accepted"]
+            + 64 * stats["instances_entered"] + 12 * stats["texels_fetched"] + 4 * pixels)
+
+
+# ------------------------------------------------------------------------- reference / CPU arm ---
+def reference_frames(scene_file, frames, threads=None):
+    """Runs the reference's AVX renderer (oracle/_ref) for `frames` frames; returns ms per frame list or None."""
+    binary = os.path.join(REPO, "oracle", "_ref", "bin", "ref_" + REF_VARIANT)
+    if not os.path.exists(binary):
+        return None
+    env = dict(os.environ)
+    if threads:
+        env["REF_THREADS"] = str(threads)
+    out = subprocess.run([binary, scene_file, "--frames", str(frames), "--width", str(WIDTH), "--height", str(HEIGHT)],
+                         capture_output=True, text=True, env=env, check=True).stdout
+    info = json.loads([l for l in out.splitlines() if l.startswith("{")][-1])
+    return info
+
+
+def cpu_baseline(scene_file, pack, rays, frames):
+    """The reference's CPU path on this box's host cores, bounded sample (`frames` full frames after 1 warm-up)."""
+    cores = os.cpu_count() or 1
+    info = None
+    try:
+        info = reference_frames(scene_file, frames + 1)
+    except (subprocess.CalledProcessError, OSError, ValueError, IndexError):
+        info = None
+    if info is not None:
+        ms = statistics.median(info["ms_total"][1:])
+        return {"value": rays / ms / 1e3, "unit": "Mrays/s", "cores": info["threads"], "kind": "reference",
+                "sample": "%d full 1920x1080 frames of the same scene after 1 warm-up, median; reference AVX path (SIMD_LANE_SIZE 8) built by oracle/ref_recipe, %d threads" % (frames, info["threads"]),
+                "ms_per_frame": ms, "frames_per_s": 1e3 / ms,
+                "rays_reference_convention": sum(info["rays"].values())}
+    # the reference binary did not travel: time the C port instead (only place bench.py may run oracle/)
+    sys.path.insert(0, os.path.join(REPO, "oracle"))
+    import oracle_ffi
+    times = []
+    for _ in range(max(2, frames // 2)):
+        t = time.perf_counter()
+        oracle_ffi.render(pack, BOUNCES, FILTER, want_ids=False, threads=cores)
+        times.append((time.perf_counter() - t) * 1e3)
+    ms = statistics.median(times[1:]) if len(times) > 1 else times[0]
+    return {"value": rays / ms / 1e3, "unit": "Mrays/s", "cores": cores, "kind": "port",
+            "sample": "%d full frames, C oracle port (scalar per ray), %d threads" % (len(times), cores), "ms_per_frame": ms, "frames_per_s": 1e3 / ms}
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    scene_file, scene = build_scene()
+    pack = scene.pack()
+    # active rays of the frame, from the C oracle's counters (deterministic, = the GPU path's counters)
+    sys.path.insert(0, os.path.join(REPO, "oracle"))
+    import oracle_ffi
+    stats = oracle_ffi.render(pack, BOUNCES, FILTER, want_ids=False)["stats"]
+    rays = stats["primary_rays"] + stats["shadow_rays"] + stats["reflection_rays"] + stats["refraction_rays"]
+
+    frames = args.warmup + args.steps
+    info = None
+    try:
+        info = reference_frames(scene_file, frames)
+    except (subprocess.CalledProcessError, OSError, ValueError, IndexError):
+        info = None
+    if info is not None:
+        ms = info["ms_total"][args.warmup:]
+        kind, cores = "reference", info["threads"]
+        sample = "each step = one full 1920x1080 frame, reference AVX path (SIMD_LANE_SIZE 8), %d threads" % cores
+    else:
+        cores = os.cpu_count() or 1
+        ms = []
+        for i in range(frames):
+            t = time.perf_counter()
+            oracle_ffi.render(pack, BOUNCES, FILTER, want_ids=False, threads=cores)
+            if i >= args.warmup:
+                ms.append((time.perf_counter() - t) * 1e3)
+        kind = "port"
+        sample = "each step = one full 1920x1080 frame, C oracle port, %d threads" % cores
+    total_ms = sum(ms)
+    value = rays * len(ms) / total_ms / 1e3
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": len(ms), "warmup": args.warmup,
+        "ms_per_step": total_ms / len(ms), "frames_per_s": 1e3 * len(ms) / total_ms, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic (procedural Sponza stand-in, seed 1234)", "config": workload_config(args.gpus),
+        "rays_per_frame": rays,
+        "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------ GPU arm ---
+def run_gpu_arm(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from b200rt.device import Renderer
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the render path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    scene_file, scene = build_scene()
+    pack = scene.pack()
+    pixels = WIDTH * HEIGHT
+
+    # one instrumented frame (outside every timed region): ray counts + traversal counters of the WHOLE frame
+    counting = Renderer(WIDTH, HEIGHT, BOUNCES, FILTER, device=local_rank, count_traversal=True)
+    counting.upload_static(pack)
+    full_stats = counting.render(pack, want_presented=False)["stats"]
+    counting.close()
+    rays = full_stats["primary_rays"] + full_stats["shadow_rays"] + full_stats["reflection_rays"] + full_stats["refraction_rays"]
+
+    renderer = Renderer(WIDTH, HEIGHT, BOUNCES, FILTER, device=local_rank, tile_stride=world, tile_phase=rank)
+    renderer.upload_static(pack)
+    stream = torch.cuda.current_stream()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device="cuda")
+    clocks = ClockSampler(local_rank)
+
+    if world == 1:
+        # ---- resident: kernels only, CUDA events on the launching stream (inside the library) ----------
+        first = renderer.render(pack)                      # uploads the frame once; also the e2e warm-up
+        for _ in range(args.warmup):
+            renderer.time_resident(1, L2_FLUSH_BYTES)
+        barrier()
+        with clocks:
+            ms_render, ms_fxaa = renderer.time_resident(args.steps, L2_FLUSH_BYTES)
+        barrier()
+        ms_step = ms_render + ms_fxaa
+        warm_render, warm_fxaa = renderer.time_resident(args.steps, 0)
+
+        # ---- e2e: Scene::update + b200rt_render_frame, host buffers in and out ------------------------
+        out = {"frame_buffer": first["frame_buffer"], "presented": first["presented"]}
+        for _ in range(args.warmup):
+            scene.update(0.0, 0)
+            renderer.render(pack.with_frame(scene.frame_view()), out=out)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            scene.update(0.0, 0)                           # host per-frame prep incl. TLAS rebuild (Scene.cpp:139-171)
+            frame_pack = pack.with_frame(scene.frame_view())
+            renderer.render(frame_pack, out=out)
+        barrier()
+        e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+        h2d = pack.frame_bytes()
+        d2h = pixels * 4 + pixels * 3
+        launches = 2 * args.steps
+        kernel_ms = ms_render
+    else:
+        # ---- N GPUs: each rank traces its interleaved tiles, one collective moves the frame to rank 0,
+        # rank 0 runs FXAA. Timed on the device with events on the stream everything is issued on. ------
+        renderer.set_stream(stream.cuda_stream)
+        fb = torch.zeros(HEIGHT, WIDTH, dtype=torch.int32, device="cuda")
+        presented = torch.empty(HEIGHT, WIDTH, 3, dtype=torch.uint8, device="cuda")
+        host_fb = torch.empty(HEIGHT, WIDTH, dtype=torch.int32).pin_memory()
+        host_rgb = torch.empty(HEIGHT, WIDTH, 3, dtype=torch.uint8).pin_memory()
+
+        def step(e2e):
+            if e2e:
+                scene.update(0.0, 0)
+                frame_pack = pack.with_frame(scene.frame_view())
+            else:
+                frame_pack = pack
+            renderer.render_device(frame_pack, fb.data_ptr())
+            dist.reduce(fb, dst=0, op=dist.ReduceOp.SUM)   # tiles are disjoint and the rest is zero: SUM == gather
+            if rank == 0:
+                renderer.present_device(fb.data_ptr(), presented.data_ptr())
+                if e2e:
+                    host_fb.copy_(fb, non_blocking=True)
+                    host_rgb.copy_(presented, non_blocking=True)
+                    torch.cuda.synchronize()
+            if rank != 0:
+                fb.zero_()
+
+        for _ in range(args.warmup):
+            step(False)
+        barrier()
+        with clocks:
+            start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            total = 0.0
+            for _ in range(args.steps):
+                flush.fill_(1)                              # evict L2, outside the timed region
+                barrier()
+                start.record(stream)
+                step(False)
+                end.record(stream)
+                torch.cuda.synchronize()
+                total += start.elapsed_time(end)
+        barrier()
+        t = torch.tensor([total / args.steps], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_step = float(t.item())
+        ms_render, ms_fxaa, warm_render, warm_fxaa = ms_step, 0.0, None, None
+        kernel_ms = None
+
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            step(True)
+        barrier()
+        t = torch.tensor([(time.perf_counter() - t0) * 1e3 / args.steps], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_ms = float(t.item())
+        h2d = pack.frame_bytes()
+        d2h = (pixels * 4 + pixels * 3) if rank == 0 else 0
+        launches = (2 if rank == 0 else 1) * args.steps
+
+    if rank == 0:
+        peak, peak_source = load_peaks()
+        alg_bytes = algorithmic_bytes(full_stats, pixels)
+        roofline = None
+        if kernel_ms:
+            achieved = alg_bytes / (kernel_ms * 1e-3) / 1e9
+            roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                        "kernel": "render_kernel<false>", "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": alg_bytes,
+                        "peak_source": peak_source,
+                        "note": "working set (BVH + triangles) is L2-resident: this is an L2/latency regime, HBM peak is the agreed denominator"}
+        baseline = cpu_baseline(scene_file, pack, rays, frames=6) if world == 1 else None
+        line = {
+            "metric": METRIC, "value": rays / ms_step / 1e3, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_step, "frames_per_s": 1e3 / ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic (procedural Sponza stand-in, seed 1234; sponza.obj is missing from the reference checkout)",
+            "config": workload_config(world),
+            "rays_per_frame": rays, "rays": {k: full_stats[k] for k in ("primary_rays", "shadow_rays", "reflection_rays", "refraction_rays")},
+            "ms_render_kernel": ms_render, "ms_fxaa_kernel": ms_fxaa,
+            "warm_l2": None if warm_render is None else {"ms_render_kernel": warm_render, "ms_fxaa_kernel": warm_fxaa, "value": rays / (warm_render + warm_fxaa) / 1e3},
+            "e2e": {"value": rays / e2e_ms / 1e3, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "frames_per_s": 1e3 / e2e_ms},
+            "gpu_launches": launches,
+            "clocks": clocks.summary(),
+            "roofline": roofline,
+            "cpu_baseline": baseline,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    return run_gpu_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -36,7 +36,8 @@ struct DeviceBuffer {
 struct b200rt_ctx {
 	b200rt_config config;
 	std::string   error;
-	cudaStream_t  stream = nullptr;
+	cudaStream_t  stream = nullptr;      // stream in use (the context's own, or a caller's: b200rt_set_stream)
+	cudaStream_t  own_stream = nullptr;
 	cudaEvent_t   ev[4] = { nullptr, nullptr, nullptr, nullptr }; // total begin, render begin, render end / fxaa begin, fxaa end
 
 	// static scene in HBM
@@ -50,7 +51,7 @@ struct b200rt_ctx {
 	void * frame_staging = nullptr; size_t frame_staging_bytes = 0;
 
 	// outputs
-	DeviceBuffer frame_buffer, presented, colour_float, ids, hits, counters;
+	DeviceBuffer frame_buffer, presented, colour_float, ids, hits, counters, l2_scratch;
 	void * pinned_out = nullptr; size_t pinned_out_bytes = 0;
 	FrameCounters * pinned_counters = nullptr;
 
@@ -66,6 +67,13 @@ static int fail(b200rt_ctx * ctx, const std::string & message) { ctx->error = me
 extern "C" const char * b200rt_last_error(const b200rt_ctx * ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
 
 extern "C" uint64_t b200rt_stream(const b200rt_ctx * ctx) { return ctx ? uint64_t(reinterpret_cast<uintptr_t>(ctx->stream)) : 0; }
+
+extern "C" int b200rt_set_stream(b200rt_ctx * ctx, uint64_t stream) {
+	if (!ctx) return -1;
+	cudaStreamSynchronize(ctx->stream);
+	ctx->stream = stream ? reinterpret_cast<cudaStream_t>(uintptr_t(stream)) : ctx->own_stream;
+	return 0;
+}
 
 extern "C" int b200rt_create(const b200rt_config * config, b200rt_ctx ** out) {
 	if (!config || !out) { g_create_error = "null argument"; return -1; }
@@ -87,7 +95,8 @@ extern "C" int b200rt_create(const b200rt_config * config, b200rt_ctx ** out) {
 
 	auto bail = [&](const char * what, cudaError_t err) { g_create_error = std::string(what) + ": " + cudaGetErrorString(err); b200rt_destroy(ctx); return -1; };
 
-	if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
+	if ((e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
+	ctx->stream = ctx->own_stream;
 	for (auto & ev : ctx->ev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) return bail("cudaEventCreate", e);
 
 	cudaDeviceProp prop;
@@ -125,12 +134,12 @@ extern "C" void b200rt_destroy(b200rt_ctx * ctx) {
 	cudaSetDevice(ctx->config.device);
 	if (ctx->stream) cudaStreamSynchronize(ctx->stream);
 	for (DeviceBuffer * b : { &ctx->nodes, &ctx->hot, &ctx->cold, &ctx->materials, &ctx->textures, &ctx->texels, &ctx->sky, &ctx->gamma,
-	                          &ctx->frame_block, &ctx->frame_buffer, &ctx->presented, &ctx->colour_float, &ctx->ids, &ctx->hits, &ctx->counters }) b->release();
+	                          &ctx->frame_block, &ctx->frame_buffer, &ctx->presented, &ctx->colour_float, &ctx->ids, &ctx->hits, &ctx->counters, &ctx->l2_scratch }) b->release();
 	if (ctx->frame_staging) cudaFreeHost(ctx->frame_staging);
 	if (ctx->pinned_out) cudaFreeHost(ctx->pinned_out);
 	if (ctx->pinned_counters) cudaFreeHost(ctx->pinned_counters);
 	for (auto & ev : ctx->ev) if (ev) cudaEventDestroy(ev);
-	if (ctx->stream) cudaStreamDestroy(ctx->stream);
+	if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
 	delete ctx;
 }
 
@@ -375,6 +384,7 @@ static void fill_stats(b200rt_ctx * ctx, b200rt_stats * stats) {
 	const FrameCounters & c = *ctx->pinned_counters;
 	stats->primary_rays = c.primary; stats->shadow_rays = c.shadow; stats->reflection_rays = c.reflection; stats->refraction_rays = c.refraction;
 	stats->nodes_visited = c.nodes; stats->triangles_tested = c.triangles; stats->texels_fetched = c.texels;
+	stats->hits_accepted = c.accepted; stats->instances_entered = c.instances;
 	stats->device_ms_render = stats->device_ms_fxaa = stats->device_ms_total = 0.0f;
 	cudaEventElapsedTime(&stats->device_ms_render, ctx->ev[1], ctx->ev[2]);
 	cudaEventElapsedTime(&stats->device_ms_fxaa,   ctx->ev[2], ctx->ev[3]);
@@ -466,14 +476,16 @@ extern "C" int b200rt_present_device(b200rt_ctx * ctx, uint64_t frame_buffer_dev
 	return 0;
 }
 
-extern "C" int b200rt_time_resident(b200rt_ctx * ctx, int repeat, float * ms_render, float * ms_fxaa) {
+extern "C" int b200rt_time_resident(b200rt_ctx * ctx, int repeat, uint64_t flush_l2_bytes, float * ms_render, float * ms_fxaa) {
 	if (!ctx) return -1;
 	if (!ctx->have_frame) return fail(ctx, "no frame has been rendered yet");
 	if (repeat < 1) repeat = 1;
 	CHECK_CUDA(ctx, cudaSetDevice(ctx->config.device));
 	unsigned * fb = static_cast<unsigned *>(ctx->frame_buffer.ptr);
 	float total_render = 0.0f, total_fxaa = 0.0f;
+	if (flush_l2_bytes) CHECK_CUDA(ctx, ctx->l2_scratch.ensure(size_t(flush_l2_bytes)));
 	for (int i = 0; i < repeat; i++) {
+		if (flush_l2_bytes) CHECK_CUDA(ctx, cudaMemsetAsync(ctx->l2_scratch.ptr, i & 0xff, size_t(flush_l2_bytes), ctx->stream)); // evict L2, untimed
 		CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
 		if (launch_render(ctx, fb, nullptr, false)) return -1;
 		CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));

@@ -68,7 +68,7 @@ struct SceneParams {
 
 struct FrameCounters {   // accumulated with one atomicAdd per warp
 	unsigned long long primary, shadow, reflection, refraction;
-	unsigned long long nodes, triangles, texels;
+	unsigned long long nodes, triangles, texels, accepted, instances;
 	unsigned int next_unit;      // work-stealing cursor (WorkerThread.cpp:53-54)
 	unsigned int pad;
 };

@@ -30,7 +30,7 @@ render_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, float *
 	const int lane = threadIdx.x & 31;
 	const unsigned total_units = unsigned(P.tile_count_mine) * 32u;
 
-	Counters cnt = { 0, 0, 0, 0, 0, 0 };
+	Counters cnt = { 0, 0, 0, 0, 0, 0, 0, 0 };
 	unsigned primary = 0;
 
 	for (;;) {
@@ -62,7 +62,10 @@ render_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, float *
 	}
 	if (COUNT) {
 		const unsigned s_nodes = warp_sum(cnt.nodes), s_tris = warp_sum(cnt.triangles), s_texels = warp_sum(cnt.texels);
+		const unsigned s_accepted = warp_sum(cnt.accepted), s_instances = warp_sum(cnt.instances);
 		if (lane == 0) {
+			atomicAdd(&counters->accepted, (unsigned long long)s_accepted);
+			atomicAdd(&counters->instances, (unsigned long long)s_instances);
 			atomicAdd(&counters->nodes, (unsigned long long)s_nodes);
 			atomicAdd(&counters->triangles, (unsigned long long)s_tris);
 			atomicAdd(&counters->texels, (unsigned long long)s_texels);
@@ -79,7 +82,7 @@ primary_hits_kernel(const SceneParams P, int * __restrict__ ids, float * __restr
 	if (px >= P.width || py >= P.height) return;
 
 	const Ray ray = primary_ray(P, px, py);
-	Counters cnt = { 0, 0, 0, 0, 0, 0 };
+	Counters cnt = { 0, 0, 0, 0, 0, 0, 0, 0 };
 	Candidate best;
 	trace_closest<false>(P, ray.origin, ray.direction, best, cnt);
 

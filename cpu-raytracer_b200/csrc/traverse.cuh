@@ -33,7 +33,7 @@ struct Candidate {         // closest hit so far
 	int primitive;         // flattened triangle index within its BLAS, or sphere / plane index
 };
 
-struct Counters { unsigned nodes, triangles, texels, shadow, reflection, refraction; };
+struct Counters { unsigned nodes, triangles, texels, shadow, reflection, refraction, accepted, instances; };
 
 // AABB::intersect, AABB.cpp:38-52. MINPS/MAXPS NaN semantics matter: a ray with a zero
 // direction component lying exactly on a slab plane produces 0 * inf = NaN.
@@ -112,6 +112,7 @@ __device__ __forceinline__ void blas_trace(const float4 * __restrict__ nodes, co
 				float t, u, v;
 				if (COUNT) cnt.triangles++;
 				if (triangle_test(hot + 3 * size_t(i), o, d, best.t, t, u, v)) {
+					if (COUNT) cnt.accepted++;
 					best.t = t; best.u = u; best.v = v; best.instance = instance; best.primitive = i;
 				}
 			}
@@ -235,6 +236,7 @@ __device__ __forceinline__ void trace_closest(const SceneParams & P, v3 o, v3 d,
 			for (int i = left_or_first; i < left_or_first + count; i++) {
 				const int instance = __ldg(P.tlas_indices + i);
 				const DeviceInstance inst = load_instance_inverse(P.instances + instance);
+				if (COUNT) cnt.instances++;
 				// Mesh::trace, Mesh.cpp:17-31 (the differentials are transformed in shade.cuh, for the winner only)
 				blas_trace<COUNT>(P.nodes + 2 * size_t(inst.node_offset), P.triangles_hot + 3 * size_t(inst.triangle_offset),
 				                  transform_position(inst.inverse, o), transform_direction(inst.inverse, d), instance, best, blas_stack, cnt);
@@ -278,6 +280,7 @@ __device__ __forceinline__ bool trace_any(const SceneParams & P, v3 o, v3 d, flo
 			for (int i = left_or_first; i < left_or_first + count; i++) {
 				const int instance = __ldg(P.tlas_indices + i);
 				const DeviceInstance inst = load_instance_inverse(P.instances + instance);
+				if (COUNT) cnt.instances++;
 				if (blas_intersect<COUNT>(P.nodes + 2 * size_t(inst.node_offset), P.triangles_hot + 3 * size_t(inst.triangle_offset),
 				                          transform_position(inst.inverse, o), transform_direction(inst.inverse, d), max_distance, blas_stack, cnt)) return true;
 			}

@@ -54,6 +54,7 @@ class Stats(C.Structure):
     _fields_ = [
         ("primary_rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("reflection_rays", C.c_uint64), ("refraction_rays", C.c_uint64),
         ("nodes_visited", C.c_uint64), ("triangles_tested", C.c_uint64), ("texels_fetched", C.c_uint64),
+        ("hits_accepted", C.c_uint64), ("instances_entered", C.c_uint64),
         ("device_ms_render", C.c_float), ("device_ms_fxaa", C.c_float), ("device_ms_total", C.c_float),
     ]
 
@@ -119,7 +120,8 @@ def device_lib():
         lib.b200rt_render_frame.argtypes = [C.c_void_p, C.POINTER(Frame), C.POINTER(Outputs)]
         lib.b200rt_render_frame_device.argtypes = [C.c_void_p, C.POINTER(Frame), C.c_uint64, C.POINTER(Stats)]
         lib.b200rt_present_device.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_float)]
-        lib.b200rt_time_resident.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+        lib.b200rt_time_resident.argtypes = [C.c_void_p, C.c_int, C.c_uint64, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+        lib.b200rt_set_stream.argtypes = [C.c_void_p, C.c_uint64]
         lib.b200rt_stream.argtypes = [C.c_void_p]
         lib.b200rt_stream.restype = C.c_uint64
         _device = lib

@@ -86,11 +86,15 @@ class Renderer:
         self._check(self._lib.b200rt_present_device(self._h, C.c_uint64(frame_buffer_ptr), C.c_uint64(presented_ptr), C.byref(ms)))
         return ms.value
 
-    def time_resident(self, repeat=1):
+    def time_resident(self, repeat=1, flush_l2_bytes=0):
         """Average device time (ms) of render and FXAA kernels over `repeat` launches on resident inputs."""
         a, b = C.c_float(), C.c_float()
-        self._check(self._lib.b200rt_time_resident(self._h, repeat, C.byref(a), C.byref(b)))
+        self._check(self._lib.b200rt_time_resident(self._h, repeat, C.c_uint64(flush_l2_bytes), C.byref(a), C.byref(b)))
         return a.value, b.value
+
+    def set_stream(self, stream):
+        """Issue this context's work on a caller-owned CUDA stream (integer handle); 0 = back to its own."""
+        self._check(self._lib.b200rt_set_stream(self._h, C.c_uint64(stream)))
 
     @property
     def stream(self):

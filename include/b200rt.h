@@ -145,7 +145,9 @@ typedef struct {
 	uint64_t primary_rays, shadow_rays, reflection_rays, refraction_rays;
 	uint64_t nodes_visited;        /* TLAS + BLAS nodes whose box was tested                 */
 	uint64_t triangles_tested;
-	uint64_t texels_fetched;
+	uint64_t texels_fetched;       /* texture texels + sky probe texels                        */
+	uint64_t hits_accepted;        /* closest-hit candidates that replaced the running closest hit */
+	uint64_t instances_entered;    /* Mesh::trace / Mesh::intersect calls (TLAS leaf visits)    */
 	float    device_ms_render;     /* CUDA-event time of the ray tracing kernel(s)           */
 	float    device_ms_fxaa;       /* CUDA-event time of the FXAA kernel                     */
 	float    device_ms_total;      /* uploads + kernels + downloads on the context's stream  */
@@ -187,12 +189,17 @@ int b200rt_render_frame_device(b200rt_ctx * ctx, const b200rt_frame * frame,
  * multi-GPU gather): in uint32 [height][width], out uint8 [height][width][3].              */
 int b200rt_present_device(b200rt_ctx * ctx, uint64_t frame_buffer_dev, uint64_t presented_dev, float * device_ms);
 
-/* Re-times the last frame without host<->device traffic: `repeat` back-to-back launches of
- * the render (+FXAA) kernels on resident inputs; returns the average per-frame device time. */
-int b200rt_time_resident(b200rt_ctx * ctx, int repeat, float * ms_render, float * ms_fxaa);
+/* Re-times the last frame without host<->device traffic: `repeat` launches of the render
+ * (+FXAA) kernels on resident inputs, each timed with CUDA events on the context's stream;
+ * returns the average per-frame device times. flush_l2_bytes > 0: before every timed launch
+ * (outside the timed region) a scratch buffer of that size is overwritten to evict L2.       */
+int b200rt_time_resident(b200rt_ctx * ctx, int repeat, uint64_t flush_l2_bytes, float * ms_render, float * ms_fxaa);
 
-/* The CUDA stream (cudaStream_t as integer) all work of this context is issued on.        */
+/* The CUDA stream (cudaStream_t as integer) all work of this context is issued on. A caller
+ * that orders this context's work against its own (e.g. NCCL on a torch stream) may replace
+ * it; stream 0 restores the context's own stream. The context never owns a caller's stream.  */
 uint64_t b200rt_stream(const b200rt_ctx * ctx);
+int      b200rt_set_stream(b200rt_ctx * ctx, uint64_t stream);
 
 #ifdef __cplusplus
 }

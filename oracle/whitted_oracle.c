@@ -52,7 +52,7 @@ typedef struct {           /* RayHit.h:4-22 (+ ids, as in the instrumented refer
 
 typedef struct {           /* per-thread counters */
 	uint64_t primary, shadow, reflection, refraction;
-	uint64_t nodes, triangles, texels;
+	uint64_t nodes, triangles, texels, accepted, instances;
 } counters_t;
 
 typedef struct {
@@ -221,6 +221,7 @@ static void blas_trace(const ctx_t * ctx, const b200rt_blas * blas, const ray_t 
 				float t, u, v;
 				cnt->triangles++;
 				if (triangle_test(&hot[i], ray->origin, ray->direction, hit->distance, &t, &u, &v)) {
+					cnt->accepted++;
 					triangle_hit_record(&hot[i], &cold[i], blas->material_offset, ray, world, t, u, v, hit);
 					hit->instance_id = instance;
 					hit->triangle_id = i;
@@ -273,6 +274,7 @@ static int blas_intersect(const ctx_t * ctx, const b200rt_blas * blas, v3 origin
 /* Mesh::trace, Mesh.cpp:17-31: ray (and its four differentials) into object space */
 static void mesh_trace(const ctx_t * ctx, int instance, const ray_t * ray, hit_t * hit, counters_t * cnt) {
 	const b200rt_instance * inst = &ctx->f->instances[instance];
+	cnt->instances++;
 	ray_t local;
 	local.origin    = transform_position (inst->inverse, ray->origin);
 	local.direction = transform_direction(inst->inverse, ray->direction);
@@ -286,6 +288,7 @@ static void mesh_trace(const ctx_t * ctx, int instance, const ray_t * ray, hit_t
 /* Mesh::intersect, Mesh.cpp:33-40 */
 static int mesh_intersect(const ctx_t * ctx, int instance, v3 origin, v3 direction, float max_distance, counters_t * cnt) {
 	const b200rt_instance * inst = &ctx->f->instances[instance];
+	cnt->instances++;
 	return blas_intersect(ctx, &ctx->s->blas[inst->blas], transform_position(inst->inverse, origin), transform_direction(inst->inverse, direction), max_distance, cnt);
 }
 
@@ -989,6 +992,7 @@ int oracle_render(const b200rt_static_scene * scene, const b200rt_frame * frame,
 			s->primary_rays += workers[t].cnt.primary; s->shadow_rays += workers[t].cnt.shadow;
 			s->reflection_rays += workers[t].cnt.reflection; s->refraction_rays += workers[t].cnt.refraction;
 			s->nodes_visited += workers[t].cnt.nodes; s->triangles_tested += workers[t].cnt.triangles; s->texels_fetched += workers[t].cnt.texels;
+			s->hits_accepted += workers[t].cnt.accepted; s->instances_entered += workers[t].cnt.instances;
 		}
 	}
 	free(workers); free(ids);
