@@ -274,6 +274,9 @@ def run_gpu_arm(args):
         host_fb = torch.empty(HEIGHT, WIDTH, dtype=torch.int32).pin_memory()
         host_rgb = torch.empty(HEIGHT, WIDTH, 3, dtype=torch.uint8).pin_memory()
 
+        from b200rt.multigpu import FrameGather
+        gather = FrameGather()
+
         def step(e2e):
             if e2e:
                 scene.update(0.0, 0)
@@ -281,7 +284,7 @@ def run_gpu_arm(args):
             else:
                 frame_pack = pack
             renderer.render_device(frame_pack, fb.data_ptr())
-            dist.reduce(fb, dst=0, op=dist.ReduceOp.SUM)   # tiles are disjoint and the rest is zero: SUM == gather
+            gather(fb)                                     # tiles are disjoint and the rest is zero: SUM == gather (b200rt/multigpu.py)
             if rank == 0:
                 renderer.present_device(fb.data_ptr(), presented.data_ptr())
                 if e2e:

@@ -165,6 +165,7 @@ extern "C" int b200rt_upload_static(b200rt_ctx * ctx, const b200rt_static_scene 
 		const b200rt_blas & d = s->blas[b];
 		if (d.node_offset < 0 || d.node_count <= 0 || d.node_offset + d.node_count > s->node_count || d.triangle_offset < 0 || d.triangle_count < 0 || d.triangle_offset + d.triangle_count > s->triangle_count) return fail(ctx, "BLAS range out of bounds");
 		for (int n = 0; n < d.node_count; n++) {
+			if (n == 1) continue; // never written by the reference's builders (BottomLevelBVH.cpp:92,132): unreachable, may hold garbage
 			const b200rt_bvh_node & node = s->nodes[d.node_offset + n];
 			const int count = node.count & 0x3FFFFFFF;
 			if (count > 0) { if (node.left_or_first < 0 || node.left_or_first + count > d.triangle_count) return fail(ctx, "BLAS leaf range out of bounds"); }
@@ -255,6 +256,7 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 		if (f->tlas_indices[i] < 0 || f->tlas_indices[i] >= f->instance_count) return fail(ctx, "TLAS primitive index out of range");
 	}
 	for (int n = 0; n < f->tlas_node_count; n++) {
+		if (n == 1) continue; // unused slot, as in the BLAS
 		const b200rt_bvh_node & node = f->tlas_nodes[n];
 		const int count = node.count & 0x3FFFFFFF;
 		if (count > 0) { if (node.left_or_first < 0 || node.left_or_first + count > f->instance_count) return fail(ctx, "TLAS leaf range out of bounds"); }

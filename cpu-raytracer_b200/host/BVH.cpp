@@ -146,6 +146,10 @@ void BottomLevelBVH::load_from_disk(const std::string & name) {
 	read_array(file.f, file_indices, index_count, name);
 
 	for (int i : file_indices) if (i < 0 || size_t(i) >= triangle_count) throw std::runtime_error("index out of range in BVH cache " + name);
+	// Node 1 is never written by the reference's builders (root 0, child pairs from 2:
+	// BottomLevelBVH.cpp:92,132), so a cache written by the reference holds heap garbage there.
+	// It is unreachable; clear it instead of validating it.
+	if (n_nodes > 1) memset(&nodes[1], 0, sizeof(BVHNode));
 	for (const BVHNode & n : nodes) {
 		if (node_is_leaf(n)) {
 			if (n.left_or_first < 0 || size_t(n.left_or_first) + size_t(node_count(n)) > index_count) throw std::runtime_error("leaf range out of bounds in BVH cache " + name);
