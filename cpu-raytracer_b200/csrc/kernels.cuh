@@ -25,7 +25,7 @@ __device__ __forceinline__ bool unit_pixel(const SceneParams & P, unsigned unit,
 // Persistent warps pull units off one device-side counter — the GPU form of the reference's
 // InterlockedDecrement tile countdown (WorkerThread.cpp:53-65).
 template<bool COUNT>
-__global__ void __launch_bounds__(RT_BLOCK_THREADS)
+__global__ void __launch_bounds__(RT_BLOCK_THREADS, RT_MIN_BLOCKS)
 render_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, float * __restrict__ colour_float, FrameCounters * __restrict__ counters) {
 	const int lane = threadIdx.x & 31;
 	const unsigned total_units = unsigned(P.tile_count_mine) * 32u;

@@ -10,6 +10,10 @@ namespace rt {
 
 #define RT_MAX_BOUNCES 8
 #define RT_BLOCK_THREADS 256
+#ifndef RT_MIN_BLOCKS
+#define RT_MIN_BLOCKS 4   // resident 256-thread blocks per SM the register allocation is sized for: 64 registers, 32 warps/SM.
+                          // Measured on the bench frame (gpurun_out/r1_variants_*.log): 2 -> 1.87 ms, 3 -> 1.53, 4 -> 1.46, 5 -> 1.48, 6 -> 1.57, 8 -> 1.69
+#endif
 
 // Raytracer::render_tile, Raytracer.cpp:45-59: primary ray + its differentials for pixel (i, j)
 __device__ __forceinline__ Ray primary_ray(const SceneParams & P, int i, int j) {

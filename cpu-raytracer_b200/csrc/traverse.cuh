@@ -37,11 +37,28 @@ struct Counters { unsigned nodes, triangles, texels, shadow, reflection, refract
 
 // AABB::intersect, AABB.cpp:38-52. MINPS/MAXPS NaN semantics matter: a ray with a zero
 // direction component lying exactly on a slab plane produces 0 * inf = NaN.
-__device__ __forceinline__ bool aabb_intersect(float4 n0, float4 n1, v3 o, v3 inv_d, float max_distance) {
+//
+// The slab distances are computed with the reference's operations ((plane - o) * inv_d). How the
+// six of them are reduced depends on the ray:
+//   regular ray  (origin and 1/direction all finite): no NaN can appear (finite - finite is finite,
+//     finite * finite is finite or +-inf), so MINPS/MAXPS equal IEEE min/max and the reduction is
+//     6 FMNMX + 2 FMNMX3 instead of 24 FSETP+FSEL — the v1 profile had 31 % of all issued
+//     instructions there (profiles/r01_ncu_full_render_v1.csv);
+//   irregular ray (a zero direction component, or NaN upstream): the exact x86 emulation.
+// `exact` is a per-ray flag, computed once per (ray, space).
+__device__ __forceinline__ bool ray_is_regular(v3 o, v3 inv_d) {
+	return isfinite(o.x) && isfinite(o.y) && isfinite(o.z) && isfinite(inv_d.x) && isfinite(inv_d.y) && isfinite(inv_d.z);
+}
+__device__ __forceinline__ bool aabb_intersect(float4 n0, float4 n1, v3 o, v3 inv_d, float max_distance, bool exact) {
 	float t0x = (n0.x - o.x) * inv_d.x, t1x = (n0.w - o.x) * inv_d.x;
 	float t0y = (n0.y - o.y) * inv_d.y, t1y = (n1.x - o.y) * inv_d.y;
 	float t0z = (n0.z - o.z) * inv_d.z, t1z = (n1.y - o.z) * inv_d.z;
 
+	if (!exact) {
+		const float t_near = fmaxf(fmaxf(RT_EPSILON,   fminf(t0x, t1x)), fmaxf(fminf(t0y, t1y), fminf(t0z, t1z)));
+		const float t_far  = fminf(fminf(max_distance, fmaxf(t0x, t1x)), fminf(fmaxf(t0y, t1y), fmaxf(t0z, t1z)));
+		return t_near < t_far;
+	}
 	float tminx = sse_min(t0x, t1x), tmaxx = sse_max(t0x, t1x);
 	float tminy = sse_min(t0y, t1y), tmaxy = sse_max(t0y, t1y);
 	float tminz = sse_min(t0z, t1z), tmaxz = sse_max(t0z, t1z);
@@ -95,6 +112,7 @@ __device__ __forceinline__ DeviceInstance load_instance_inverse(const DeviceInst
 template<bool COUNT>
 __device__ __forceinline__ void blas_trace(const float4 * __restrict__ nodes, const float4 * __restrict__ hot, v3 o, v3 d, int instance, Candidate & best, int * stack, Counters & cnt) {
 	const v3 inv_d = V(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+	const bool exact = !ray_is_regular(o, inv_d);
 
 	int stack_size = 1;
 	stack[0] = 0;
@@ -104,7 +122,7 @@ __device__ __forceinline__ void blas_trace(const float4 * __restrict__ nodes, co
 		const float4 n0 = __ldg(nodes + 2 * index), n1 = __ldg(nodes + 2 * index + 1);
 		if (COUNT) cnt.nodes++;
 
-		if (!aabb_intersect(n0, n1, o, inv_d, best.t)) continue;
+		if (!aabb_intersect(n0, n1, o, inv_d, best.t, exact)) continue;
 
 		const int left_or_first = __float_as_int(n1.z), count = __float_as_int(n1.w);
 		if ((count & 0x3FFFFFFF) > 0) {
@@ -130,6 +148,7 @@ __device__ __forceinline__ void blas_trace(const float4 * __restrict__ nodes, co
 template<bool COUNT>
 __device__ __forceinline__ bool blas_intersect(const float4 * __restrict__ nodes, const float4 * __restrict__ hot, v3 o, v3 d, float max_distance, int * stack, Counters & cnt) {
 	const v3 inv_d = V(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+	const bool exact = !ray_is_regular(o, inv_d);
 
 	int stack_size = 1;
 	stack[0] = 0;
@@ -139,7 +158,7 @@ __device__ __forceinline__ bool blas_intersect(const float4 * __restrict__ nodes
 		const float4 n0 = __ldg(nodes + 2 * index), n1 = __ldg(nodes + 2 * index + 1);
 		if (COUNT) cnt.nodes++;
 
-		if (!aabb_intersect(n0, n1, o, inv_d, max_distance)) continue;
+		if (!aabb_intersect(n0, n1, o, inv_d, max_distance, exact)) continue;
 
 		const int left_or_first = __float_as_int(n1.z), count = __float_as_int(n1.w);
 		if ((count & 0x3FFFFFFF) > 0) {
@@ -221,6 +240,7 @@ __device__ __forceinline__ void trace_closest(const SceneParams & P, v3 o, v3 d,
 	int blas_stack[RT_STACK_SIZE];
 
 	const v3 inv_d = V(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+	const bool exact = !ray_is_regular(o, inv_d);
 	int stack_size = 1;
 	tlas_stack[0] = 0;
 
@@ -229,7 +249,7 @@ __device__ __forceinline__ void trace_closest(const SceneParams & P, v3 o, v3 d,
 		const float4 n0 = __ldg(P.tlas_nodes + 2 * index), n1 = __ldg(P.tlas_nodes + 2 * index + 1);
 		if (COUNT) cnt.nodes++;
 
-		if (!aabb_intersect(n0, n1, o, inv_d, best.t)) continue;
+		if (!aabb_intersect(n0, n1, o, inv_d, best.t, exact)) continue;
 
 		const int left_or_first = __float_as_int(n1.z), count = __float_as_int(n1.w);
 		if ((count & 0x3FFFFFFF) > 0) {
@@ -265,6 +285,7 @@ __device__ __forceinline__ bool trace_any(const SceneParams & P, v3 o, v3 d, flo
 	int blas_stack[RT_STACK_SIZE];
 
 	const v3 inv_d = V(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+	const bool exact = !ray_is_regular(o, inv_d);
 	int stack_size = 1;
 	tlas_stack[0] = 0;
 
@@ -273,7 +294,7 @@ __device__ __forceinline__ bool trace_any(const SceneParams & P, v3 o, v3 d, flo
 		const float4 n0 = __ldg(P.tlas_nodes + 2 * index), n1 = __ldg(P.tlas_nodes + 2 * index + 1);
 		if (COUNT) cnt.nodes++;
 
-		if (!aabb_intersect(n0, n1, o, inv_d, max_distance)) continue;
+		if (!aabb_intersect(n0, n1, o, inv_d, max_distance, exact)) continue;
 
 		const int left_or_first = __float_as_int(n1.z), count = __float_as_int(n1.w);
 		if ((count & 0x3FFFFFFF) > 0) {

@@ -110,7 +110,7 @@ def device_lib():
     """libb200rt.so — the CUDA render path. There is no CPU fallback: a missing library is an error."""
     global _device
     if _device is None:
-        lib = _load(os.path.join(PKG_ROOT, "libb200rt.so"))
+        lib = _load(os.environ.get("B200RT_LIB") or os.path.join(PKG_ROOT, "libb200rt.so"))  # B200RT_LIB: a kernel variant under test (tools/)
         lib.b200rt_create.argtypes = [C.POINTER(Config), C.POINTER(C.c_void_p)]
         lib.b200rt_destroy.argtypes = [C.c_void_p]
         lib.b200rt_destroy.restype = None
