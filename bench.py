@@ -249,7 +249,7 @@ def run_gpu_arm(args):
         warm_render, warm_fxaa = renderer.time_resident(args.steps, 0)
 
         # ---- e2e: Scene::update + b200rt_render_frame, host buffers in and out ------------------------
-        out = {"frame_buffer": first["frame_buffer"], "presented": first["presented"]}
+        out = renderer.alloc_outputs()                     # page-locked host images: the device -> host copies land in them directly
         for _ in range(args.warmup):
             scene.update(0.0, 0)
             renderer.render(pack.with_frame(scene.frame_view()), out=out)

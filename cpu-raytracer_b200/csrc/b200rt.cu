@@ -143,6 +143,23 @@ extern "C" void b200rt_destroy(b200rt_ctx * ctx) {
 	delete ctx;
 }
 
+// Page-locked host memory for output images: b200rt_render_frame copies device -> caller buffer
+// directly (one DMA, no staging copy) when the buffer is page-locked.
+extern "C" int b200rt_host_alloc(uint64_t bytes, void ** out) {
+	if (!out) return -1;
+	*out = nullptr;
+	cudaError_t e = cudaHostAlloc(out, size_t(bytes ? bytes : 16), cudaHostAllocDefault);
+	if (e != cudaSuccess) { g_create_error = std::string("cudaHostAlloc: ") + cudaGetErrorString(e); *out = nullptr; return -1; }
+	return 0;
+}
+extern "C" void b200rt_host_free(void * p) { if (p) cudaFreeHost(p); }
+
+static bool is_page_locked(const void * p) {
+	cudaPointerAttributes attr;
+	if (cudaPointerGetAttributes(&attr, p) != cudaSuccess) { cudaGetLastError(); return false; }
+	return attr.type == cudaMemoryTypeHost;
+}
+
 // ------------------------------------------------------------------------ static upload ---
 static int upload(b200rt_ctx * ctx, DeviceBuffer & buffer, const void * host, size_t bytes) {
 	CHECK_CUDA(ctx, buffer.ensure(bytes));
@@ -426,9 +443,13 @@ extern "C" int b200rt_render_frame(b200rt_ctx * ctx, const b200rt_frame * frame,
 	}
 
 	// device -> pinned host, then one synchronisation
+	// page-locked caller buffers (b200rt_host_alloc, cudaHostRegister, ...) are written by the DMA
+	// engine directly; pageable ones go through the context's pinned staging block + one memcpy
 	char * pinned = static_cast<char *>(ctx->pinned_out);
-	if (out->frame_buffer)   CHECK_CUDA(ctx, cudaMemcpyAsync(pinned + off_fb,  fb, pixels * 4, cudaMemcpyDeviceToHost, ctx->stream));
-	if (out->presented_rgb8) CHECK_CUDA(ctx, cudaMemcpyAsync(pinned + off_rgb, ctx->presented.ptr, pixels * 3, cudaMemcpyDeviceToHost, ctx->stream));
+	const bool direct_fb  = out->frame_buffer   && is_page_locked(out->frame_buffer);
+	const bool direct_rgb = out->presented_rgb8 && is_page_locked(out->presented_rgb8);
+	if (out->frame_buffer)   CHECK_CUDA(ctx, cudaMemcpyAsync(direct_fb  ? static_cast<void *>(out->frame_buffer)   : pinned + off_fb,  fb, pixels * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (out->presented_rgb8) CHECK_CUDA(ctx, cudaMemcpyAsync(direct_rgb ? static_cast<void *>(out->presented_rgb8) : pinned + off_rgb, ctx->presented.ptr, pixels * 3, cudaMemcpyDeviceToHost, ctx->stream));
 	CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->pinned_counters, ctx->counters.ptr, sizeof(FrameCounters), cudaMemcpyDeviceToHost, ctx->stream));
 	if (out->colour_float) CHECK_CUDA(ctx, cudaMemcpyAsync(out->colour_float, ctx->colour_float.ptr, pixels * 12, cudaMemcpyDeviceToHost, ctx->stream));
 	if (out->primary_ids)  CHECK_CUDA(ctx, cudaMemcpyAsync(out->primary_ids, ctx->ids.ptr, pixels * 8, cudaMemcpyDeviceToHost, ctx->stream));
@@ -440,8 +461,8 @@ extern "C" int b200rt_render_frame(b200rt_ctx * ctx, const b200rt_frame * frame,
 	cudaError_t sync = cudaStreamSynchronize(ctx->stream);
 	if (sync != cudaSuccess) { cudaEventDestroy(total_end); ctx->error = std::string("render failed: ") + cudaGetErrorString(sync); return -1; }
 
-	if (out->frame_buffer)   memcpy(out->frame_buffer,   pinned + off_fb,  pixels * 4);
-	if (out->presented_rgb8) memcpy(out->presented_rgb8, pinned + off_rgb, pixels * 3);
+	if (out->frame_buffer   && !direct_fb)  memcpy(out->frame_buffer,   pinned + off_fb,  pixels * 4);
+	if (out->presented_rgb8 && !direct_rgb) memcpy(out->presented_rgb8, pinned + off_rgb, pixels * 3);
 	if (out->stats) {
 		fill_stats(ctx, out->stats);
 		cudaEventElapsedTime(&out->stats->device_ms_total, end, total_end);

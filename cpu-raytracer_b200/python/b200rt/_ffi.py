@@ -121,6 +121,9 @@ def device_lib():
         lib.b200rt_render_frame_device.argtypes = [C.c_void_p, C.POINTER(Frame), C.c_uint64, C.POINTER(Stats)]
         lib.b200rt_present_device.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_float)]
         lib.b200rt_time_resident.argtypes = [C.c_void_p, C.c_int, C.c_uint64, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+        lib.b200rt_host_alloc.argtypes = [C.c_uint64, C.POINTER(C.c_void_p)]
+        lib.b200rt_host_free.argtypes = [C.c_void_p]
+        lib.b200rt_host_free.restype = None
         lib.b200rt_set_stream.argtypes = [C.c_void_p, C.c_uint64]
         lib.b200rt_stream.argtypes = [C.c_void_p]
         lib.b200rt_stream.restype = C.c_uint64

@@ -28,11 +28,15 @@ class Renderer:
             raise DeviceError(self._lib.b200rt_last_error(None).decode())
         self.width, self.height = width, height
         self._keep = None
+        self._pinned = []
 
     def close(self):
         if self._h:
             self._lib.b200rt_destroy(self._h)
             self._h = C.c_void_p()
+            for p in self._pinned:     # arrays handed out by alloc_outputs() die with the renderer
+                self._lib.b200rt_host_free(p)
+            self._pinned = []
 
     def __del__(self):
         try:
@@ -47,6 +51,20 @@ class Renderer:
     def upload_static(self, pack):
         view = pack.static_view()
         self._check(self._lib.b200rt_upload_static(self._h, C.byref(view)))
+
+    def alloc_outputs(self):
+        """Page-locked output images (b200rt_host_alloc): render(..., out=...) then DMAs straight into them."""
+        h, w = self.height, self.width
+        res = {}
+        for name, shape, dtype in (("frame_buffer", (h, w), np.uint32), ("presented", (h, w, 3), np.uint8)):
+            nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+            p = C.c_void_p()
+            if self._lib.b200rt_host_alloc(nbytes, C.byref(p)) != 0:
+                raise DeviceError(self._lib.b200rt_last_error(None).decode())
+            self._pinned.append(p)
+            buf = (C.c_uint8 * nbytes).from_address(p.value)
+            res[name] = np.frombuffer(buf, dtype=dtype).reshape(shape)
+        return res
 
     def render(self, pack, want_ids=False, want_float=False, want_presented=True, want_frame_buffer=True, out=None):
         """One frame through b200rt_render_frame (host buffers in, host buffers out)."""

@@ -179,6 +179,12 @@ int b200rt_upload_static(b200rt_ctx * ctx, const b200rt_static_scene * scene);
  * per-frame data, renders, applies FXAA, downloads the requested outputs.                  */
 int b200rt_render_frame(b200rt_ctx * ctx, const b200rt_frame * frame, const b200rt_outputs * outputs);
 
+/* Page-locked host memory for the output images. Optional: any host pointer works in
+ * b200rt_outputs, but a page-locked one (from here, or cudaHostRegister'ed by the caller) is
+ * filled by the DMA engine directly, without the staging copy a pageable buffer needs.       */
+int  b200rt_host_alloc(uint64_t bytes, void ** out);
+void b200rt_host_free(void * p);
+
 /* Same, but leaves the results in device memory (for callers that keep the image on the
  * GPU, e.g. the multi-GPU gather over NCCL): frame_buffer_dev is uint32 [height][width]
  * (only this context's tiles are written), presented_dev is uint8 [height][width][3] or 0. */

