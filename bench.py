@@ -274,8 +274,18 @@ def run_gpu_arm(args):
         host_fb = torch.empty(HEIGHT, WIDTH, dtype=torch.int32).pin_memory()
         host_rgb = torch.empty(HEIGHT, WIDTH, 3, dtype=torch.uint8).pin_memory()
 
-        from b200rt.multigpu import FrameGather
+        from b200rt.multigpu import FrameGather, PeerFrame
         gather = FrameGather()
+        peer = None
+        if os.environ.get("B200RT_GATHER", "p2p") == "p2p":
+            try:
+                peer = PeerFrame(HEIGHT, WIDTH)
+                if rank == 0:
+                    fb = peer.local                        # rank 0 presents straight out of the shared image
+            except Exception as e:                         # no symmetric memory on this box: NCCL reduction instead
+                if rank == 0:
+                    print("PeerFrame unavailable (%s): gathering with an NCCL reduce" % (str(e).splitlines() or ["?"])[0], file=sys.stderr)
+                peer = None
 
         def step(e2e):
             if e2e:
@@ -283,16 +293,32 @@ def run_gpu_arm(args):
                 frame_pack = pack.with_frame(scene.frame_view())
             else:
                 frame_pack = pack
-            renderer.render_device(frame_pack, fb.data_ptr())
-            gather(fb)                                     # tiles are disjoint and the rest is zero: SUM == gather (b200rt/multigpu.py)
+            if peer is not None:
+                peer.barrier()                             # rank 0 has finished reading the previous frame
+                renderer.render_device(frame_pack, peer.root_ptr, wait=False)   # pixels are stored into rank 0's image over NVLink
+                peer.barrier()                             # all tiles have landed
+            else:
+                fb.zero_()                                 # every rank: only its own tiles may be non-zero going into the SUM
+                renderer.render_device(frame_pack, fb.data_ptr(), wait=False)
+                gather(fb)                                 # tiles are disjoint and the rest is zero: SUM == gather (b200rt/multigpu.py)
             if rank == 0:
-                renderer.present_device(fb.data_ptr(), presented.data_ptr())
+                renderer.present_device(fb.data_ptr(), presented.data_ptr(), wait=False)
                 if e2e:
                     host_fb.copy_(fb, non_blocking=True)
                     host_rgb.copy_(presented, non_blocking=True)
                     torch.cuda.synchronize()
-            if rank != 0:
-                fb.zero_()
+
+        # the gathered frame must be the single-GPU frame, bit for bit (checked once, untimed)
+        step(False)
+        gather_verified = None
+        if rank == 0:
+            whole = Renderer(WIDTH, HEIGHT, BOUNCES, FILTER, device=local_rank)
+            whole.upload_static(pack)
+            expect = whole.render(pack)
+            whole.close()
+            torch.cuda.synchronize()
+            gather_verified = bool(np.array_equal(fb.cpu().numpy().view(np.uint32), expect["frame_buffer"])
+                                   and np.array_equal(presented.cpu().numpy(), expect["presented"]))
 
         for _ in range(args.warmup):
             step(False)
@@ -348,6 +374,8 @@ def run_gpu_arm(args):
             "warm_l2": None if warm_render is None else {"ms_render_kernel": warm_render, "ms_fxaa_kernel": warm_fxaa, "value": rays / (warm_render + warm_fxaa) / 1e3},
             "e2e": {"value": rays / e2e_ms / 1e3, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "frames_per_s": 1e3 / e2e_ms},
             "gpu_launches": launches,
+            "gather_verified": gather_verified if world > 1 else None,
+            "gather": None if world == 1 else ("render kernel stores into rank 0's image over NVLink peer memory + device barrier" if peer is not None else "NCCL reduce(SUM) of disjoint tiles"),
             "clocks": clocks.summary(),
             "roofline": roofline,
             "cpu_baseline": baseline,

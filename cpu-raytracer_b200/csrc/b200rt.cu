@@ -48,7 +48,9 @@ struct b200rt_ctx {
 
 	// per-frame data: one pinned staging block + one device block, sub-allocated
 	DeviceBuffer frame_block;
-	void * frame_staging = nullptr; size_t frame_staging_bytes = 0;
+	void * frame_staging = nullptr; size_t frame_staging_bytes = 0; // two halves, used alternately
+	cudaEvent_t staged[2] = { nullptr, nullptr };                  // the host->device copy out of each half
+	int staging_half = 0;
 
 	// outputs
 	DeviceBuffer frame_buffer, presented, colour_float, ids, hits, counters, l2_scratch;
@@ -98,6 +100,7 @@ extern "C" int b200rt_create(const b200rt_config * config, b200rt_ctx ** out) {
 	if ((e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
 	ctx->stream = ctx->own_stream;
 	for (auto & ev : ctx->ev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) return bail("cudaEventCreate", e);
+	for (auto & ev : ctx->staged) if ((e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
 
 	cudaDeviceProp prop;
 	if ((e = cudaGetDeviceProperties(&prop, config->device)) != cudaSuccess) return bail("cudaGetDeviceProperties", e);
@@ -139,6 +142,7 @@ extern "C" void b200rt_destroy(b200rt_ctx * ctx) {
 	if (ctx->pinned_out) cudaFreeHost(ctx->pinned_out);
 	if (ctx->pinned_counters) cudaFreeHost(ctx->pinned_counters);
 	for (auto & ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+	for (auto & ev : ctx->staged) if (ev) cudaEventDestroy(ev);
 	if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
 	delete ctx;
 }
@@ -295,14 +299,21 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 	const size_t total         = off_lights    + size_t(f->light_count) * sizeof(DeviceLight);
 
 	if (total > ctx->frame_staging_bytes) {
+		CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 		if (ctx->frame_staging) cudaFreeHost(ctx->frame_staging);
 		ctx->frame_staging = nullptr; ctx->frame_staging_bytes = 0;
-		CHECK_CUDA(ctx, cudaMallocHost(&ctx->frame_staging, total * 2));
+		CHECK_CUDA(ctx, cudaMallocHost(&ctx->frame_staging, total * 4));
 		ctx->frame_staging_bytes = total * 2;
 	}
 	CHECK_CUDA(ctx, ctx->frame_block.ensure(total));
 
-	char * base = static_cast<char *>(ctx->frame_staging);
+	// Frames may be issued without waiting for the previous one (b200rt_render_frame_device with
+	// stats == NULL): the two staging halves alternate, and a half is rewritten only after the
+	// copy that last read it has completed.
+	const int half = ctx->staging_half;
+	ctx->staging_half ^= 1;
+	CHECK_CUDA(ctx, cudaEventSynchronize(ctx->staged[half]));
+	char * base = static_cast<char *>(ctx->frame_staging) + size_t(half) * ctx->frame_staging_bytes;
 	memcpy(base + off_nodes,   f->tlas_nodes,   size_t(f->tlas_node_count) * sizeof(b200rt_bvh_node));
 	memcpy(base + off_indices, f->tlas_indices, size_t(f->instance_count) * sizeof(int));
 
@@ -341,6 +352,7 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 	}
 
 	CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->frame_block.ptr, base, total, cudaMemcpyHostToDevice, ctx->stream));
+	CHECK_CUDA(ctx, cudaEventRecord(ctx->staged[half], ctx->stream));
 
 	const char * dev = static_cast<const char *>(ctx->frame_block.ptr);
 	SceneParams & P = ctx->params;
@@ -481,9 +493,10 @@ extern "C" int b200rt_render_frame_device(b200rt_ctx * ctx, const b200rt_frame *
 	if (launch_render(ctx, reinterpret_cast<unsigned *>(uintptr_t(frame_buffer_dev)), nullptr, false)) return -1;
 	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
 	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));
+	if (!stats) return 0; // asynchronous: the caller orders later work on the context's stream
 	CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->pinned_counters, ctx->counters.ptr, sizeof(FrameCounters), cudaMemcpyDeviceToHost, ctx->stream));
 	CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-	if (stats) { fill_stats(ctx, stats); cudaEventElapsedTime(&stats->device_ms_total, ctx->ev[0], ctx->ev[3]); }
+	fill_stats(ctx, stats); cudaEventElapsedTime(&stats->device_ms_total, ctx->ev[0], ctx->ev[3]);
 	return 0;
 }
 
@@ -494,8 +507,9 @@ extern "C" int b200rt_present_device(b200rt_ctx * ctx, uint64_t frame_buffer_dev
 	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
 	if (launch_fxaa(ctx, reinterpret_cast<const unsigned *>(uintptr_t(frame_buffer_dev)), reinterpret_cast<unsigned char *>(uintptr_t(presented_dev)))) return -1;
 	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));
+	if (!device_ms) return 0; // asynchronous
 	CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-	if (device_ms) cudaEventElapsedTime(device_ms, ctx->ev[2], ctx->ev[3]);
+	cudaEventElapsedTime(device_ms, ctx->ev[2], ctx->ev[3]);
 	return 0;
 }
 

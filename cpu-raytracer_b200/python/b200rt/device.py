@@ -92,14 +92,21 @@ class Renderer:
         res["stats"] = stats.as_dict()
         return res
 
-    def render_device(self, pack, frame_buffer_ptr):
-        """Render this context's tiles into a device buffer (uint32 [H][W]) owned by the caller."""
-        stats = _ffi.Stats()
+    def render_device(self, pack, frame_buffer_ptr, wait=True):
+        """Render this context's tiles into a device buffer (uint32 [H][W]) owned by the caller.
+        wait=False only enqueues on the context's stream (no statistics)."""
         frame = pack.frame_view()
+        if not wait:
+            self._check(self._lib.b200rt_render_frame_device(self._h, C.byref(frame), C.c_uint64(frame_buffer_ptr), None))
+            return None
+        stats = _ffi.Stats()
         self._check(self._lib.b200rt_render_frame_device(self._h, C.byref(frame), C.c_uint64(frame_buffer_ptr), C.byref(stats)))
         return stats.as_dict()
 
-    def present_device(self, frame_buffer_ptr, presented_ptr):
+    def present_device(self, frame_buffer_ptr, presented_ptr, wait=True):
+        if not wait:
+            self._check(self._lib.b200rt_present_device(self._h, C.c_uint64(frame_buffer_ptr), C.c_uint64(presented_ptr), None))
+            return None
         ms = C.c_float()
         self._check(self._lib.b200rt_present_device(self._h, C.c_uint64(frame_buffer_ptr), C.c_uint64(presented_ptr), C.byref(ms)))
         return ms.value

@@ -190,6 +190,8 @@ void b200rt_host_free(void * p);
  * (only this context's tiles are written), presented_dev is uint8 [height][width][3] or 0. */
 int b200rt_render_frame_device(b200rt_ctx * ctx, const b200rt_frame * frame,
                                uint64_t frame_buffer_dev, b200rt_stats * stats);
+/* stats == NULL (and device_ms == NULL below): the call only ENQUEUES on the context's stream and
+ * returns; the caller synchronises (or orders a collective) on b200rt_stream().              */
 
 /* FXAA + gamma over a full pre-FXAA frame that is already in device memory (after the
  * multi-GPU gather): in uint32 [height][width], out uint8 [height][width][3].              */
