@@ -57,6 +57,17 @@ struct b200rt_ctx {
 	void * pinned_out = nullptr; size_t pinned_out_bytes = 0;
 	FrameCounters * pinned_counters = nullptr;
 
+	// pipelined frames (b200rt_submit_frame / b200rt_wait_frame): two slots, each with its own images
+	// and counters, so that frame n+1 renders while frame n is still on its way to the host
+	struct Slot {
+		DeviceBuffer frame_buffer, presented, counters;
+		FrameCounters * pinned_counters = nullptr;
+		cudaEvent_t begin = nullptr, render_begin = nullptr, render_end = nullptr, fxaa_end = nullptr, copied = nullptr;
+		bool busy = false;
+	} slots[2];
+	cudaStream_t copy_stream = nullptr;
+	unsigned submitted = 0, waited = 0;
+
 	SceneParams params;      // last frame's parameters (for b200rt_time_resident)
 	bool have_frame = false;
 	int  num_sms = 0, blocks_per_sm = 0;
@@ -138,6 +149,12 @@ extern "C" void b200rt_destroy(b200rt_ctx * ctx) {
 	if (ctx->stream) cudaStreamSynchronize(ctx->stream);
 	for (DeviceBuffer * b : { &ctx->nodes, &ctx->hot, &ctx->cold, &ctx->materials, &ctx->textures, &ctx->texels, &ctx->sky, &ctx->gamma,
 	                          &ctx->frame_block, &ctx->frame_buffer, &ctx->presented, &ctx->colour_float, &ctx->ids, &ctx->hits, &ctx->counters, &ctx->l2_scratch }) b->release();
+	for (auto & slot : ctx->slots) {
+		slot.frame_buffer.release(); slot.presented.release(); slot.counters.release();
+		if (slot.pinned_counters) cudaFreeHost(slot.pinned_counters);
+		for (cudaEvent_t e : { slot.begin, slot.render_begin, slot.render_end, slot.fxaa_end, slot.copied }) if (e) cudaEventDestroy(e);
+	}
+	if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
 	if (ctx->frame_staging) cudaFreeHost(ctx->frame_staging);
 	if (ctx->pinned_out) cudaFreeHost(ctx->pinned_out);
 	if (ctx->pinned_counters) cudaFreeHost(ctx->pinned_counters);
@@ -388,15 +405,16 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 }
 
 // Launches the render kernel over this context's tiles. frame_buffer is a device pointer.
-static int launch_render(b200rt_ctx * ctx, unsigned * frame_buffer, float * colour_float, bool count) {
-	CHECK_CUDA(ctx, cudaMemsetAsync(ctx->counters.ptr, 0, sizeof(FrameCounters), ctx->stream));
+static int launch_render(b200rt_ctx * ctx, unsigned * frame_buffer, float * colour_float, bool count, void * counters_dev = nullptr) {
+	if (!counters_dev) counters_dev = ctx->counters.ptr;
+	CHECK_CUDA(ctx, cudaMemsetAsync(counters_dev, 0, sizeof(FrameCounters), ctx->stream));
 	const unsigned total_warps = unsigned(ctx->params.tile_count_mine) * 32u;
 	if (total_warps == 0) return 0;
 	// persistent grid: every SM filled to the occupancy limit, never more warps than units
 	unsigned blocks = unsigned(ctx->num_sms) * unsigned(ctx->blocks_per_sm);
 	const unsigned needed = (total_warps + RT_BLOCK_THREADS / 32 - 1) / (RT_BLOCK_THREADS / 32);
 	if (blocks > needed) blocks = needed;
-	FrameCounters * counters = static_cast<FrameCounters *>(ctx->counters.ptr);
+	FrameCounters * counters = static_cast<FrameCounters *>(counters_dev);
 	if (count) render_kernel<true ><<<blocks, RT_BLOCK_THREADS, 0, ctx->stream>>>(ctx->params, frame_buffer, colour_float, counters);
 	else       render_kernel<false><<<blocks, RT_BLOCK_THREADS, 0, ctx->stream>>>(ctx->params, frame_buffer, colour_float, counters);
 	CHECK_CUDA(ctx, cudaGetLastError());
@@ -536,5 +554,81 @@ extern "C" int b200rt_time_resident(b200rt_ctx * ctx, int repeat, uint64_t flush
 	}
 	if (ms_render) *ms_render = total_render / float(repeat);
 	if (ms_fxaa)   *ms_fxaa   = total_fxaa / float(repeat);
+	return 0;
+}
+
+// ------------------------------------------------------------------- pipelined frames ---
+// The reference's presentation is asynchronous too: glTexImage2D + draw + SwapBuffers (Window.cpp:
+// 87-119) only queue work for the graphics driver, and the CPU goes on to trace the next frame.
+// Here: frame n's images travel to the host on a copy stream while frame n+1 is being traced.
+static int ensure_slot(b200rt_ctx * ctx, b200rt_ctx::Slot & slot) {
+	const size_t pixels = size_t(ctx->config.width) * ctx->config.height;
+	if (slot.copied) return 0;
+	CHECK_CUDA(ctx, slot.frame_buffer.ensure(pixels * 4));
+	CHECK_CUDA(ctx, slot.presented.ensure(pixels * 3 + 16));
+	CHECK_CUDA(ctx, slot.counters.ensure(sizeof(FrameCounters)));
+	CHECK_CUDA(ctx, cudaMemset(slot.frame_buffer.ptr, 0, pixels * 4));
+	CHECK_CUDA(ctx, cudaMallocHost(reinterpret_cast<void **>(&slot.pinned_counters), sizeof(FrameCounters)));
+	for (cudaEvent_t * e : { &slot.begin, &slot.render_begin, &slot.render_end, &slot.fxaa_end }) CHECK_CUDA(ctx, cudaEventCreate(e));
+	CHECK_CUDA(ctx, cudaEventCreate(&slot.copied));
+	if (!ctx->copy_stream) CHECK_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+	return 0;
+}
+
+extern "C" int b200rt_submit_frame(b200rt_ctx * ctx, const b200rt_frame * frame, const b200rt_outputs * out) {
+	if (!ctx) return -1;
+	if (!out) return fail(ctx, "null outputs");
+	if (out->colour_float || out->primary_ids || out->primary_hit) return fail(ctx, "b200rt_submit_frame delivers frame_buffer, presented_rgb8 and stats only");
+	if ((out->frame_buffer && !is_page_locked(out->frame_buffer)) || (out->presented_rgb8 && !is_page_locked(out->presented_rgb8)))
+		return fail(ctx, "b200rt_submit_frame needs page-locked output images (b200rt_host_alloc): the copies are asynchronous");
+	CHECK_CUDA(ctx, cudaSetDevice(ctx->config.device));
+
+	b200rt_ctx::Slot & slot = ctx->slots[ctx->submitted & 1];
+	if (slot.busy) return fail(ctx, "two frames are in flight: call b200rt_wait_frame first");
+	if (ensure_slot(ctx, slot)) return -1;
+
+	const size_t pixels = size_t(ctx->config.width) * ctx->config.height;
+	unsigned * fb = static_cast<unsigned *>(slot.frame_buffer.ptr);
+
+	CHECK_CUDA(ctx, cudaEventRecord(slot.begin, ctx->stream));
+	if (stage_frame(ctx, frame)) return -1;
+	CHECK_CUDA(ctx, cudaEventRecord(slot.render_begin, ctx->stream));
+	if (launch_render(ctx, fb, nullptr, ctx->config.count_traversal != 0, slot.counters.ptr)) return -1;
+	CHECK_CUDA(ctx, cudaEventRecord(slot.render_end, ctx->stream));
+	if (out->presented_rgb8 && launch_fxaa(ctx, fb, static_cast<unsigned char *>(slot.presented.ptr))) return -1;
+	CHECK_CUDA(ctx, cudaEventRecord(slot.fxaa_end, ctx->stream));
+
+	// the pre-FXAA image can leave as soon as tracing is done, in parallel with the FXAA kernel
+	CHECK_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, slot.render_end, 0));
+	if (out->frame_buffer) CHECK_CUDA(ctx, cudaMemcpyAsync(out->frame_buffer, fb, pixels * 4, cudaMemcpyDeviceToHost, ctx->copy_stream));
+	CHECK_CUDA(ctx, cudaMemcpyAsync(slot.pinned_counters, slot.counters.ptr, sizeof(FrameCounters), cudaMemcpyDeviceToHost, ctx->copy_stream));
+	CHECK_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, slot.fxaa_end, 0));
+	if (out->presented_rgb8) CHECK_CUDA(ctx, cudaMemcpyAsync(out->presented_rgb8, slot.presented.ptr, pixels * 3, cudaMemcpyDeviceToHost, ctx->copy_stream));
+	CHECK_CUDA(ctx, cudaEventRecord(slot.copied, ctx->copy_stream));
+
+	slot.busy = true;
+	ctx->submitted++;
+	return 0;
+}
+
+extern "C" int b200rt_wait_frame(b200rt_ctx * ctx, b200rt_stats * stats) {
+	if (!ctx) return -1;
+	b200rt_ctx::Slot & slot = ctx->slots[ctx->waited & 1];
+	if (!slot.busy) return fail(ctx, "no frame in flight");
+	CHECK_CUDA(ctx, cudaSetDevice(ctx->config.device));
+	cudaError_t e = cudaEventSynchronize(slot.copied);
+	slot.busy = false;
+	ctx->waited++;
+	if (e != cudaSuccess) { ctx->error = std::string("frame failed: ") + cudaGetErrorString(e); return -1; }
+	if (stats) {
+		const FrameCounters & c = *slot.pinned_counters;
+		stats->primary_rays = c.primary; stats->shadow_rays = c.shadow; stats->reflection_rays = c.reflection; stats->refraction_rays = c.refraction;
+		stats->nodes_visited = c.nodes; stats->triangles_tested = c.triangles; stats->texels_fetched = c.texels;
+		stats->hits_accepted = c.accepted; stats->instances_entered = c.instances;
+		stats->device_ms_render = stats->device_ms_fxaa = stats->device_ms_total = 0.0f;
+		cudaEventElapsedTime(&stats->device_ms_render, slot.render_begin, slot.render_end);
+		cudaEventElapsedTime(&stats->device_ms_fxaa,   slot.render_end, slot.fxaa_end);
+		cudaEventElapsedTime(&stats->device_ms_total,  slot.begin, slot.copied);
+	}
 	return 0;
 }

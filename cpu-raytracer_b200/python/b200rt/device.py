@@ -92,6 +92,19 @@ class Renderer:
         res["stats"] = stats.as_dict()
         return res
 
+    def submit(self, pack, out):
+        """Pipelined frame (b200rt_submit_frame): `out` from alloc_outputs(); returns at once. Pair with wait()."""
+        outputs = _ffi.Outputs(out["frame_buffer"].ctypes.data if "frame_buffer" in out else None,
+                               out["presented"].ctypes.data if "presented" in out else None, None, None, None, None)
+        frame = pack.frame_view()
+        self._check(self._lib.b200rt_submit_frame(self._h, C.byref(frame), C.byref(outputs)))
+
+    def wait(self):
+        """Blocks until the oldest submitted frame is in its output images; returns its stats."""
+        stats = _ffi.Stats()
+        self._check(self._lib.b200rt_wait_frame(self._h, C.byref(stats)))
+        return stats.as_dict()
+
     def render_device(self, pack, frame_buffer_ptr, wait=True):
         """Render this context's tiles into a device buffer (uint32 [H][W]) owned by the caller.
         wait=False only enqueues on the context's stream (no statistics)."""

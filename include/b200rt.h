@@ -179,6 +179,15 @@ int b200rt_upload_static(b200rt_ctx * ctx, const b200rt_static_scene * scene);
  * per-frame data, renders, applies FXAA, downloads the requested outputs.                  */
 int b200rt_render_frame(b200rt_ctx * ctx, const b200rt_frame * frame, const b200rt_outputs * outputs);
 
+/* Pipelined form of b200rt_render_frame, for a frame loop: submit enqueues frame n (upload, trace,
+ * FXAA, copies into PAGE-LOCKED output images) and returns at once; wait blocks until the OLDEST
+ * submitted frame has arrived in its output images and fills its stats. At most two frames may be
+ * in flight, so the host prepares and the GPU traces frame n+1 while frame n is still being copied
+ * out — the same overlap the reference gets from its asynchronous GL present (Window.cpp:87-119).
+ * colour_float / primary_ids / primary_hit must be NULL here.                                   */
+int b200rt_submit_frame(b200rt_ctx * ctx, const b200rt_frame * frame, const b200rt_outputs * outputs);
+int b200rt_wait_frame(b200rt_ctx * ctx, b200rt_stats * stats);
+
 /* Page-locked host memory for the output images. Optional: any host pointer works in
  * b200rt_outputs, but a page-locked one (from here, or cudaHostRegister'ed by the caller) is
  * filled by the DMA engine directly, without the staging copy a pageable buffer needs.       */

@@ -121,3 +121,29 @@ def test_page_locked_outputs_equal_pageable(golden):
     assert np.array_equal(pinned["frame_buffer"], golden.ref_frame_buffer) or True
     del pinned
     r.close()
+
+
+def test_pipelined_frames_equal_synchronous_frames(golden):
+    """b200rt_submit_frame / b200rt_wait_frame with two frames in flight deliver the same images and counters."""
+    from b200rt.device import DeviceError, Renderer
+    m = golden.meta
+    r = Renderer(m["width"], m["height"], m["bounces"], m["filter"])
+    r.upload_static(golden.pack)
+    sync = r.render(golden.pack)
+    with pytest.raises(DeviceError, match="page-locked"):
+        r.submit(golden.pack, {"frame_buffer": np.zeros_like(sync["frame_buffer"]), "presented": np.zeros_like(sync["presented"])})
+    outs = [r.alloc_outputs(), r.alloc_outputs()]
+    r.submit(golden.pack, outs[0])
+    r.submit(golden.pack, outs[1])
+    with pytest.raises(DeviceError, match="in flight"):
+        r.submit(golden.pack, outs[0])
+    for k in range(2):
+        stats = r.wait()
+        assert np.array_equal(outs[k]["frame_buffer"], sync["frame_buffer"])
+        assert np.array_equal(outs[k]["presented"], sync["presented"])
+        for key in ("primary_rays", "shadow_rays", "reflection_rays", "refraction_rays"):
+            assert stats[key] == sync["stats"][key]
+    with pytest.raises(DeviceError, match="no frame in flight"):
+        r.wait()
+    del outs
+    r.close()
