@@ -134,12 +134,11 @@ __device__ __forceinline__ void blas_trace(const float4 * __restrict__ nodes, co
 					best.t = t; best.u = u; best.v = v; best.instance = instance; best.primitive = i;
 				}
 			}
-		} else if (visit_left_first(count, d)) {
-			stack[stack_size++] = left_or_first + 1;
-			stack[stack_size++] = left_or_first;
-		} else {
-			stack[stack_size++] = left_or_first;
-			stack[stack_size++] = left_or_first + 1;
+		} else { // push far, then near (BottomLevelBVH.cpp:380-387), without a divergent branch
+			const int left_first = visit_left_first(count, d) ? 1 : 0;
+			stack[stack_size]     = left_or_first + left_first;
+			stack[stack_size + 1] = left_or_first + 1 - left_first;
+			stack_size += 2;
 		}
 	}
 }
@@ -167,12 +166,11 @@ __device__ __forceinline__ bool blas_intersect(const float4 * __restrict__ nodes
 				if (COUNT) cnt.triangles++;
 				if (triangle_test(hot + 3 * size_t(i), o, d, max_distance, t, u, v)) return true;
 			}
-		} else if (visit_left_first(count, d)) {
-			stack[stack_size++] = left_or_first + 1;
-			stack[stack_size++] = left_or_first;
-		} else {
-			stack[stack_size++] = left_or_first;
-			stack[stack_size++] = left_or_first + 1;
+		} else { // push far, then near (BottomLevelBVH.cpp:380-387), without a divergent branch
+			const int left_first = visit_left_first(count, d) ? 1 : 0;
+			stack[stack_size]     = left_or_first + left_first;
+			stack[stack_size + 1] = left_or_first + 1 - left_first;
+			stack_size += 2;
 		}
 	}
 	return false;
