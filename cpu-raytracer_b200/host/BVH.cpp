@@ -204,6 +204,22 @@ void BottomLevelBVH::build(std::vector<TriangleHot> hot, std::vector<TriangleCol
 	flatten();
 }
 
+void BottomLevelBVH::build_sbvh(std::vector<TriangleHot> hot, std::vector<TriangleCold> cold, const std::vector<Vector3> & vertices, int threads) {
+	if (vertices.size() != hot.size() * 3) throw std::runtime_error("build_sbvh needs three vertices per triangle");
+	file_hot  = std::move(hot);
+	file_cold = std::move(cold);
+
+	std::vector<BuildTriangle> triangles(file_hot.size());
+	for (size_t i = 0; i < triangles.size(); i++) {
+		for (int k = 0; k < 3; k++) triangles[i].vertex[k] = vertices[3 * i + k];
+		triangles[i].finish();
+	}
+	SBVHResult result = b200rt::build_sbvh(triangles, threads);
+	nodes        = std::move(result.nodes);
+	file_indices = std::move(result.indices);
+	flatten();
+}
+
 void BottomLevelBVH::flatten() {
 	triangles_hot .resize(file_indices.size());
 	triangles_cold.resize(file_indices.size());

@@ -50,6 +50,30 @@ private:
 	void build_recursive(BVHNode & node, const std::vector<BuildPrimitive> & primitives, std::vector<BVHNode> & nodes, int & node_index, int first_index, int index_count);
 };
 
+// A triangle as the SBVH builder sees it (Triangle.h:9-26): the three ORIGINAL vertices (not
+// p0 + edge, which rounds differently), their box (fattened twice, Triangle.h:16-21) and the
+// centroid the object splits sort by.
+struct BuildTriangle {
+	Vector3 vertex[3];
+	AABB    aabb;
+	Vector3 position;
+
+	void finish(); // box + centroid from the vertices
+};
+
+// Spatial-split BVH (Stich et al. 2009) the way the reference builds it (BVHBuilders.h:48-329,
+// BVHPartitions.h:116-378): full-sweep object split with child boxes clipped to the node box,
+// 256-bin spatial split considered when the object split's child overlap exceeds alpha = 1e-4 of
+// the root area, reference unsplitting, leaves below 3 references. Output is byte-identical to
+// the reference's (same decisions, same node numbering, same leaf order) and independent of
+// `threads`: subtrees are built as relocatable pieces by a task pool and stitched in depth-first
+// order.
+struct SBVHResult {
+	std::vector<BVHNode> nodes;    // root 0, node 1 unused, child pairs from 2
+	std::vector<int>     indices;  // triangle ids in leaf order; size >= triangle count (duplicated references)
+};
+SBVHResult build_sbvh(const std::vector<BuildTriangle> & triangles, int threads);
+
 // One mesh's acceleration structure + triangles, shared between instances.
 struct BottomLevelBVH {
 	std::vector<TriangleHot>  triangles_hot;   // flattened: leaf order (after flatten())
@@ -63,8 +87,12 @@ struct BottomLevelBVH {
 	void load_from_disk(const std::string & bvh_filename);
 	void save_to_disk  (const std::string & bvh_filename) const; // writes the un-flattened form back
 
-	// Builds a plain SAH BVH over (hot, cold) given in OBJ order (used when no cache exists).
+	// Builds a plain SAH BVH over (hot, cold) given in OBJ order (MESH_ACCELERATOR_BVH, Config.h:32).
 	void build(std::vector<TriangleHot> hot, std::vector<TriangleCold> cold);
+
+	// Builds the SBVH (MESH_ACCELERATOR_SBVH, the reference's default, Config.h:35) from the original
+	// vertices; `vertices` holds 3 per triangle, in (hot, cold) order.
+	void build_sbvh(std::vector<TriangleHot> hot, std::vector<TriangleCold> cold, const std::vector<Vector3> & vertices, int threads);
 
 private:
 	// Un-flattened form as stored on disk

@@ -1,5 +1,8 @@
 #include "Scene.h"
 
+#include <cstdlib>
+#include <thread>
+
 #include <algorithm>
 #include <cstdio>
 #include <fstream>
@@ -144,7 +147,7 @@ void Scene::load_mtl(BottomLevelBVH & bvh, const std::string & obj_path) {
 // Triangle soup from a Wavefront OBJ. Polygons are fan-triangulated. Needs `vn` (the
 // reference indexes normals unconditionally, OBJLoader.cpp:143-145); `vt` is optional and V is
 // flipped to 1 - v (OBJLoader.cpp:139-141).
-void Scene::load_obj(const std::string & obj_path, std::vector<TriangleHot> & hot, std::vector<TriangleCold> & cold, const std::vector<std::string> & material_names) {
+void Scene::load_obj(const std::string & obj_path, std::vector<TriangleHot> & hot, std::vector<TriangleCold> & cold, std::vector<Vector3> & vertices, const std::vector<std::string> & material_names) {
 	std::ifstream in(obj_path);
 	if (!in) throw std::runtime_error("Failed to load obj file " + obj_path);
 
@@ -205,6 +208,7 @@ void Scene::load_obj(const std::string & obj_path, std::vector<TriangleHot> & ho
 				}
 				t.material_id = material_id;
 				hot.push_back(h); cold.push_back(t);
+				vertices.push_back(p[0]); vertices.push_back(p[1]); vertices.push_back(p[2]);
 			}
 		}
 	}
@@ -225,9 +229,12 @@ int Scene::load_blas(const std::string & obj_path) {
 		load_mtl(*bvh, obj_path);
 	} else {
 		load_mtl(*bvh, obj_path);
-		std::vector<TriangleHot> hot; std::vector<TriangleCold> cold;
-		load_obj(obj_path, hot, cold, last_material_names);
-		bvh->build(std::move(hot), std::move(cold));
+		std::vector<TriangleHot> hot; std::vector<TriangleCold> cold; std::vector<Vector3> vertices;
+		load_obj(obj_path, hot, cold, vertices, last_material_names);
+		// MESH_ACCELERATOR (Config.h:32-35): the reference's default is the SBVH; B200RT_MESH_ACCELERATOR=bvh selects the plain SAH BVH
+		const char * accel = getenv("B200RT_MESH_ACCELERATOR");
+		if (accel && std::string(accel) == "bvh") bvh->build(std::move(hot), std::move(cold));
+		else bvh->build_sbvh(std::move(hot), std::move(cold), vertices, int(std::max(1u, std::thread::hardware_concurrency())));
 		try { bvh->save_to_disk(bvh_path); } catch (const std::exception &) { /* read-only asset dir: keep going uncached */ }
 	}
 

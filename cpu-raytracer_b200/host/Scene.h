@@ -99,7 +99,7 @@ struct Scene {
 private:
 	int reserve_material() { materials.emplace_back(); return int(materials.size()) - 1; } // MaterialBuffer::reserve
 	void load_mtl(BottomLevelBVH & bvh, const std::string & obj_path);
-	void load_obj(const std::string & obj_path, std::vector<TriangleHot> & hot, std::vector<TriangleCold> & cold, const std::vector<std::string> & material_names);
+	void load_obj(const std::string & obj_path, std::vector<TriangleHot> & hot, std::vector<TriangleCold> & cold, std::vector<Vector3> & vertices, const std::vector<std::string> & material_names);
 
 	// flat staging
 	std::vector<BVHNode> flat_nodes; std::vector<TriangleHot> flat_hot; std::vector<TriangleCold> flat_cold;

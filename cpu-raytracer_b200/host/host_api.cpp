@@ -3,6 +3,7 @@
 
 #include <exception>
 #include <string>
+#include <vector>
 
 #include "Scene.h"
 
@@ -73,6 +74,21 @@ int b200rt_scene_blas_original_indices(const b200rt_scene * s, int blas, int32_t
 	const std::vector<int> & map = s->scene.blas[blas]->original_index;
 	if (out) for (int i = 0; i < capacity && i < int(map.size()); i++) out[i] = map[i];
 	return int(map.size());
+}
+
+int b200rt_build_sbvh(const float * vertices, int triangle_count, int threads, b200rt_bvh_node * nodes, int node_capacity, int32_t * indices, int index_capacity, int * node_count, int * index_count) {
+	if (!vertices || triangle_count <= 0 || !node_count || !index_count) { g_error = "bad argument"; return -1; }
+	return guarded([&] {
+		std::vector<b200rt::BuildTriangle> triangles(triangle_count);
+		for (int i = 0; i < triangle_count; i++) {
+			for (int k = 0; k < 3; k++) triangles[i].vertex[k] = b200rt::Vector3(vertices[9 * i + 3 * k], vertices[9 * i + 3 * k + 1], vertices[9 * i + 3 * k + 2]);
+			triangles[i].finish();
+		}
+		b200rt::SBVHResult r = b200rt::build_sbvh(triangles, threads);
+		*node_count = int(r.nodes.size()); *index_count = int(r.indices.size());
+		if (nodes)   for (int i = 0; i < node_capacity  && i < *node_count;  i++) nodes[i]   = r.nodes[i];
+		if (indices) for (int i = 0; i < index_capacity && i < *index_count; i++) indices[i] = r.indices[i];
+	});
 }
 
 int b200rt_tile_count(int width, int height, int * tiles_x, int * tiles_y) {

@@ -45,6 +45,15 @@ int b200rt_scene_frame_view (b200rt_scene * scene, b200rt_frame * out);
  * (the inverse of BottomLevelBVH::flatten, BottomLevelBVH.cpp:196-212). Returns the count.   */
 int b200rt_scene_blas_original_indices(const b200rt_scene * scene, int blas, int32_t * out, int capacity);
 
+/* BottomLevelBVH::build_sbvh (BottomLevelBVH.cpp:108-147 -> BVHBuilders::build_sbvh, BVHBuilders.h:48-329):
+ * builds the reference's spatial-split BVH over `triangle_count` triangles given as float[n][3][3]
+ * vertex positions, on `threads` host threads (the result does not depend on the thread count).
+ * Outputs are in the `<obj>.bvh` form: nodes (root 0, node 1 unused) whose leaves index `indices`.
+ * Call with nodes == NULL / indices == NULL first to learn the counts.                          */
+int b200rt_build_sbvh(const float * vertices, int triangle_count, int threads,
+                      b200rt_bvh_node * nodes, int node_capacity, int32_t * indices, int index_capacity,
+                      int * node_count, int * index_count);
+
 /* Tile partition helper: number of 32x32 tiles and the tiles of one GPU.   */
 int b200rt_tile_count(int width, int height, int * tiles_x, int * tiles_y);
 
