@@ -5,6 +5,8 @@
 #include <cstring>
 #include <stdexcept>
 
+#include <zlib.h>
+
 namespace b200rt {
 
 static void set_aabb(BVHNode & node, const AABB & box) {
@@ -119,31 +121,34 @@ struct File {
 	File(const std::string & name, const char * mode) : f(fopen(name.c_str(), mode)) { }
 	~File() { if (f) fclose(f); }
 };
-template<typename T> void read_array(FILE * f, std::vector<T> & v, size_t n, const std::string & name) {
-	v.resize(n);
-	if (n && fread(v.data(), sizeof(T), n, f) != n) throw std::runtime_error("truncated BVH cache " + name);
-}
 }
 
-void BottomLevelBVH::load_from_disk(const std::string & name) {
-	File file(name, "rb");
-	if (!file.f) throw std::runtime_error("cannot open BVH cache " + name);
-
+// Parses the reference's headerless dump (BottomLevelBVH.cpp:149-192) from memory and validates
+// every index before anything is trusted.
+void BottomLevelBVH::parse_legacy(const unsigned char * data, size_t size, const std::string & name) {
+	size_t at = 0;
 	auto read_count = [&](const char * what) {
 		int32_t n = 0;
-		if (fread(&n, sizeof(n), 1, file.f) != 1 || n < 0) throw std::runtime_error(std::string("bad ") + what + " in BVH cache " + name);
+		if (at + 4 > size) throw std::runtime_error(std::string("truncated BVH cache ") + name);
+		memcpy(&n, data + at, 4); at += 4;
+		if (n < 0) throw std::runtime_error(std::string("bad ") + what + " in BVH cache " + name);
 		return size_t(n);
 	};
+	auto read_array = [&](auto & v, size_t n) {
+		using T = typename std::remove_reference<decltype(v)>::type::value_type;
+		if (n > (size - at) / sizeof(T)) throw std::runtime_error("truncated BVH cache " + name);
+		v.resize(n);
+		if (n) memcpy(v.data(), data + at, n * sizeof(T));
+		at += n * sizeof(T);
+	};
 
-	size_t triangle_count = read_count("triangle count");
-	read_array(file.f, file_hot,  triangle_count, name);
-	read_array(file.f, file_cold, triangle_count, name);
-
-	size_t n_nodes = read_count("node count");
-	read_array(file.f, nodes, n_nodes, name);
-
-	size_t index_count = read_count("index count");
-	read_array(file.f, file_indices, index_count, name);
+	const size_t triangle_count = read_count("triangle count");
+	read_array(file_hot,  triangle_count);
+	read_array(file_cold, triangle_count);
+	const size_t n_nodes = read_count("node count");
+	read_array(nodes, n_nodes);
+	const size_t index_count = read_count("index count");
+	read_array(file_indices, index_count);
 
 	for (int i : file_indices) if (i < 0 || size_t(i) >= triangle_count) throw std::runtime_error("index out of range in BVH cache " + name);
 	// Node 1 is never written by the reference's builders (root 0, child pairs from 2:
@@ -160,6 +165,21 @@ void BottomLevelBVH::load_from_disk(const std::string & name) {
 	flatten();
 }
 
+static std::vector<unsigned char> read_whole_file(const std::string & name) {
+	File file(name, "rb");
+	if (!file.f) throw std::runtime_error("cannot open BVH cache " + name);
+	std::vector<unsigned char> bytes;
+	unsigned char chunk[1 << 16];
+	size_t n;
+	while ((n = fread(chunk, 1, sizeof(chunk), file.f)) > 0) bytes.insert(bytes.end(), chunk, chunk + n);
+	return bytes;
+}
+
+void BottomLevelBVH::load_from_disk(const std::string & name) {
+	const std::vector<unsigned char> bytes = read_whole_file(name);
+	parse_legacy(bytes.data(), bytes.size(), name);
+}
+
 void BottomLevelBVH::save_to_disk(const std::string & name) const {
 	File file(name, "wb");
 	if (!file.f) throw std::runtime_error("cannot write BVH cache " + name);
@@ -173,6 +193,57 @@ void BottomLevelBVH::save_to_disk(const std::string & name) const {
 	fwrite(nodes.data(), sizeof(BVHNode), nodes.size(), file.f);
 	write_count(file_indices.size());
 	fwrite(file_indices.data(), sizeof(int), file_indices.size(), file.f);
+}
+
+// ------------------------------------------------------------------ versioned container ---
+namespace {
+const char     CONTAINER_MAGIC[8] = { 'B', '2', '0', '0', 'B', 'V', 'H', 0 };
+const uint32_t CONTAINER_ENDIAN   = 0x01020304u;
+const uint32_t CONTAINER_VERSION  = 1;
+struct ContainerHeader { char magic[8]; uint32_t endian_tag, version, triangle_count, node_count, index_count, crc; };
+static_assert(sizeof(ContainerHeader) == 32, "container header is 32 bytes");
+
+std::vector<unsigned char> legacy_payload(const std::vector<TriangleHot> & hot, const std::vector<TriangleCold> & cold, const std::vector<BVHNode> & nodes, const std::vector<int> & indices) {
+	std::vector<unsigned char> out;
+	auto put = [&](const void * p, size_t n) { const unsigned char * b = static_cast<const unsigned char *>(p); out.insert(out.end(), b, b + n); };
+	int32_t c = int32_t(hot.size());     put(&c, 4); put(hot.data(), hot.size() * sizeof(TriangleHot)); put(cold.data(), cold.size() * sizeof(TriangleCold));
+	c = int32_t(nodes.size());           put(&c, 4); put(nodes.data(), nodes.size() * sizeof(BVHNode));
+	c = int32_t(indices.size());         put(&c, 4); put(indices.data(), indices.size() * sizeof(int));
+	return out;
+}
+}
+
+void BottomLevelBVH::save_container(const std::string & name) const {
+	const std::vector<unsigned char> payload = legacy_payload(file_hot, file_cold, nodes, file_indices);
+	ContainerHeader h;
+	memcpy(h.magic, CONTAINER_MAGIC, 8);
+	h.endian_tag = CONTAINER_ENDIAN; h.version = CONTAINER_VERSION;
+	h.triangle_count = uint32_t(file_hot.size()); h.node_count = uint32_t(nodes.size()); h.index_count = uint32_t(file_indices.size());
+	h.crc = uint32_t(crc32(0L, payload.data(), uInt(payload.size())));
+
+	const std::string partial = name + ".part"; // written beside, renamed when complete: a reader never sees half a file
+	{
+		File file(partial, "wb");
+		if (!file.f) throw std::runtime_error("cannot write BVH container " + name);
+		if (fwrite(&h, sizeof(h), 1, file.f) != 1 || fwrite(payload.data(), 1, payload.size(), file.f) != payload.size()) throw std::runtime_error("short write to BVH container " + name);
+	}
+	if (rename(partial.c_str(), name.c_str()) != 0) throw std::runtime_error("cannot rename BVH container " + name);
+}
+
+void BottomLevelBVH::load_container(const std::string & name) {
+	const std::vector<unsigned char> bytes = read_whole_file(name);
+	ContainerHeader h;
+	if (bytes.size() < sizeof(h))                         throw std::runtime_error("truncated header in BVH container " + name);
+	memcpy(&h, bytes.data(), sizeof(h));
+	if (memcmp(h.magic, CONTAINER_MAGIC, 8) != 0)         throw std::runtime_error("not a BVH container (bad magic): " + name);
+	if (h.endian_tag != CONTAINER_ENDIAN)                 throw std::runtime_error("BVH container written on a machine of the other endianness: " + name);
+	if (h.version != CONTAINER_VERSION)                   throw std::runtime_error("unsupported BVH container version in " + name);
+
+	const size_t expect = 12 + size_t(h.triangle_count) * (sizeof(TriangleHot) + sizeof(TriangleCold)) + size_t(h.node_count) * sizeof(BVHNode) + size_t(h.index_count) * sizeof(int);
+	if (bytes.size() - sizeof(h) != expect)               throw std::runtime_error("size mismatch in BVH container " + name);
+	const unsigned char * payload = bytes.data() + sizeof(h);
+	if (uint32_t(crc32(0L, payload, uInt(expect))) != h.crc) throw std::runtime_error("checksum mismatch in BVH container " + name);
+	parse_legacy(payload, expect, name);
 }
 
 void BottomLevelBVH::build(std::vector<TriangleHot> hot, std::vector<TriangleCold> cold) {

@@ -87,6 +87,16 @@ struct BottomLevelBVH {
 	void load_from_disk(const std::string & bvh_filename);
 	void save_to_disk  (const std::string & bvh_filename) const; // writes the un-flattened form back
 
+	// Versioned container around the same payload: the reference's dump has no
+	// magic, version or checksum, so a truncated or foreign file is only noticed as garbage geometry.
+	//   char magic[8] = "B200BVH\0"; u32 endian_tag = 0x01020304; u32 version = 1;
+	//   u32 triangle_count, node_count, index_count; u32 crc32(payload); then the legacy payload.
+	// load_container throws std::runtime_error on a bad magic / version / endianness / size / CRC.
+	// `<obj>.bvh` stays the legacy dump (the reference reads it); the container lives beside it as
+	// `<obj>.b200bvh` and is preferred when valid.
+	void load_container(const std::string & filename);
+	void save_container(const std::string & filename) const;
+
 	// Builds a plain SAH BVH over (hot, cold) given in OBJ order (MESH_ACCELERATOR_BVH, Config.h:32).
 	void build(std::vector<TriangleHot> hot, std::vector<TriangleCold> cold);
 
@@ -101,6 +111,7 @@ private:
 	std::vector<int>          file_indices;
 
 	void flatten(); // BottomLevelBVH.cpp:196-212
+	void parse_legacy(const unsigned char * data, size_t size, const std::string & name);
 };
 
 } // namespace b200rt

@@ -222,10 +222,20 @@ int Scene::load_blas(const std::string & obj_path) {
 	if (it != blas_cache.end()) return it->second;
 
 	auto bvh = std::make_unique<BottomLevelBVH>();
-	const std::string bvh_path = obj_path + ".bvh";
+	const std::string bvh_path = obj_path + ".bvh";            // the reference's dump: what its binary reads and writes
+	const std::string container_path = obj_path + ".b200bvh";   // the same payload behind a header with a checksum
 
-	if (file_exists(bvh_path)) {
+	bool loaded = false;
+	if (file_exists(container_path)) {
+		try { bvh->load_container(container_path); loaded = true; }
+		catch (const std::exception & e) { fprintf(stderr, "b200rt: ignoring %s (%s)\n", container_path.c_str(), e.what()); *bvh = BottomLevelBVH(); }
+	}
+	if (!loaded && file_exists(bvh_path)) {
 		bvh->load_from_disk(bvh_path);
+		loaded = true;
+		try { bvh->save_container(container_path); } catch (const std::exception &) { }
+	}
+	if (loaded) {
 		load_mtl(*bvh, obj_path);
 	} else {
 		load_mtl(*bvh, obj_path);
@@ -235,7 +245,7 @@ int Scene::load_blas(const std::string & obj_path) {
 		const char * accel = getenv("B200RT_MESH_ACCELERATOR");
 		if (accel && std::string(accel) == "bvh") bvh->build(std::move(hot), std::move(cold));
 		else bvh->build_sbvh(std::move(hot), std::move(cold), vertices, int(std::max(1u, std::thread::hardware_concurrency())));
-		try { bvh->save_to_disk(bvh_path); } catch (const std::exception &) { /* read-only asset dir: keep going uncached */ }
+		try { bvh->save_to_disk(bvh_path); bvh->save_container(container_path); } catch (const std::exception &) { /* read-only asset dir: keep going uncached */ }
 	}
 
 	blas.push_back(std::move(bvh));

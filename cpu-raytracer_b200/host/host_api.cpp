@@ -91,6 +91,16 @@ int b200rt_build_sbvh(const float * vertices, int triangle_count, int threads, b
 	});
 }
 
+int b200rt_bvh_to_container(const char * legacy_bvh, const char * container) {
+	if (!legacy_bvh || !container) { g_error = "null argument"; return -1; }
+	return guarded([&] { b200rt::BottomLevelBVH bvh; bvh.load_from_disk(legacy_bvh); bvh.save_container(container); });
+}
+
+int b200rt_bvh_container_to_legacy(const char * container, const char * legacy_bvh) {
+	if (!legacy_bvh || !container) { g_error = "null argument"; return -1; }
+	return guarded([&] { b200rt::BottomLevelBVH bvh; bvh.load_container(container); bvh.save_to_disk(legacy_bvh); });
+}
+
 int b200rt_tile_count(int width, int height, int * tiles_x, int * tiles_y) {
 	// Window.cpp:11-12: 32x32 tiles, the last row / column may be partial
 	int tx = (width + 31) / 32, ty = (height + 31) / 32;

@@ -54,6 +54,14 @@ int b200rt_build_sbvh(const float * vertices, int triangle_count, int threads,
                       b200rt_bvh_node * nodes, int node_capacity, int32_t * indices, int index_capacity,
                       int * node_count, int * index_count);
 
+/* `<obj>.bvh` is the reference's headerless dump (BottomLevelBVH.cpp:149-192: no magic, version or
+ * checksum). `<obj>.b200bvh` wraps the same payload in a 32-byte header: magic "B200BVH\0", endian
+ * tag 0x01020304, version, the three counts, CRC-32 of the payload. The scene loader prefers a
+ * valid container, falls back to the dump, and writes both. These convert between the two; a
+ * damaged container is reported (-1 + message), never loaded.                                   */
+int b200rt_bvh_to_container(const char * legacy_bvh, const char * container);
+int b200rt_bvh_container_to_legacy(const char * container, const char * legacy_bvh);
+
 /* Tile partition helper: number of 32x32 tiles and the tiles of one GPU.   */
 int b200rt_tile_count(int width, int height, int * tiles_x, int * tiles_y);
 
