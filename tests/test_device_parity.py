@@ -147,3 +147,28 @@ def test_pipelined_frames_equal_synchronous_frames(golden):
         r.wait()
     del outs
     r.close()
+
+
+def test_pipelined_animation_frames_match_the_reference():
+    """Config 3 (dynamic scene): frames 0 and 45 of the animation — different instance matrices and a
+    different per-frame TopLevelBVH — in flight together through b200rt_submit_frame; each must come
+    out as the real reference rendered it (tests/golden/dynamic_b3_aniso_f0 / _f45)."""
+    from conftest import Golden
+    from b200rt.device import Renderer
+    f0, f45 = Golden("dynamic_b3_aniso_f0"), Golden("dynamic_b3_aniso_f45")
+    assert np.array_equal(f0.pack.a["s_nodes"], f45.pack.a["s_nodes"])            # same static scene ...
+    assert not np.array_equal(f0.pack.a["f_instances"], f45.pack.a["f_instances"])  # ... different frame data
+    m = f0.meta
+    r = Renderer(m["width"], m["height"], m["bounces"], m["filter"])
+    r.upload_static(f0.pack)
+    outs = [r.alloc_outputs(), r.alloc_outputs()]
+    for round_ in range(3):
+        r.submit(f0.pack, outs[0])
+        r.submit(f45.pack, outs[1])
+        r.wait()
+        r.wait()
+        for out, g in ((outs[0], f0), (outs[1], f45)):
+            diff = np.abs(unpack_rgb(out["frame_buffer"]) - unpack_rgb(g.ref_frame_buffer))
+            assert (diff.max(-1) > 0).mean() <= 2e-3 and diff.max() <= 8
+    del outs
+    r.close()
