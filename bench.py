@@ -213,7 +213,11 @@ def run_gpu_arm(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
+    if world > 1 and rank != 0:
+        dist.barrier()                                     # rank 0 generates the stand-in assets and the BVH caches first
     scene_file, scene = build_scene()
+    if world > 1 and rank == 0:
+        dist.barrier()
     pack = scene.pack()
     pixels = WIDTH * HEIGHT
 
@@ -287,6 +291,8 @@ def run_gpu_arm(args):
     else:
         # ---- N GPUs: each rank traces its interleaved tiles, one collective moves the frame to rank 0,
         # rank 0 runs FXAA. Timed on the device with events on the stream everything is issued on. ------
+        stream = torch.cuda.Stream()                       # ONE stream for kernels, barriers / collectives and copies of this rank
+        torch.cuda.set_stream(stream)
         renderer.set_stream(stream.cuda_stream)
         fb = torch.zeros(HEIGHT, WIDTH, dtype=torch.int32, device="cuda")
         presented = torch.empty(HEIGHT, WIDTH, 3, dtype=torch.uint8, device="cuda")
@@ -306,16 +312,23 @@ def run_gpu_arm(args):
                     print("PeerFrame unavailable (%s): gathering with an NCCL reduce" % (str(e).splitlines() or ["?"])[0], file=sys.stderr)
                 peer = None
 
-        def step(e2e):
+        phase_events = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        phase_ms = [0.0, 0.0, 0.0]
+
+        def step(e2e, phases=False):
             if e2e:
                 scene.update(0.0, 0)
                 frame_pack = pack.with_frame(scene.frame_view())
             else:
                 frame_pack = pack
             if peer is not None:
+                if phases: phase_events[0].record(stream)
                 peer.barrier()                             # rank 0 has finished reading the previous frame
+                if phases: phase_events[1].record(stream)
                 renderer.render_device(frame_pack, peer.root_ptr, wait=False)   # pixels are stored into rank 0's image over NVLink
+                if phases: phase_events[2].record(stream)
                 peer.barrier()                             # all tiles have landed
+                if phases: phase_events[3].record(stream)
             else:
                 fb.zero_()                                 # every rank: only its own tiles may be non-zero going into the SUM
                 renderer.render_device(frame_pack, fb.data_ptr(), wait=False)
@@ -336,8 +349,16 @@ def run_gpu_arm(args):
             expect = whole.render(pack)
             whole.close()
             torch.cuda.synchronize()
-            gather_verified = bool(np.array_equal(fb.cpu().numpy().view(np.uint32), expect["frame_buffer"])
-                                   and np.array_equal(presented.cpu().numpy(), expect["presented"]))
+            got_fb, got_rgb = fb.cpu().numpy().view(np.uint32), presented.cpu().numpy()
+            gather_verified = bool(np.array_equal(got_fb, expect["frame_buffer"]) and np.array_equal(got_rgb, expect["presented"]))
+            if not gather_verified:
+                from b200rt.multigpu import TILE, tile_grid
+                bad = got_fb != expect["frame_buffer"]
+                tx, _ = tile_grid(WIDTH, HEIGHT)
+                ys, xs = np.nonzero(bad)
+                owners = ((ys // TILE) * tx + xs // TILE) % world
+                print("gather mismatch: %d frame-buffer pixels (by owning rank: %s), %d presented bytes; zero pixels among them: %d"
+                      % (bad.sum(), np.bincount(owners, minlength=world).tolist(), (got_rgb != expect["presented"]).sum(), (got_fb[bad] == 0).sum()), file=sys.stderr)
 
         for _ in range(args.warmup):
             step(False)
@@ -349,10 +370,13 @@ def run_gpu_arm(args):
                 flush.fill_(1)                              # evict L2, outside the timed region
                 barrier()
                 start.record(stream)
-                step(False)
+                step(False, phases=peer is not None)
                 end.record(stream)
                 torch.cuda.synchronize()
                 total += start.elapsed_time(end)
+                if peer is not None:
+                    for k in range(3):
+                        phase_ms[k] += phase_events[k].elapsed_time(phase_events[k + 1]) / args.steps
         barrier()
         t = torch.tensor([total / args.steps], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -411,6 +435,7 @@ def run_gpu_arm(args):
                     "api": e2e_api, "unpipelined_ms_per_step": e2e_sync_ms},
             "gpu_launches": launches,
             "gather_verified": gather_verified if world > 1 else None,
+            "rank0_phases_ms": None if world == 1 or peer is None else {"barrier_before": phase_ms[0], "upload_and_render": phase_ms[1], "barrier_after": phase_ms[2]},
             "gather": None if world == 1 else ("render kernel stores into rank 0's image over NVLink peer memory + device barrier" if peer is not None else "NCCL reduce(SUM) of disjoint tiles"),
             "clocks": clocks.summary(),
             "roofline": roofline,

@@ -54,6 +54,8 @@ struct b200rt_ctx {
 
 	// outputs
 	DeviceBuffer frame_buffer, presented, colour_float, ids, hits, counters, l2_scratch;
+	DeviceBuffer tile_cost, tile_order; // schedule of the render kernel (kernels.cuh: tile_schedule_kernel)
+	int tile_count_mine = 0;
 	void * pinned_out = nullptr; size_t pinned_out_bytes = 0;
 	FrameCounters * pinned_counters = nullptr;
 
@@ -84,7 +86,14 @@ extern "C" uint64_t b200rt_stream(const b200rt_ctx * ctx) { return ctx ? uint64_
 extern "C" int b200rt_set_stream(b200rt_ctx * ctx, uint64_t stream) {
 	if (!ctx) return -1;
 	cudaStreamSynchronize(ctx->stream);
-	ctx->stream = stream ? reinterpret_cast<cudaStream_t>(uintptr_t(stream)) : ctx->own_stream;
+	ctx->stream = reinterpret_cast<cudaStream_t>(uintptr_t(stream)); // 0 is a stream too: CUDA's default stream
+	return 0;
+}
+
+extern "C" int b200rt_reset_stream(b200rt_ctx * ctx) {
+	if (!ctx) return -1;
+	cudaStreamSynchronize(ctx->stream);
+	ctx->stream = ctx->own_stream;
 	return 0;
 }
 
@@ -138,6 +147,16 @@ extern "C" int b200rt_create(const b200rt_config * config, b200rt_ctx ** out) {
 	if ((e = ctx->counters.ensure(sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMalloc", e);
 	if ((e = cudaMemset(ctx->frame_buffer.ptr, 0, pixels * 4)) != cudaSuccess) return bail("cudaMemset", e);
 	if ((e = cudaMallocHost(reinterpret_cast<void **>(&ctx->pinned_counters), sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMallocHost", e);
+	{ // schedule buffers; the first frame has no cost history: tiles in index order
+		const int tiles = ((config->width + 31) / 32) * ((config->height + 31) / 32);
+		ctx->tile_count_mine = tiles > config->tile_phase ? (tiles - config->tile_phase + config->tile_stride - 1) / config->tile_stride : 0;
+		const int mine = std::max(ctx->tile_count_mine, 1);
+		std::vector<unsigned> identity(mine);
+		for (int i = 0; i < mine; i++) identity[i] = unsigned(i);
+		if ((e = ctx->tile_cost.ensure(size_t(mine) * 4)) != cudaSuccess || (e = ctx->tile_order.ensure(size_t(mine) * 4)) != cudaSuccess) return bail("cudaMalloc", e);
+		if ((e = cudaMemset(ctx->tile_cost.ptr, 0, size_t(mine) * 4)) != cudaSuccess) return bail("cudaMemset", e);
+		if ((e = cudaMemcpy(ctx->tile_order.ptr, identity.data(), size_t(mine) * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return bail("cudaMemcpy", e);
+	}
 
 	*out = ctx;
 	return 0;
@@ -148,7 +167,7 @@ extern "C" void b200rt_destroy(b200rt_ctx * ctx) {
 	cudaSetDevice(ctx->config.device);
 	if (ctx->stream) cudaStreamSynchronize(ctx->stream);
 	for (DeviceBuffer * b : { &ctx->nodes, &ctx->hot, &ctx->cold, &ctx->materials, &ctx->textures, &ctx->texels, &ctx->sky, &ctx->gamma,
-	                          &ctx->frame_block, &ctx->frame_buffer, &ctx->presented, &ctx->colour_float, &ctx->ids, &ctx->hits, &ctx->counters, &ctx->l2_scratch }) b->release();
+	                          &ctx->frame_block, &ctx->frame_buffer, &ctx->presented, &ctx->colour_float, &ctx->ids, &ctx->hits, &ctx->counters, &ctx->l2_scratch, &ctx->tile_cost, &ctx->tile_order }) b->release();
 	for (auto & slot : ctx->slots) {
 		slot.frame_buffer.release(); slot.presented.release(); slot.counters.release();
 		if (slot.pinned_counters) cudaFreeHost(slot.pinned_counters);
@@ -399,6 +418,8 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 	P.tile_stride = c.tile_stride; P.tile_phase = c.tile_phase;
 	const int tiles = P.tiles_x * P.tiles_y;
 	P.tile_count_mine = tiles > c.tile_phase ? (tiles - c.tile_phase + c.tile_stride - 1) / c.tile_stride : 0;
+	P.tile_order = static_cast<const unsigned *>(ctx->tile_order.ptr);
+	P.tile_cost  = static_cast<unsigned *>(ctx->tile_cost.ptr);
 
 	ctx->have_frame = true;
 	return 0;
@@ -408,6 +429,7 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 static int launch_render(b200rt_ctx * ctx, unsigned * frame_buffer, float * colour_float, bool count, void * counters_dev = nullptr) {
 	if (!counters_dev) counters_dev = ctx->counters.ptr;
 	CHECK_CUDA(ctx, cudaMemsetAsync(counters_dev, 0, sizeof(FrameCounters), ctx->stream));
+	CHECK_CUDA(ctx, cudaMemsetAsync(&static_cast<FrameCounters *>(counters_dev)->first_idle_ns, 0xFF, sizeof(unsigned long long), ctx->stream));
 	const unsigned total_warps = unsigned(ctx->params.tile_count_mine) * 32u;
 	if (total_warps == 0) return 0;
 	// persistent grid: every SM filled to the occupancy limit, never more warps than units
@@ -417,6 +439,14 @@ static int launch_render(b200rt_ctx * ctx, unsigned * frame_buffer, float * colo
 	FrameCounters * counters = static_cast<FrameCounters *>(counters_dev);
 	if (count) render_kernel<true ><<<blocks, RT_BLOCK_THREADS, 0, ctx->stream>>>(ctx->params, frame_buffer, colour_float, counters);
 	else       render_kernel<false><<<blocks, RT_BLOCK_THREADS, 0, ctx->stream>>>(ctx->params, frame_buffer, colour_float, counters);
+	CHECK_CUDA(ctx, cudaGetLastError());
+	return 0;
+}
+
+// After the frame (outside the render kernel's timed events): order the tiles for the next one.
+static int launch_schedule(b200rt_ctx * ctx) {
+	if (ctx->params.tile_count_mine == 0) return 0;
+	tile_schedule_kernel<<<1, 1024, 0, ctx->stream>>>(static_cast<unsigned *>(ctx->tile_cost.ptr), static_cast<unsigned *>(ctx->tile_order.ptr), ctx->params.tile_count_mine);
 	CHECK_CUDA(ctx, cudaGetLastError());
 	return 0;
 }
@@ -435,6 +465,7 @@ static void fill_stats(b200rt_ctx * ctx, b200rt_stats * stats) {
 	stats->nodes_visited = c.nodes; stats->triangles_tested = c.triangles; stats->texels_fetched = c.texels;
 	stats->hits_accepted = c.accepted; stats->instances_entered = c.instances;
 	stats->device_ms_render = stats->device_ms_fxaa = stats->device_ms_total = 0.0f;
+	stats->device_ms_tail = c.last_done_ns > c.first_idle_ns ? float(double(c.last_done_ns - c.first_idle_ns) * 1e-6) : 0.0f;
 	cudaEventElapsedTime(&stats->device_ms_render, ctx->ev[1], ctx->ev[2]);
 	cudaEventElapsedTime(&stats->device_ms_fxaa,   ctx->ev[2], ctx->ev[3]);
 }
@@ -464,6 +495,7 @@ extern "C" int b200rt_render_frame(b200rt_ctx * ctx, const b200rt_frame * frame,
 	if (launch_render(ctx, fb, out->colour_float ? static_cast<float *>(ctx->colour_float.ptr) : nullptr, ctx->config.count_traversal != 0)) return -1;
 	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
 	if (out->presented_rgb8 && launch_fxaa(ctx, fb, static_cast<unsigned char *>(ctx->presented.ptr))) return -1;
+	if (launch_schedule(ctx)) return -1;
 	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));
 
 	if (out->primary_ids || out->primary_hit) {
@@ -510,6 +542,7 @@ extern "C" int b200rt_render_frame_device(b200rt_ctx * ctx, const b200rt_frame *
 	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
 	if (launch_render(ctx, reinterpret_cast<unsigned *>(uintptr_t(frame_buffer_dev)), nullptr, false)) return -1;
 	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
+	if (launch_schedule(ctx)) return -1;
 	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));
 	if (!stats) return 0; // asynchronous: the caller orders later work on the context's stream
 	CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->pinned_counters, ctx->counters.ptr, sizeof(FrameCounters), cudaMemcpyDeviceToHost, ctx->stream));
@@ -545,6 +578,7 @@ extern "C" int b200rt_time_resident(b200rt_ctx * ctx, int repeat, uint64_t flush
 		if (launch_render(ctx, fb, nullptr, false)) return -1;
 		CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
 		if (launch_fxaa(ctx, fb, static_cast<unsigned char *>(ctx->presented.ptr))) return -1;
+		if (launch_schedule(ctx)) return -1;
 		CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));
 		CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 		float a = 0.0f, b = 0.0f;
@@ -596,6 +630,7 @@ extern "C" int b200rt_submit_frame(b200rt_ctx * ctx, const b200rt_frame * frame,
 	if (launch_render(ctx, fb, nullptr, ctx->config.count_traversal != 0, slot.counters.ptr)) return -1;
 	CHECK_CUDA(ctx, cudaEventRecord(slot.render_end, ctx->stream));
 	if (out->presented_rgb8 && launch_fxaa(ctx, fb, static_cast<unsigned char *>(slot.presented.ptr))) return -1;
+	if (launch_schedule(ctx)) return -1;
 	CHECK_CUDA(ctx, cudaEventRecord(slot.fxaa_end, ctx->stream));
 
 	// the pre-FXAA image can leave as soon as tracing is done, in parallel with the FXAA kernel
@@ -626,6 +661,7 @@ extern "C" int b200rt_wait_frame(b200rt_ctx * ctx, b200rt_stats * stats) {
 		stats->nodes_visited = c.nodes; stats->triangles_tested = c.triangles; stats->texels_fetched = c.texels;
 		stats->hits_accepted = c.accepted; stats->instances_entered = c.instances;
 		stats->device_ms_render = stats->device_ms_fxaa = stats->device_ms_total = 0.0f;
+		stats->device_ms_tail = c.last_done_ns > c.first_idle_ns ? float(double(c.last_done_ns - c.first_idle_ns) * 1e-6) : 0.0f;
 		cudaEventElapsedTime(&stats->device_ms_render, slot.render_begin, slot.render_end);
 		cudaEventElapsedTime(&stats->device_ms_fxaa,   slot.render_end, slot.fxaa_end);
 		cudaEventElapsedTime(&stats->device_ms_total,  slot.begin, slot.copied);

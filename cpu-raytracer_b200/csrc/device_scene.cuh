@@ -64,6 +64,10 @@ struct SceneParams {
 	int width, height, bounces, mipmap_filter;
 	float max_anisotropy;
 	int tiles_x, tiles_y, tile_stride, tile_phase, tile_count_mine;
+	// schedule (kernels.cuh, tile_schedule_kernel): this GPU's tiles in hand-out order, and where this
+	// frame's cost per tile is accumulated for the next frame's order
+	const unsigned * __restrict__ tile_order;
+	unsigned * __restrict__ tile_cost;
 };
 
 struct FrameCounters {   // accumulated with one atomicAdd per warp
@@ -71,6 +75,7 @@ struct FrameCounters {   // accumulated with one atomicAdd per warp
 	unsigned long long nodes, triangles, texels, accepted, instances;
 	unsigned int next_unit;      // work-stealing cursor (WorkerThread.cpp:53-54)
 	unsigned int pad;
+	unsigned long long first_idle_ns, last_done_ns; // globaltimer when the first / the last warp ran out of work: the tail of the launch
 };
 
 } // namespace rt

@@ -12,10 +12,12 @@ __device__ __forceinline__ unsigned warp_sum(unsigned v) {
 
 // Maps a work unit to a pixel. The frame is cut into the reference's 32x32 tiles (Window.h:32-33,
 // Window.cpp:11-12); this GPU owns the tiles t with t % tile_stride == tile_phase (SURVEY.md
-// 8(e)); a unit is one warp-sized 8x4 pixel block, 32 units per tile, numbered tile-major so that
+// 8(e)), handed out in the order of P.tile_order (tile_schedule_kernel: expensive tiles first); a
+// unit is one warp-sized 8x4 pixel block, 32 units per tile, numbered tile-major so that
 // consecutive units (taken by neighbouring warps) stay in one tile.
-__device__ __forceinline__ bool unit_pixel(const SceneParams & P, unsigned unit, int lane, int & px, int & py) {
-	const int tile = P.tile_phase + int(unit >> 5) * P.tile_stride;
+__device__ __forceinline__ bool unit_pixel(const SceneParams & P, unsigned unit, int lane, int & local_tile, int & px, int & py) {
+	local_tile = int(__ldg(P.tile_order + (unit >> 5)));
+	const int tile = P.tile_phase + local_tile * P.tile_stride;
 	const int sub  = int(unit & 31);
 	px = (tile % P.tiles_x) * 32 + (sub & 3) * 8 + (lane & 7);
 	py = (tile / P.tiles_x) * 32 + (sub >> 2) * 4 + (lane >> 3);
@@ -39,8 +41,9 @@ render_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, float *
 		unit = __shfl_sync(0xffffffffu, unit, 0);
 		if (unit >= total_units) break;
 
-		int px, py;
-		if (unit_pixel(P, unit, lane, px, py)) {
+		const long long unit_begin = clock64();
+		int local_tile, px, py;
+		if (unit_pixel(P, unit, lane, local_tile, px, py)) {
 			const Ray ray = primary_ray(P, px, py);
 			primary++;
 			const v3 colour = shade_pixel<COUNT>(P, ray, cnt);
@@ -50,6 +53,14 @@ render_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, float *
 			if (colour_float) { colour_float[3 * p] = colour.x; colour_float[3 * p + 1] = colour.y; colour_float[3 * p + 2] = colour.z; }
 		}
 		__syncwarp();
+		if (lane == 0) atomicAdd(P.tile_cost + local_tile, unsigned((clock64() - unit_begin) >> 6)); // what this tile cost, for the next frame's order
+	}
+
+	if (lane == 0) { // when did this warp run dry? (min / max over warps = how long the launch ran partly empty)
+		unsigned long long now;
+		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+		atomicMin(&counters->first_idle_ns, now);
+		atomicMax(&counters->last_done_ns, now);
 	}
 
 	// one atomic per warp and counter
@@ -71,6 +82,33 @@ render_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, float *
 			atomicAdd(&counters->texels, (unsigned long long)s_texels);
 		}
 	}
+}
+
+// Next frame's hand-out order from this frame's measured tile costs: most expensive first (counting
+// sort over 256 logarithmic cost classes, one block), so that the launch does not end with a few
+// warps inside a costly tile and the rest of the GPU idle. Any order gives the same image; the
+// reference's countdown uses index order (WorkerThread.cpp:53-58). Resets the costs.
+// Measured (tools/tail_probe.py, bench frame): time with some warps already out of work 0.17 -> 0.08
+// ms on one GPU's share of the frame. Splitting expensive tiles into 8-pixel items as well was tried
+// and dropped: what bounds a costly unit is the serial recursion of its most expensive PIXEL
+// (~0.3 ms), so narrower warps only multiplied the warp-time.
+__global__ void __launch_bounds__(1024)
+tile_schedule_kernel(unsigned * __restrict__ tile_cost, unsigned * __restrict__ tile_order, int tile_count) {
+	__shared__ unsigned histogram[256];
+	__shared__ unsigned offset[256];
+	for (int i = threadIdx.x; i < 256; i += blockDim.x) histogram[i] = 0;
+	__syncthreads();
+	auto cost_class = [](unsigned cost) { // 8 classes per octave, expensive = low class number
+		const int k = 255 - int(8.0f * log2f(float(cost) + 1.0f));
+		return k < 0 ? 0 : k;
+	};
+	for (int t = threadIdx.x; t < tile_count; t += blockDim.x) atomicAdd(&histogram[cost_class(tile_cost[t])], 1u);
+	__syncthreads();
+	if (threadIdx.x == 0) { unsigned sum = 0; for (int i = 0; i < 256; i++) { offset[i] = sum; sum += histogram[i]; } }
+	__syncthreads();
+	for (int t = threadIdx.x; t < tile_count; t += blockDim.x) tile_order[atomicAdd(&offset[cost_class(tile_cost[t])], 1u)] = unsigned(t);
+	__syncthreads();
+	for (int t = threadIdx.x; t < tile_count; t += blockDim.x) tile_cost[t] = 0;
 }
 
 // Closest-hit record of the primary ray per pixel: (instance, flattened triangle) and

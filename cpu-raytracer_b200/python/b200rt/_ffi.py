@@ -55,7 +55,7 @@ class Stats(C.Structure):
         ("primary_rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("reflection_rays", C.c_uint64), ("refraction_rays", C.c_uint64),
         ("nodes_visited", C.c_uint64), ("triangles_tested", C.c_uint64), ("texels_fetched", C.c_uint64),
         ("hits_accepted", C.c_uint64), ("instances_entered", C.c_uint64),
-        ("device_ms_render", C.c_float), ("device_ms_fxaa", C.c_float), ("device_ms_total", C.c_float),
+        ("device_ms_render", C.c_float), ("device_ms_fxaa", C.c_float), ("device_ms_total", C.c_float), ("device_ms_tail", C.c_float),
     ]
 
     def as_dict(self):
@@ -127,6 +127,7 @@ def device_lib():
         lib.b200rt_host_free.argtypes = [C.c_void_p]
         lib.b200rt_host_free.restype = None
         lib.b200rt_set_stream.argtypes = [C.c_void_p, C.c_uint64]
+        lib.b200rt_reset_stream.argtypes = [C.c_void_p]
         lib.b200rt_stream.argtypes = [C.c_void_p]
         lib.b200rt_stream.restype = C.c_uint64
         _device = lib

@@ -131,8 +131,12 @@ class Renderer:
         return a.value, b.value
 
     def set_stream(self, stream):
-        """Issue this context's work on a caller-owned CUDA stream (integer handle); 0 = back to its own."""
+        """Issue this context's work on a caller-owned CUDA stream (integer handle; 0 is CUDA's default stream)."""
         self._check(self._lib.b200rt_set_stream(self._h, C.c_uint64(stream)))
+
+    def reset_stream(self):
+        """Back to the context's own stream."""
+        self._check(self._lib.b200rt_reset_stream(self._h))
 
     @property
     def stream(self):

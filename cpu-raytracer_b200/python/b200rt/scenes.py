@@ -101,8 +101,10 @@ class SceneWriter:
 
     def write(self, path):
         os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
-        with open(path, "w") as f:
+        partial = "%s.%d.part" % (path, os.getpid())       # several ranks may write the same scene file: never expose half of it
+        with open(partial, "w") as f:
             f.write("\n".join(self.lines) + "\n")
+        os.replace(partial, path)
         return path
 
 

@@ -151,6 +151,7 @@ typedef struct {
 	float    device_ms_render;     /* CUDA-event time of the ray tracing kernel(s)           */
 	float    device_ms_fxaa;       /* CUDA-event time of the FXAA kernel                     */
 	float    device_ms_total;      /* uploads + kernels + downloads on the context's stream  */
+	float    device_ms_tail;       /* part of device_ms_render during which some warps had already run out of work */
 } b200rt_stats;
 
 /* Host buffers to fill; any pointer may be NULL to skip that output.                      */
@@ -213,10 +214,13 @@ int b200rt_present_device(b200rt_ctx * ctx, uint64_t frame_buffer_dev, uint64_t 
 int b200rt_time_resident(b200rt_ctx * ctx, int repeat, uint64_t flush_l2_bytes, float * ms_render, float * ms_fxaa);
 
 /* The CUDA stream (cudaStream_t as integer) all work of this context is issued on. A caller
- * that orders this context's work against its own (e.g. NCCL on a torch stream) may replace
- * it; stream 0 restores the context's own stream. The context never owns a caller's stream.  */
+ * that orders this context's work against its own (e.g. a collective on a torch stream) may
+ * replace it with b200rt_set_stream — ANY handle, including 0 = CUDA's default stream, is taken
+ * as given; b200rt_reset_stream goes back to the context's own stream. The context never owns a
+ * caller's stream.                                                                            */
 uint64_t b200rt_stream(const b200rt_ctx * ctx);
 int      b200rt_set_stream(b200rt_ctx * ctx, uint64_t stream);
+int      b200rt_reset_stream(b200rt_ctx * ctx);
 
 #ifdef __cplusplus
 }
