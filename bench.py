@@ -38,13 +38,24 @@ sys.path.insert(0, os.path.join(REPO, "cpu-raytracer_b200", "python"))
 WIDTH, HEIGHT, BOUNCES, FILTER = 1920, 1080, 3, "tri"
 REF_VARIANT = "l8_b3_tri"
 METRIC = "Mrays/s, Sponza(stand-in) 1920x1080, trilinear mip-maps, point+directional light with shadows, 3 bounces"
+WORKLOAD = "configs[1]: Sponza 1920x1080 trilinear, point + directional lights with shadows, 3 bounces (stand-in geometry, seed 1234)"
+SCENE = "sponza"
+DATA_NOTE = "synthetic (procedural Sponza stand-in, seed 1234; sponza.obj is missing from the reference checkout)"
 L2_FLUSH_BYTES = 256 << 20
+
+# --workload sibenik4k: BASELINE.json configs[4] (the multi-GPU scaling case of north_star), not the headline line
+OTHER_WORKLOADS = {
+    "sibenik4k": dict(WIDTH=3840, HEIGHT=2160, BOUNCES=3, FILTER="aniso", REF_VARIANT="l8_b3_aniso", SCENE="sibenik",
+                      DATA_NOTE="synthetic (procedural Sibenik stand-in, seed 4321; sibenik.obj is missing from the reference checkout)",
+                      METRIC="Mrays/s, Sibenik(stand-in) 3840x2160, anisotropic mip-maps, spot+point light with shadows, 3 bounces",
+                      WORKLOAD="configs[4]: Sibenik 3840x2160, spot + point shadows, 3 bounces, tiles partitioned across the GPUs (stand-in geometry, seed 4321)"),
+}
 
 
 def workload_config(n_gpus):
     return {
-        "workload": "configs[1]: Sponza 1920x1080 trilinear, point + directional lights with shadows, 3 bounces (stand-in geometry, seed 1234)",
-        "resolution": [WIDTH, HEIGHT], "bounces": BOUNCES, "mipmap_filter": "trilinear", "fxaa": True,
+        "workload": WORKLOAD,
+        "resolution": [WIDTH, HEIGHT], "bounces": BOUNCES, "mipmap_filter": {"tri": "trilinear", "aniso": "anisotropic", "ewa": "ewa"}[FILTER], "fxaa": True,
         "tiles": "32x32, tile t -> GPU t %% %d, device-side work counter per GPU" % n_gpus,
         "l2": "flushed between timed steps (256 MiB memset, outside the timed region)",
         "ray_count": "active rays (primary + shadow + reflection + refraction), reference's PerformanceStats per ray",
@@ -96,7 +107,7 @@ class ClockSampler:
 def build_scene():
     from b200rt import standin
     from b200rt.host import HostScene
-    scene_file = standin.sponza_standin(width=WIDTH, height=HEIGHT)
+    scene_file = (standin.sponza_standin if SCENE == "sponza" else standin.sibenik_standin)(width=WIDTH, height=HEIGHT)
     scene = HostScene(scene_file)
     scene.update(0.0, 0)
     return scene_file, scene
@@ -187,7 +198,7 @@ def run_reference_arm(args):
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": len(ms), "warmup": args.warmup,
         "ms_per_step": total_ms / len(ms), "frames_per_s": 1e3 * len(ms) / total_ms, "higher_is_better": True, "scaling": "strong",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic (procedural Sponza stand-in, seed 1234)", "config": workload_config(args.gpus),
+        "vs_baseline": None, "dtype": "f32", "data": DATA_NOTE, "config": workload_config(args.gpus),
         "rays_per_frame": rays,
         "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -426,7 +437,7 @@ def run_gpu_arm(args):
         line = {
             "metric": METRIC, "value": rays / ms_step / 1e3, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "frames_per_s": 1e3 / ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic (procedural Sponza stand-in, seed 1234; sponza.obj is missing from the reference checkout)",
+            "dtype": "f32", "data": DATA_NOTE,
             "config": workload_config(world),
             "rays_per_frame": rays, "rays": {k: full_stats[k] for k in ("primary_rays", "shadow_rays", "reflection_rays", "refraction_rays")},
             "ms_render_kernel": ms_render, "ms_fxaa_kernel": ms_fxaa,
@@ -453,7 +464,10 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="sponza1080", choices=["sponza1080"] + sorted(OTHER_WORKLOADS))
     args = ap.parse_args()
+    if args.workload != "sponza1080":
+        globals().update(OTHER_WORKLOADS[args.workload])
     if args.warmup < 3:
         args.warmup = 3
     if args.impl == "reference":

@@ -215,7 +215,9 @@ extern "C" int b200rt_upload_static(b200rt_ctx * ctx, const b200rt_static_scene 
 	if (s->node_count <= 0 || s->triangle_count <= 0 || s->blas_count <= 0 || !s->nodes || !s->triangles_hot || !s->triangles_cold || !s->blas) return fail(ctx, "static scene needs at least one BLAS with nodes and triangles");
 	if (s->material_count <= 0 || s->material_count > 256 || !s->materials) return fail(ctx, "material_count must be in 1..256 (MAX_MATERIALS, Config.h:18)");
 	if (s->sky_size <= 0 || !s->sky) return fail(ctx, "a sky probe is required (Sky.cpp:11)");
-	if (s->texture_count < 0 || (s->texture_count > 0 && (!s->textures || !s->texels))) return fail(ctx, "bad texture arrays");
+	const bool gpu_ingest = !s->texels && s->texels_rgb8;
+	if (s->texture_count < 0 || (s->texture_count > 0 && (!s->textures || (!s->texels && !s->texels_rgb8)))) return fail(ctx, "bad texture arrays");
+	if (gpu_ingest && !s->gamma_lut) return fail(ctx, "texels_rgb8 needs gamma_lut");
 
 	// validate indices: the kernels trust them
 	for (int b = 0; b < s->blas_count; b++) {
@@ -287,13 +289,53 @@ extern "C" int b200rt_upload_static(b200rt_ctx * ctx, const b200rt_static_scene 
 			}
 			return 0;
 		};
-		if (upload_rgb(ctx->texels, s->texels, size_t(s->texel_count))) return -1;
+		if (!gpu_ingest) {
+			if (upload_rgb(ctx->texels, s->texels, size_t(s->texel_count))) return -1;
+		} else {
+			// the 8-bit level-0 images go up as they are; conversion and mip chains are built in HBM
+			size_t level0_texels = 0;
+			for (int t = 0; t < s->texture_count; t++) level0_texels += size_t(s->textures[t].width) * s->textures[t].height;
+			DeviceBuffer bytes, lut;
+			cudaError_t e = bytes.ensure(level0_texels * 3);
+			if (e == cudaSuccess) e = lut.ensure(256 * sizeof(float));
+			if (e == cudaSuccess) e = ctx->texels.ensure(std::max<size_t>(size_t(s->texel_count), 1) * sizeof(float4));
+			if (e == cudaSuccess) e = cudaMemcpyAsync(bytes.ptr, s->texels_rgb8, level0_texels * 3, cudaMemcpyHostToDevice, ctx->stream);
+			if (e == cudaSuccess) e = cudaMemcpyAsync(lut.ptr, s->gamma_lut, 256 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream);
+			size_t source = 0;
+			for (int t = 0; t < s->texture_count && e == cudaSuccess; t++) {
+				const b200rt_texture & tex = s->textures[t];
+				float4 * pool = static_cast<float4 *>(ctx->texels.ptr) + tex.texel_offset;
+				const long long n = (long long)tex.width * tex.height;
+				texture_level0_kernel<<<unsigned(std::min<long long>((n + 255) / 256, 148 * 8)), 256, 0, ctx->stream>>>(static_cast<const unsigned char *>(bytes.ptr) + source * 3, static_cast<const float *>(lut.ptr), pool, n);
+				source += size_t(n);
+				int previous_width = tex.width;
+				for (int level = 1; level < tex.mip_levels && tex.mipmapped; level++) {
+					const int w = tex.width >> level, h = tex.height >> level;
+					texture_mip_kernel<<<dim3((w + 31) / 32, (h + 7) / 8), 256, 0, ctx->stream>>>(pool + tex.mip_offsets[level - 1], pool + tex.mip_offsets[level], w, h, previous_width);
+					previous_width = w;
+				}
+				e = cudaGetLastError();
+			}
+			if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+			bytes.release(); lut.release();
+			if (e != cudaSuccess) { ctx->error = std::string("texture ingest: ") + cudaGetErrorString(e); return -1; }
+		}
 		if (upload_rgb(ctx->sky, s->sky, size_t(s->sky_size) * s->sky_size + 1)) return -1; // + the pad texel (Sky.cpp:45)
 	}
 	ctx->sky_size = s->sky_size;
 	ctx->blas.assign(s->blas, s->blas + s->blas_count);
 	ctx->have_static = true;
 	ctx->have_frame = false;
+	return 0;
+}
+
+extern "C" int b200rt_download_texels(b200rt_ctx * ctx, float * texels, int64_t first, int64_t count) {
+	if (!ctx) return -1;
+	if (!texels || first < 0 || count < 0 || size_t(first + count) * sizeof(float4) > ctx->texels.bytes) return fail(ctx, "texel range out of bounds");
+	CHECK_CUDA(ctx, cudaSetDevice(ctx->config.device));
+	std::vector<float4> staging(static_cast<size_t>(count));
+	CHECK_CUDA(ctx, cudaMemcpy(staging.data(), static_cast<const float4 *>(ctx->texels.ptr) + first, size_t(count) * sizeof(float4), cudaMemcpyDeviceToHost));
+	for (int64_t i = 0; i < count; i++) { texels[3 * i] = staging[i].x; texels[3 * i + 1] = staging[i].y; texels[3 * i + 2] = staging[i].z; }
 	return 0;
 }
 

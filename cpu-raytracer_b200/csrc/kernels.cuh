@@ -138,6 +138,31 @@ primary_hits_kernel(const SceneParams P, int * __restrict__ ids, float * __restr
 	}
 }
 
+// -------------------------------------------------------------------- texture ingest ---
+// Texture::load's two host loops (Texture.cpp:62-117) on the device. Level 0: 8-bit sRGB -> linear
+// float through the 256-entry table of gamma_to_linear(i * 0.00392156862f) (the reference converts
+// texel by texel; 256 possible inputs give 256 possible outputs). Level k: 2x2 box filter of level
+// k-1, summed in the reference's order ((c0 + c1) + c2) + c3, times 0.25. Texels are float4 (pad 0).
+__global__ void __launch_bounds__(256)
+texture_level0_kernel(const unsigned char * __restrict__ rgb8, const float * __restrict__ gamma_lut, float4 * __restrict__ out, long long texel_count) {
+	__shared__ float lut[256];
+	lut[threadIdx.x] = gamma_lut[threadIdx.x];
+	__syncthreads();
+	for (long long i = blockIdx.x * 256ll + threadIdx.x; i < texel_count; i += gridDim.x * 256ll)
+		out[i] = make_float4(lut[rgb8[3 * i]], lut[rgb8[3 * i + 1]], lut[rgb8[3 * i + 2]], 0.0f);
+}
+
+__global__ void __launch_bounds__(256)
+texture_mip_kernel(const float4 * __restrict__ previous, float4 * __restrict__ out, int width, int height, int previous_width) {
+	const int i = blockIdx.x * 32 + (threadIdx.x & 31), j = blockIdx.y * 8 + (threadIdx.x >> 5);
+	if (i >= width || j >= height) return;
+	const float4 c0 = previous[size_t(2 * i)     + size_t(2 * j)     * previous_width];
+	const float4 c1 = previous[size_t(2 * i + 1) + size_t(2 * j)     * previous_width];
+	const float4 c2 = previous[size_t(2 * i)     + size_t(2 * j + 1) * previous_width];
+	const float4 c3 = previous[size_t(2 * i + 1) + size_t(2 * j + 1) * previous_width];
+	out[size_t(i) + size_t(j) * width] = make_float4((((c0.x + c1.x) + c2.x) + c3.x) * 0.25f, (((c0.y + c1.y) + c2.y) + c3.y) * 0.25f, (((c0.z + c1.z) + c2.z) + c3.z) * 0.25f, 0.0f);
+}
+
 // ------------------------------------------------------------------------------ FXAA ---
 // Data/Shaders/fragment_fxaa.glsl:11-74 (+ fragment_identity.glsl) as a compute kernel. Sampler
 // state of Window.cpp:48-50: NEAREST, GL_REPEAT, RGBA8; uv of pixel (px, py) = ((px+.5)/W,

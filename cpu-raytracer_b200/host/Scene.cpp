@@ -434,6 +434,8 @@ b200rt_static_scene Scene::static_view() {
 	s.materials = flat_materials.data(); s.material_count = int(flat_materials.size());
 	s.textures = texture_pool.textures.data(); s.texture_count = int(texture_pool.textures.size());
 	s.texels = texture_pool.texels.data();     s.texel_count = int64_t(texture_pool.texels.size() / 3);
+	s.texels_rgb8 = texture_pool.rgb8.empty() ? nullptr : texture_pool.rgb8.data();
+	s.gamma_lut   = texture_pool.gamma_lut;
 	s.sky = sky.data();                  s.sky_size = sky_size;
 	return s;
 }

@@ -209,6 +209,10 @@ int TexturePool::load(const std::string & path) {
 	return index;
 }
 
+TexturePool::TexturePool() {
+	for (int i = 0; i < 256; i++) gamma_lut[i] = gamma_to_linear(float(i) * 0.00392156862f);
+}
+
 int TexturePool::add(const Image & image) {
 	const int w = image.width, h = image.height;
 
@@ -224,13 +228,17 @@ int TexturePool::add(const Image & image) {
 
 	// Level 0: byte/255 (as a multiply by 0.00392156862f, Texture.cpp:13-20) then sRGB -> linear.
 	// A 256-entry table gives the same floats as converting texel by texel.
-	float lut[256];
-	for (int i = 0; i < 256; i++) lut[i] = gamma_to_linear(float(i) * 0.00392156862f);
+	const float * lut = gamma_lut;
 
 	const size_t base = texels.size();
 	texels.resize(base + size_t(w) * h * 3);
+	const size_t base8 = rgb8.size();
+	rgb8.resize(base8 + size_t(w) * h * 3);
 	for (size_t p = 0; p < size_t(w) * h; p++) {
-		for (int c = 0; c < 3; c++) texels[base + p * 3 + c] = lut[image.rgba[p * 4 + c]];
+		for (int c = 0; c < 3; c++) {
+			rgb8[base8 + p * 3 + c] = image.rgba[p * 4 + c];
+			texels[base + p * 3 + c] = lut[image.rgba[p * 4 + c]];
+		}
 	}
 
 	if (texture.mipmapped) {

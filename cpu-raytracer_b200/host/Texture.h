@@ -27,7 +27,11 @@ void save_tga(const std::string & path, int width, int height, const uint8_t * r
 
 struct TexturePool {
 	std::vector<b200rt_texture> textures;
-	std::vector<float>          texels; // float[n][3]
+	std::vector<float>          texels; // float[n][3]: every pyramid, built on the host
+	std::vector<uint8_t>        rgb8;   // level-0 images only, 3 bytes per texel, texture after texture: input of the GPU ingest
+	float                       gamma_lut[256]; // Math::gamma_to_linear(i * 0.00392156862f)
+
+	TexturePool();
 
 	// Returns the texture index; a path is loaded once (texture_cache, Texture.cpp:10,31-34).
 	int load(const std::string & path);

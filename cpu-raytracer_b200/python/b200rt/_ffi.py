@@ -23,6 +23,7 @@ class StaticScene(C.Structure):
         ("textures", C.c_void_p), ("texture_count", C.c_int32),
         ("texels", C.c_void_p), ("texel_count", C.c_int64),
         ("sky", C.c_void_p), ("sky_size", C.c_int32),
+        ("texels_rgb8", C.c_void_p), ("gamma_lut", C.c_void_p),
     ]
 
 
@@ -121,6 +122,7 @@ def device_lib():
         lib.b200rt_render_frame_device.argtypes = [C.c_void_p, C.POINTER(Frame), C.c_uint64, C.POINTER(Stats)]
         lib.b200rt_present_device.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_float)]
         lib.b200rt_time_resident.argtypes = [C.c_void_p, C.c_int, C.c_uint64, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+        lib.b200rt_download_texels.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64]
         lib.b200rt_submit_frame.argtypes = [C.c_void_p, C.POINTER(Frame), C.POINTER(Outputs)]
         lib.b200rt_wait_frame.argtypes = [C.c_void_p, C.POINTER(Stats)]
         lib.b200rt_host_alloc.argtypes = [C.c_uint64, C.POINTER(C.c_void_p)]

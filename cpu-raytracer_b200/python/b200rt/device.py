@@ -48,9 +48,14 @@ class Renderer:
         if rc != 0:
             raise DeviceError(self._lib.b200rt_last_error(self._h).decode())
 
-    def upload_static(self, pack):
-        view = pack.static_view()
+    def upload_static(self, pack, gpu_texture_ingest=False):
+        view = pack.static_view(gpu_texture_ingest)
         self._check(self._lib.b200rt_upload_static(self._h, C.byref(view)))
+
+    def download_texels(self, first, count):
+        out = np.zeros((count, 3), dtype=np.float32)
+        self._check(self._lib.b200rt_download_texels(self._h, out.ctypes.data, first, count))
+        return out
 
     def alloc_outputs(self):
         """Page-locked output images (b200rt_host_alloc): render(..., out=...) then DMAs straight into them."""

@@ -48,6 +48,10 @@ class ScenePack:
         sky_texels = static_view.sky_size * static_view.sky_size + 1
         a["s_sky"] = _copy(static_view.sky, sky_texels * 12)
         a["s_sky_size"] = np.array([static_view.sky_size], dtype=np.int32)
+        if static_view.texels_rgb8 and static_view.gamma_lut:   # level-0 8-bit images + table: input of the GPU texture ingest
+            level0 = sum(int(t[2]) * int(t[3]) for t in a["s_textures"].view("<i4").reshape(-1, 22)) if a["s_textures"].size else 0
+            a["s_texels_rgb8"] = _copy(static_view.texels_rgb8, level0 * 3)
+            a["s_gamma_lut"] = _copy(static_view.gamma_lut, 256 * 4)
         a.update(cls._capture_frame(frame_view))
         return cls(a)
 
@@ -88,13 +92,20 @@ class ScenePack:
         arr = self.a[key]
         return arr.ctypes.data if arr.size else None
 
-    def static_view(self):
+    def static_view(self, gpu_texture_ingest=False):
+        """gpu_texture_ingest: hand the device the 8-bit level-0 images instead of the float pyramids."""
         s = _ffi.StaticScene()
         for field, count_field, rec in _STATIC_ARRAYS:
             setattr(s, field, self._ptr("s_" + field))
             setattr(s, count_field, self.a["s_" + field].size // rec)
         s.sky = self._ptr("s_sky")
         s.sky_size = int(self.a["s_sky_size"][0])
+        if gpu_texture_ingest:
+            if "s_texels_rgb8" not in self.a:
+                raise ValueError("this pack carries no 8-bit texture images")
+            s.texels = None
+            s.texels_rgb8 = self._ptr("s_texels_rgb8")
+            s.gamma_lut = self._ptr("s_gamma_lut")
         return s
 
     def frame_view(self):

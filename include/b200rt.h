@@ -84,6 +84,14 @@ typedef struct {
 	const b200rt_texture       * textures;       int32_t texture_count;
 	const float                * texels;         int64_t texel_count;     /* float[texel_count][3] */
 	const float                * sky;            int32_t sky_size;        /* float[size*size (+1)][3], Sky.cpp:13-25 */
+	/* Optional texture ingest ON THE GPU (replaces the host loops of Texture::load, Texture.cpp:62-117):
+	 * when texels == NULL and texels_rgb8 != NULL the device converts the 8-bit level-0 images
+	 * (texture after texture, width*height*3 bytes each, row 0 = top) through gamma_lut — the 256
+	 * values of Math::gamma_to_linear(i * 0.00392156862f), Texture.cpp:13-20,64-72 — and box-filters
+	 * the mip chains itself, with the reference's association ((c0+c1)+c2)+c3)*0.25. Same floats as
+	 * the host path; a fifth of the upload. texel_count is the size of the whole pyramid pool either way. */
+	const uint8_t              * texels_rgb8;
+	const float                * gamma_lut;      /* float[256] */
 } b200rt_static_scene;
 
 /* Mesh, Mesh.h:8-16: instance of a BLAS. Matrices are the reference's Matrix4 (column-major
@@ -179,6 +187,10 @@ int b200rt_upload_static(b200rt_ctx * ctx, const b200rt_static_scene * scene);
 /* Replaces Main.cpp:56-59 for one frame. Host buffers in, host buffers out: uploads the
  * per-frame data, renders, applies FXAA, downloads the requested outputs.                  */
 int b200rt_render_frame(b200rt_ctx * ctx, const b200rt_frame * frame, const b200rt_outputs * outputs);
+
+/* Reads the texel pool back (float[count][3], the layout of b200rt_static_scene.texels): lets a
+ * test compare the GPU-ingested pyramids with the host-built ones.                              */
+int b200rt_download_texels(b200rt_ctx * ctx, float * texels, int64_t first, int64_t count);
 
 /* Pipelined form of b200rt_render_frame, for a frame loop: submit enqueues frame n (upload, trace,
  * FXAA, copies into PAGE-LOCKED output images) and returns at once; wait blocks until the OLDEST
