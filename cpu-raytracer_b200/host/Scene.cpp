@@ -1,6 +1,8 @@
 #include "Scene.h"
 
+#include <cmath>
 #include <cstdlib>
+#include <limits>
 #include <thread>
 
 #include <algorithm>
@@ -144,9 +146,91 @@ void Scene::load_mtl(BottomLevelBVH & bvh, const std::string & obj_path) {
 	if (materials.size() > 256) throw std::runtime_error("Max Material limit reached (MAX_MATERIALS 256, Config.h:18)");
 }
 
-// Triangle soup from a Wavefront OBJ. Polygons are fan-triangulated. Needs `vn` (the
-// reference indexes normals unconditionally, OBJLoader.cpp:143-145); `vt` is optional and V is
-// flipped to 1 - v (OBJLoader.cpp:139-141).
+namespace {
+struct Corner { int v, t, n; };
+
+// Crossing-number test of (x, y) against a triangle, the way tinyobjloader's pnpoly decides it
+// (tiny_obj_loader.h:1316-1326): same edge order, same float expression.
+bool inside_triangle(const float tx[3], const float ty[3], float x, float y) {
+	bool inside = false;
+	for (int i = 0, j = 2; i < 3; j = i++) {
+		if ((ty[i] > y) != (ty[j] > y) && x < (tx[j] - tx[i]) * (y - ty[i]) / (ty[j] - ty[i]) + tx[i]) inside = !inside;
+	}
+	return inside;
+}
+
+// The reference loads meshes through tinyobjloader 2.0.0 with triangulate = true (OBJLoader.cpp:97),
+// which does NOT fan polygons: it ear-clips them in a 2-D projection (tiny_obj_loader.h:1355-1557).
+// The triangle order and the corner rotation of every triangle feed the BVH builder and the
+// barycentric interpolation, so they are reproduced exactly:
+//   * projection axes from the first corner whose cross product is above FLT_EPSILON — drop x if it
+//     holds the strictly largest component, else drop y unless z is strictly largest, then drop z;
+//   * signed area of the projected polygon by the shoelace sum;
+//   * walk a candidate ear (g, g+1, g+2): skipped when it turns against the polygon or when another
+//     remaining corner lies inside it; otherwise emitted and corner g+1 removed, g staying put;
+//   * a polygon that cannot be clipped any further in `remaining` tries is abandoned; whatever is
+//     left is emitted only when exactly three corners remain.
+void ear_clip(const std::vector<Corner> & face, const std::vector<Vector3> & positions, std::vector<Corner> & triangles) {
+	const size_t corners = face.size();
+	if (corners < 3) return;
+	if (corners == 3) { triangles.insert(triangles.end(), face.begin(), face.end()); return; }
+
+	int axis_u = 1, axis_v = 2;
+	for (size_t k = 0; k < corners; k++) {
+		const Vector3 & a = positions[face[k].v], & b = positions[face[(k + 1) % corners].v], & c = positions[face[(k + 2) % corners].v];
+		const float e0[3] = { b.x - a.x, b.y - a.y, b.z - a.z };
+		const float e1[3] = { c.x - b.x, c.y - b.y, c.z - b.z };
+		const float cx = fabsf(e0[1] * e1[2] - e0[2] * e1[1]);
+		const float cy = fabsf(e0[2] * e1[0] - e0[0] * e1[2]);
+		const float cz = fabsf(e0[0] * e1[1] - e0[1] * e1[0]);
+		const float eps = std::numeric_limits<float>::epsilon();
+		if (cx > eps || cy > eps || cz > eps) {
+			if (!(cx > cy && cx > cz)) {
+				axis_u = 0;
+				if (cz > cx && cz > cy) axis_v = 1;
+			}
+			break;
+		}
+	}
+
+	float area = 0.0f;
+	for (size_t k = 0; k < corners; k++) {
+		const Vector3 & a = positions[face[k].v], & b = positions[face[(k + 1) % corners].v];
+		area += (a[axis_u] * b[axis_v] - a[axis_v] * b[axis_u]) * 0.5f;
+	}
+
+	std::vector<Corner> left = face;
+	size_t guess = 0, tries = corners, previous = corners;
+	while (left.size() > 3 && tries > 0) {
+		const size_t n = left.size();
+		if (guess >= n) guess -= n;
+		if (previous != n) { previous = n; tries = n; } else tries--;
+
+		Corner ear[3]; float tx[3], ty[3];
+		for (int k = 0; k < 3; k++) {
+			ear[k] = left[(guess + k) % n];
+			tx[k] = positions[ear[k].v][axis_u]; ty[k] = positions[ear[k].v][axis_v];
+		}
+		const float turn = (tx[1] - tx[0]) * (ty[2] - ty[1]) - (ty[1] - ty[0]) * (tx[2] - tx[1]);
+		if (turn * area < 0.0f) { guess++; continue; }
+
+		bool blocked = false;
+		for (size_t other = 3; other < n && !blocked; other++) {
+			const Vector3 & p = positions[left[(guess + other) % n].v];
+			blocked = inside_triangle(tx, ty, p[axis_u], p[axis_v]);
+		}
+		if (blocked) { guess++; continue; }
+
+		triangles.insert(triangles.end(), ear, ear + 3);
+		left.erase(left.begin() + (guess + 1) % n);
+	}
+	if (left.size() == 3) triangles.insert(triangles.end(), left.begin(), left.end());
+}
+}
+
+// Triangle soup from a Wavefront OBJ, polygons ear-clipped like tinyobjloader does (above). Needs
+// `vn` (the reference indexes normals unconditionally, OBJLoader.cpp:143-145); `vt` is optional and
+// V is flipped to 1 - v (OBJLoader.cpp:139-141).
 void Scene::load_obj(const std::string & obj_path, std::vector<TriangleHot> & hot, std::vector<TriangleCold> & cold, std::vector<Vector3> & vertices, const std::vector<std::string> & material_names) {
 	std::ifstream in(obj_path);
 	if (!in) throw std::runtime_error("Failed to load obj file " + obj_path);
@@ -155,7 +239,6 @@ void Scene::load_obj(const std::string & obj_path, std::vector<TriangleHot> & ho
 	std::vector<float> texcoords;
 	int material_id = 0;
 
-	struct Corner { int v, t, n; };
 	std::string line;
 	while (std::getline(in, line)) {
 		std::istringstream ss(line);
@@ -187,9 +270,11 @@ void Scene::load_obj(const std::string & obj_path, std::vector<TriangleHot> & ho
 				c.v = fix(c.v, positions.size()); c.t = fix(c.t, texcoords.size() / 2); c.n = fix(c.n, normals.size());
 				corners.push_back(c);
 			}
-			for (size_t k = 1; k + 1 < corners.size(); k++) {
-				const Corner c[3] = { corners[0], corners[k], corners[k + 1] };
-				for (int i = 0; i < 3; i++) if (c[i].v < 0 || c[i].v >= int(positions.size()) || c[i].n < 0 || c[i].n >= int(normals.size())) throw std::runtime_error("OBJ face needs valid v and vn indices: " + obj_path);
+			for (const Corner & c : corners) if (c.v < 0 || c.v >= int(positions.size()) || c.n < 0 || c.n >= int(normals.size())) throw std::runtime_error("OBJ face needs valid v and vn indices: " + obj_path);
+			std::vector<Corner> triangles;
+			ear_clip(corners, positions, triangles);
+			for (size_t k = 0; k + 2 < triangles.size(); k += 3) {
+				const Corner c[3] = { triangles[k], triangles[k + 1], triangles[k + 2] };
 
 				TriangleHot  h;
 				TriangleCold t;

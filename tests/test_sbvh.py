@@ -74,3 +74,40 @@ def test_sbvh_does_not_depend_on_thread_count():
     assert len(np.unique(a_idx)) == n
     leaves = a_nodes[(a_nodes["count"] & 0x3FFFFFFF) > 0]
     assert ((leaves["left_or_first"] >= 0) & (leaves["left_or_first"] + leaves["count"] <= len(a_idx))).all()
+
+
+def _split_cache(blob):
+    n = int(blob[:4].view("<i4")[0])
+    o = 4
+    triangles = blob[o:o + n * 100]; o += n * 100          # TriangleHot[n] (36 B) then TriangleCold[n] (64 B)
+    nn = int(blob[o:o + 4].view("<i4")[0]); o += 4
+    nodes = blob[o:o + nn * 32].view(NODE); o += nn * 32
+    ni = int(blob[o:o + 4].view("<i4")[0]); o += 4
+    return n, triangles, nodes, blob[o:o + ni * 4].view("<i4")
+
+
+def test_polygon_faces_are_triangulated_like_the_reference(reference, tmp_path):
+    """An OBJ of polygon faces only (convex, concave, clockwise, tilted, collinear leading corners,
+    skew, relative indices) through the host loader: the `<obj>.bvh` it writes holds the triangles —
+    order, corner rotation, normals, texture coordinates — and the SBVH of the reference's own
+    loader + builder (tinyobjloader's ear clipping, OBJLoader.cpp:97-175)."""
+    from b200rt import scenes
+    from b200rt.host import HostScene
+    obj = tmp_path / "polygons.obj"
+    obj.write_bytes(reference["polygons_obj"].tobytes())
+    sky = scenes.write_sky(str(tmp_path / "sky.float"), 16)
+    s = scenes.SceneWriter(64, 64)
+    s.camera((0.0, 1.0, -4.0))
+    s.sky(sky)
+    s.mesh(str(obj))
+    s.point_light((10.0, 10.0, 10.0), (0.0, 5.0, -3.0))
+    HostScene(s.write(str(tmp_path / "polygons.scene")))
+
+    count, triangles, nodes, indices = _split_cache(np.fromfile(str(obj) + ".bvh", dtype=np.uint8))
+    ref_count, ref_triangles, ref_nodes, ref_indices = _split_cache(reference["polygons_cache"])
+    assert count == ref_count and count > 700
+    assert triangles.tobytes() == ref_triangles.tobytes()
+    assert np.array_equal(indices, ref_indices)
+    live = reachable(ref_nodes)
+    assert len(nodes) == len(ref_nodes) and np.array_equal(live, reachable(nodes))
+    assert nodes[live].tobytes() == ref_nodes[live].tobytes()
