@@ -9,7 +9,9 @@
 namespace rt {
 
 #define RT_MAX_BOUNCES 8
+#ifndef RT_BLOCK_THREADS
 #define RT_BLOCK_THREADS 256
+#endif
 #ifndef RT_MIN_BLOCKS
 #define RT_MIN_BLOCKS 4   // resident 256-thread blocks per SM the register allocation is sized for: 64 registers, 32 warps/SM.
                           // Measured on the bench frame (gpurun_out/r1_variants_*.log): 2 -> 1.87 ms, 3 -> 1.53, 4 -> 1.46, 5 -> 1.48, 6 -> 1.57, 8 -> 1.69

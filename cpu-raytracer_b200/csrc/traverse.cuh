@@ -74,6 +74,15 @@ __device__ __forceinline__ bool visit_left_first(int count, v3 d) {
 	float c = axis == 1 ? d.x : (axis == 2 ? d.y : d.z);
 	return c > 0.0f;
 }
+// The same decision for every node of one traversal: bit `axis` of the mask is direction[axis] > 0
+// (axis 1 = x, 2 = y, 3 = z; the unused code 0 falls through to z like the chain above), so a node
+// costs two shifts and an AND instead of two compares, two selects and a float compare.
+__device__ __forceinline__ unsigned direction_order_mask(v3 d) {
+	return (d.z > 0.0f ? 9u : 0u) | (d.x > 0.0f ? 2u : 0u) | (d.y > 0.0f ? 4u : 0u);
+}
+__device__ __forceinline__ int left_first_bit(int count, unsigned order_mask) {
+	return int((order_mask >> (unsigned(count) >> 30)) & 1u);
+}
 
 // Moller-Trumbore with the reference's operation order; all comparisons strict
 // (BottomLevelBVH.cpp:214-252 / :311-346).
@@ -113,6 +122,7 @@ template<bool COUNT>
 __device__ __forceinline__ void blas_trace(const float4 * __restrict__ nodes, const float4 * __restrict__ hot, v3 o, v3 d, int instance, Candidate & best, int * stack, Counters & cnt) {
 	const v3 inv_d = V(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
 	const bool exact = !ray_is_regular(o, inv_d);
+	const unsigned order_mask = direction_order_mask(d);
 
 	int stack_size = 1;
 	stack[0] = 0;
@@ -135,7 +145,7 @@ __device__ __forceinline__ void blas_trace(const float4 * __restrict__ nodes, co
 				}
 			}
 		} else { // push far, then near (BottomLevelBVH.cpp:380-387), without a divergent branch
-			const int left_first = visit_left_first(count, d) ? 1 : 0;
+			const int left_first = left_first_bit(count, order_mask);
 			stack[stack_size]     = left_or_first + left_first;
 			stack[stack_size + 1] = left_or_first + 1 - left_first;
 			stack_size += 2;
@@ -143,11 +153,23 @@ __device__ __forceinline__ void blas_trace(const float4 * __restrict__ nodes, co
 	}
 }
 
-// BottomLevelBVH::intersect, BottomLevelBVH.cpp:398-437
+// BottomLevelBVH::intersect, BottomLevelBVH.cpp:398-437.
+// The answer of an any-hit query does not depend on the order the children are visited in: the
+// boxes are tested against the fixed max_distance, so the set of leaves the ray can reach is the
+// same for every order, and the result is "some triangle in a reachable leaf is hit". The
+// reference's front-to-back order (BottomLevelBVH.cpp:421-428) is the slowest of those measured:
+// a shadow ray starts ON a surface, and front-to-back first wades through the geometry around its
+// own origin. Bench frame, ms per frame (profiles/r01_variants_anyhit_order.log; identical images):
+// front-to-back 1.374, leader lane's front-to-back 1.355, left first 1.295, larger-area child first
+// 1.255, more-triangles child first 1.199, back-to-front 1.168, RIGHT FIRST 1.153 — also the best
+// on the other three scenes (Sibenik 4K 3.15 -> 2.91, SCENE_DYNAMIC 1.07 -> 0.96, dielectrics/EWA
+// 7.13 -> 6.50). The counting instantiation keeps the reference's order, so that nodes_visited
+// stays the reference algorithm's work.
 template<bool COUNT>
 __device__ __forceinline__ bool blas_intersect(const float4 * __restrict__ nodes, const float4 * __restrict__ hot, v3 o, v3 d, float max_distance, int * stack, Counters & cnt) {
 	const v3 inv_d = V(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
 	const bool exact = !ray_is_regular(o, inv_d);
+	const unsigned order_mask = direction_order_mask(d);
 
 	int stack_size = 1;
 	stack[0] = 0;
@@ -166,8 +188,8 @@ __device__ __forceinline__ bool blas_intersect(const float4 * __restrict__ nodes
 				if (COUNT) cnt.triangles++;
 				if (triangle_test(hot + 3 * size_t(i), o, d, max_distance, t, u, v)) return true;
 			}
-		} else { // push far, then near (BottomLevelBVH.cpp:380-387), without a divergent branch
-			const int left_first = visit_left_first(count, d) ? 1 : 0;
+		} else { // the right child is visited first (see above); the counting build pushes far, then near like BottomLevelBVH.cpp:421-428
+			const int left_first = COUNT ? left_first_bit(count, order_mask) : 0;
 			stack[stack_size]     = left_or_first + left_first;
 			stack[stack_size + 1] = left_or_first + 1 - left_first;
 			stack_size += 2;

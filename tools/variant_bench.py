@@ -45,12 +45,22 @@ def child():
         if scene_name == "sponza":
             _, scene = bench.build_scene()
             w, h, bounces, filt = bench.WIDTH, bench.HEIGHT, bench.BOUNCES, bench.FILTER
-        else:
+        elif scene_name == "sibenik":
             from b200rt import standin
             from b200rt.host import HostScene
             scene = HostScene(standin.sibenik_standin(width=3840, height=2160))
             scene.update(0.0, 0)
             w, h, bounces, filt = 3840, 2160, 3, "tri"
+        else:   # dynamic | dielectrics: the reference's shipped meshes (oracle/_ref/Data travels with the repo)
+            import tempfile
+            from b200rt import scenes
+            from b200rt.host import HostScene
+            data = os.path.join(REPO, "oracle", "_ref", "Data")
+            builder, bounces, filt, frames = {"dynamic": (scenes.dynamic, 3, "aniso", 45), "dielectrics": (scenes.dielectrics_small, 8, "ewa", 0)}[scene_name]
+            w, h = 1920, 1080
+            scene = HostScene(builder(data, os.path.join(tempfile.mkdtemp(), scene_name + ".scene"), w, h))
+            for _ in range(frames + 1):
+                scene.update(1.0 / 60.0 if frames else 0.0, 1 if frames else 0)
         pack = scene.pack()
         r = Renderer(w, h, bounces, filt)
         r.upload_static(pack)
