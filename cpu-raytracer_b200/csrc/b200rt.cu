@@ -41,7 +41,8 @@ struct b200rt_ctx {
 	cudaEvent_t   ev[4] = { nullptr, nullptr, nullptr, nullptr }; // total begin, render begin, render end / fxaa begin, fxaa end
 
 	// static scene in HBM
-	DeviceBuffer nodes, hot, cold, materials, textures, texels, sky, gamma;
+	DeviceBuffer nodes, shadow_nodes, hot, cold, materials, textures, texels, sky, gamma;
+	std::vector<int> shadow_node_offset;  // per BLAS: first node of its threaded copy (build_shadow_nodes)
 	int sky_size = 0;
 	bool have_static = false;
 	std::vector<b200rt_blas> blas;
@@ -166,7 +167,7 @@ extern "C" void b200rt_destroy(b200rt_ctx * ctx) {
 	if (!ctx) return;
 	cudaSetDevice(ctx->config.device);
 	if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-	for (DeviceBuffer * b : { &ctx->nodes, &ctx->hot, &ctx->cold, &ctx->materials, &ctx->textures, &ctx->texels, &ctx->sky, &ctx->gamma,
+	for (DeviceBuffer * b : { &ctx->nodes, &ctx->shadow_nodes, &ctx->hot, &ctx->cold, &ctx->materials, &ctx->textures, &ctx->texels, &ctx->sky, &ctx->gamma,
 	                          &ctx->frame_block, &ctx->frame_buffer, &ctx->presented, &ctx->colour_float, &ctx->ids, &ctx->hits, &ctx->counters, &ctx->l2_scratch, &ctx->tile_cost, &ctx->tile_order }) b->release();
 	for (auto & slot : ctx->slots) {
 		slot.frame_buffer.release(); slot.presented.release(); slot.counters.release();
@@ -205,6 +206,76 @@ static int upload(b200rt_ctx * ctx, DeviceBuffer & buffer, const void * host, si
 	CHECK_CUDA(ctx, buffer.ensure(bytes));
 	if (bytes) CHECK_CUDA(ctx, cudaMemcpy(buffer.ptr, host, bytes, cudaMemcpyHostToDevice));
 	return 0;
+}
+
+// Threaded copy of one BLAS for the any-hit (shadow ray) traversal, traverse.cuh: blas_intersect.
+// The answer of an any-hit query does not depend on the order the nodes are visited in, so the
+// order is fixed — right child first, the fastest of those measured — which lets the tree be laid
+// out in exactly that order with a skip link per node: "hit an inner node" is "next record",
+// everything else is "follow the link", and the traversal needs no stack at all.
+//   record = BVHNode's 32 bytes: {min[3], max[3], skip, leaf}; skip = record that follows this
+//   node's subtree (-1 = done); leaf = 0 for an inner node, else (first_triangle << 6) | count with
+//   count in 1..63 — a larger leaf becomes a chain of records with the same box.
+// Unreachable records of the reference's array (node 1, reserved pairs) are dropped.
+static const char * build_shadow_nodes(const b200rt_bvh_node * nodes, int node_count, std::vector<b200rt_bvh_node> & out) {
+	const size_t base = out.size();
+	std::vector<int> order;            // node ids in layout order: preorder, right child first
+	{
+		std::vector<int> dfs(1, 0);
+		while (!dfs.empty()) {
+			const int n = dfs.back(); dfs.pop_back();
+			order.push_back(n);
+			if ((nodes[n].count & 0x3FFFFFFF) == 0) {
+				const int left = nodes[n].left_or_first;
+				if (left <= 0 || left + 1 >= node_count) return "BLAS child index out of bounds";
+				dfs.push_back(left); dfs.push_back(left + 1); // left + 1 is popped first
+			}
+			if (order.size() > size_t(node_count)) return "BLAS nodes do not form a tree";
+		}
+	}
+	std::vector<int> first_record(order.size());
+	std::vector<int> position_of;      // node id -> position in `order`
+	{
+		int max_node = 0;
+		for (int n : order) max_node = std::max(max_node, n);
+		position_of.assign(size_t(max_node) + 1, -1);
+		for (size_t i = 0; i < order.size(); i++) position_of[order[i]] = int(i);
+	}
+	int next = 0;
+	for (size_t i = 0; i < order.size(); i++) {
+		const int count = nodes[order[i]].count & 0x3FFFFFFF;
+		first_record[i] = next;
+		next += count > 0 ? (count + 62) / 63 : 1;
+	}
+	const int total = next;
+	// subtree extent: the layout is a preorder, so a subtree is a contiguous run; its end = the end of its last (left) child
+	std::vector<int> subtree_end(order.size());
+	for (size_t i = order.size(); i-- > 0; ) {
+		const b200rt_bvh_node & n = nodes[order[i]];
+		const int count = n.count & 0x3FFFFFFF;
+		subtree_end[i] = count > 0 ? first_record[i] + (count + 62) / 63 : subtree_end[position_of[n.left_or_first]];
+	}
+	out.resize(base + size_t(total));
+	for (size_t i = 0; i < order.size(); i++) {
+		const b200rt_bvh_node & n = nodes[order[i]];
+		const int count = n.count & 0x3FFFFFFF;
+		const int after = subtree_end[i] == total ? -1 : subtree_end[i];
+		if (count == 0) {
+			b200rt_bvh_node r = n;
+			r.left_or_first = after; r.count = 0;
+			out[base + size_t(first_record[i])] = r;
+		} else {
+			if (n.left_or_first < 0 || n.left_or_first >= (1 << 25)) return "BLAS too large for the shadow-ray layout (2^25 triangles per BLAS)";
+			for (int k = 0, done = 0; done < count; k++, done += 63) {
+				b200rt_bvh_node r = n;
+				const int part = std::min(63, count - done);
+				r.left_or_first = done + part < count ? first_record[i] + k + 1 : after;
+				r.count = ((n.left_or_first + done) << 6) | part;
+				out[base + size_t(first_record[i] + k)] = r;
+			}
+		}
+	}
+	return nullptr;
 }
 
 extern "C" int b200rt_upload_static(b200rt_ctx * ctx, const b200rt_static_scene * s) {
@@ -246,6 +317,16 @@ extern "C" int b200rt_upload_static(b200rt_ctx * ctx, const b200rt_static_scene 
 
 	// BVH nodes: same 32 bytes, viewed as two float4
 	if (upload(ctx, ctx->nodes, s->nodes, size_t(s->node_count) * sizeof(b200rt_bvh_node))) return -1;
+	{ // and the threaded copies the shadow rays walk
+		std::vector<b200rt_bvh_node> threaded;
+		threaded.reserve(size_t(s->node_count));
+		ctx->shadow_node_offset.assign(s->blas_count, 0);
+		for (int b = 0; b < s->blas_count; b++) {
+			ctx->shadow_node_offset[b] = int(threaded.size());
+			if (const char * problem = build_shadow_nodes(s->nodes + s->blas[b].node_offset, s->blas[b].node_count, threaded)) return fail(ctx, problem);
+		}
+		if (upload(ctx, ctx->shadow_nodes, threaded.data(), threaded.size() * sizeof(b200rt_bvh_node))) return -1;
+	}
 
 	{ // TriangleHot 36 B -> 48 B (three aligned float4)
 		std::vector<float> packed(size_t(s->triangle_count) * 12, 0.0f);
@@ -405,7 +486,7 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 		memcpy(&instances[i].inverse, in.inverse, 12 * sizeof(float));
 		memcpy(&instances[i].world,   in.world,   12 * sizeof(float));
 		instances[i].node_offset = blas.node_offset; instances[i].triangle_offset = blas.triangle_offset;
-		instances[i].material_offset = blas.material_offset; instances[i].pad = 0;
+		instances[i].material_offset = blas.material_offset; instances[i].shadow_node_offset = ctx->shadow_node_offset[in.blas];
 		memset(instances[i].reserved, 0, sizeof(instances[i].reserved));
 	}
 	DeviceSphere * spheres = reinterpret_cast<DeviceSphere *>(base + off_spheres);
@@ -435,6 +516,7 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 	const char * dev = static_cast<const char *>(ctx->frame_block.ptr);
 	SceneParams & P = ctx->params;
 	P.nodes = static_cast<const float4 *>(ctx->nodes.ptr);
+	P.shadow_nodes = static_cast<const float4 *>(ctx->shadow_nodes.ptr);
 	P.triangles_hot = static_cast<const float4 *>(ctx->hot.ptr);
 	P.triangles_cold = static_cast<const float4 *>(ctx->cold.ptr);
 	P.materials = static_cast<const DeviceMaterial *>(ctx->materials.ptr);

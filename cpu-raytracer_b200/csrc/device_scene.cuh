@@ -17,7 +17,7 @@ namespace rt {
 struct DeviceInstance {
 	Affine inverse;   // Mesh::transform_inv
 	Affine world;     // Transform::world_matrix
-	int node_offset, triangle_offset, material_offset, pad;
+	int node_offset, triangle_offset, material_offset, shadow_node_offset;
 	int reserved[4];    // keeps the record at 128 bytes (one L2 line)
 };
 static_assert(sizeof(DeviceInstance) == 128, "instance record is 128 bytes");
@@ -43,6 +43,7 @@ struct DeviceLight  { float4 colour_kind; float4 position_inner; float4 negdir_o
 struct SceneParams {
 	// static (uploaded once)
 	const float4 * __restrict__ nodes;          // all BLAS, concatenated
+	const float4 * __restrict__ shadow_nodes;   // the same trees threaded for the any-hit traversal (b200rt.cu: build_shadow_nodes)
 	const float4 * __restrict__ triangles_hot;
 	const float4 * __restrict__ triangles_cold;
 	const DeviceMaterial * __restrict__ materials;

@@ -113,7 +113,7 @@ __device__ __forceinline__ DeviceInstance load_instance_inverse(const DeviceInst
 	DeviceInstance r;
 	r.inverse.r0 = __ldg(p); r.inverse.r1 = __ldg(p + 1); r.inverse.r2 = __ldg(p + 2);
 	const int4 o = __ldg(reinterpret_cast<const int4 *>(p + 6));
-	r.node_offset = o.x; r.triangle_offset = o.y; r.material_offset = o.z; r.pad = 0;
+	r.node_offset = o.x; r.triangle_offset = o.y; r.material_offset = o.z; r.shadow_node_offset = o.w;
 	return r;
 }
 
@@ -194,6 +194,34 @@ __device__ __forceinline__ bool blas_intersect(const float4 * __restrict__ nodes
 			stack[stack_size + 1] = left_or_first + 1 - left_first;
 			stack_size += 2;
 		}
+	}
+	return false;
+}
+
+// The same query on the threaded copy of the tree (b200rt.cu: build_shadow_nodes): records lie in
+// the order they are visited (right child first), so a hit inner node continues with the next
+// record and everything else follows the record's skip link — no stack, no push, no pop.
+__device__ __forceinline__ bool blas_shadow(const float4 * __restrict__ records, const float4 * __restrict__ hot, v3 o, v3 d, float max_distance) {
+	const v3 inv_d = V(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+	const bool exact = !ray_is_regular(o, inv_d);
+
+	int index = 0;
+	while (index >= 0) {
+		const float4 n0 = __ldg(records + 2 * index), n1 = __ldg(records + 2 * index + 1);
+		int next = __float_as_int(n1.z);                       // skip link
+		if (aabb_intersect(n0, n1, o, inv_d, max_distance, exact)) {
+			const int leaf = __float_as_int(n1.w);
+			if (leaf != 0) {
+				const int first = leaf >> 6, count = leaf & 63;
+				for (int i = first; i < first + count; i++) {
+					float t, u, v;
+					if (triangle_test(hot + 3 * size_t(i), o, d, max_distance, t, u, v)) return true;
+				}
+			} else {
+				next = index + 1;
+			}
+		}
+		index = next;
 	}
 	return false;
 }
@@ -322,8 +350,10 @@ __device__ __forceinline__ bool trace_any(const SceneParams & P, v3 o, v3 d, flo
 				const int instance = __ldg(P.tlas_indices + i);
 				const DeviceInstance inst = load_instance_inverse(P.instances + instance);
 				if (COUNT) cnt.instances++;
-				if (blas_intersect<COUNT>(P.nodes + 2 * size_t(inst.node_offset), P.triangles_hot + 3 * size_t(inst.triangle_offset),
-				                          transform_position(inst.inverse, o), transform_direction(inst.inverse, d), max_distance, blas_stack, cnt)) return true;
+				const float4 * hot = P.triangles_hot + 3 * size_t(inst.triangle_offset);
+				const v3 local_o = transform_position(inst.inverse, o), local_d = transform_direction(inst.inverse, d);
+				if (COUNT ? blas_intersect<COUNT>(P.nodes + 2 * size_t(inst.node_offset), hot, local_o, local_d, max_distance, blas_stack, cnt)
+				          : blas_shadow(P.shadow_nodes + 2 * size_t(inst.shadow_node_offset), hot, local_o, local_d, max_distance)) return true;
 			}
 		} else if (visit_left_first(count, d)) {
 			tlas_stack[stack_size++] = left_or_first + 1;

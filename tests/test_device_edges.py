@@ -160,3 +160,33 @@ def test_frame_before_static_scene_is_refused(dynamic):
     with pytest.raises(DeviceError, match="upload_static"):
         r.render(dynamic.pack)
     r.close()
+
+
+def test_leaves_larger_than_a_shadow_record(dynamic):
+    """The shadow rays walk a threaded copy of every BLAS whose leaf records hold at most 63
+    triangles (b200rt.cu: build_shadow_nodes); a larger leaf becomes a chain of records. Collapse
+    two BLAS of the scene into a single root leaf each (514 and 24+ triangles) and compare with
+    the oracle, which walks the reference's own node array."""
+    import oracle_ffi
+    a = {k: v.copy() for k, v in dynamic.pack.a.items()}
+    nodes = a["s_nodes"].view("<i4").reshape(-1, 8)
+    blas = dynamic.pack.blas()                       # node_offset, node_count, triangle_offset, triangle_count, material_offset
+    collapsed = 0
+    for node_offset, node_count, triangle_offset, triangle_count, _ in blas:
+        if triangle_count in sorted(blas[:, 3])[-2:] or triangle_count < 64:
+            nodes[node_offset, 6] = 0                # first triangle
+            nodes[node_offset, 7] = triangle_count   # leaf: every triangle of the BLAS
+            collapsed += 1
+    assert collapsed >= 2 and blas[:, 3].max() > 63
+    from b200rt.pack import ScenePack
+    pack = ScenePack(a)
+    m = dynamic.meta
+    r = _renderer(dynamic)
+    r.upload_static(pack)
+    out = r.render(pack, want_ids=True)
+    r.close()
+    ref = oracle_ffi.render(pack, m["bounces"], m["filter"])
+    assert np.array_equal(out["ids"], ref["ids"])
+    assert out["stats"]["shadow_rays"] == ref["stats"]["shadow_rays"]
+    x, y = unpack_rgb(out["frame_buffer"]), unpack_rgb(ref["frame_buffer"])
+    assert (np.abs(x - y).max(-1) > 0).mean() <= 2e-3 and np.abs(x - y).max() <= 8
