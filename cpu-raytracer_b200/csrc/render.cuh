@@ -108,18 +108,21 @@ __device__ v3 shade_pixel(const SceneParams & P, Ray ray, Counters & cnt) {
 					const int kind = __float_as_int(l0.w);
 					cnt.shadow++;
 
+					// one shadow query for all three kinds (a single inlined copy of the traversal)
+					v3 to_light; float distance_to_light = CUDART_INF_F, distance_to_light_squared = 0.0f;
 					if (kind == 2) { // DirectionalLight.h:9-11
-						const v3 to_light = V(l2);
-						if (trace_any<COUNT>(P, hit.point, to_light, CUDART_INF_F, cnt)) continue;
+						to_light = V(l2);
+					} else {
+						to_light = V(l1) - hit.point;
+						distance_to_light_squared = dot(to_light, to_light);
+						distance_to_light         = sqrtf(distance_to_light_squared);
+						to_light = divf(to_light, distance_to_light);
+					}
+					if (trace_any<COUNT>(P, hit.point, to_light, distance_to_light, cnt)) continue;
+
+					if (kind == 2) {
 						diffuse = diffuse + light_base(V(l0), hit.normal, to_light, to_camera);
 					} else {
-						v3 to_light = V(l1) - hit.point;
-						const float distance_to_light_squared = dot(to_light, to_light);
-						const float distance_to_light         = sqrtf(distance_to_light_squared);
-						to_light = divf(to_light, distance_to_light);
-
-						if (trace_any<COUNT>(P, hit.point, to_light, distance_to_light, cnt)) continue;
-
 						v3 lighting = divf(light_base(V(l0), hit.normal, to_light, to_camera), distance_to_light_squared); // PointLight.h:9-11
 						if (kind == 1) { // SpotLight.h:17-33
 							const float d = dot(to_light, V(l2));
