@@ -420,6 +420,8 @@ def run_gpu_arm(args):
                     ncu = json.load(f)
             except (OSError, ValueError):
                 pass
+            if ncu.get("workload", "sponza1080") != args.workload:
+                ncu = {}   # the capture describes another frame: no traffic / instruction figures for this one
             sm_hz = (clocks.summary()["sm_mhz"] or 1965.0) * 1e6
             issue = None
             if ncu.get("thread_instructions_per_launch"):
