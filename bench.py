@@ -296,7 +296,7 @@ def run_gpu_arm(args):
             raise SystemExit("pipelined frames differ from the synchronous frame")
         h2d = pack.frame_bytes()
         d2h = pixels * 4 + pixels * 3
-        launches = 2 * args.steps
+        launches = 4 * args.steps      # per frame: reset_counters_kernel, render_kernel, fxaa_kernel, tile_schedule_kernel
         kernel_ms = ms_render
         e2e_api = "Scene::update + b200rt_submit_frame/b200rt_wait_frame (two frames in flight)"
     else:
@@ -405,7 +405,7 @@ def run_gpu_arm(args):
         e2e_ms = float(t.item())
         h2d = pack.frame_bytes()
         d2h = (pixels * 4 + pixels * 3) if rank == 0 else 0
-        launches = (2 if rank == 0 else 1) * args.steps
+        launches = (4 if rank == 0 else 3) * args.steps   # reset_counters, render, tile_schedule on every rank (+ fxaa on rank 0); rank 0's count
         e2e_api, e2e_sync_ms = "Scene::update + b200rt_render_frame_device per rank + NVLink gather + b200rt_present_device + D2H on rank 0", None
 
     if rank == 0:

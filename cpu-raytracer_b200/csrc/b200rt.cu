@@ -48,7 +48,10 @@ struct b200rt_ctx {
 	std::vector<b200rt_blas> blas;
 
 	// per-frame data: one pinned staging block + one device block, sub-allocated
-	DeviceBuffer frame_block;
+	DeviceBuffer frame_block[2];          // alternate with the staging halves; uploaded on upload_stream, ahead of the kernels
+	cudaStream_t upload_stream = nullptr;
+	cudaEvent_t consumed[2] = { nullptr, nullptr };                // the last kernel that reads each device block has been issued up to here
+	int block_in_use = 0;
 	void * frame_staging = nullptr; size_t frame_staging_bytes = 0; // two halves, used alternately
 	cudaEvent_t staged[2] = { nullptr, nullptr };                  // the host->device copy out of each half
 	int staging_half = 0;
@@ -65,7 +68,7 @@ struct b200rt_ctx {
 	struct Slot {
 		DeviceBuffer frame_buffer, presented, counters;
 		FrameCounters * pinned_counters = nullptr;
-		cudaEvent_t begin = nullptr, render_begin = nullptr, render_end = nullptr, fxaa_end = nullptr, copied = nullptr;
+		cudaEvent_t render_end = nullptr, fxaa_end = nullptr, copied = nullptr; // ordering only, no timestamps: a timing event costs the stream ~20 us, four of them 7 % of a pipelined frame
 		bool busy = false;
 	} slots[2];
 	cudaStream_t copy_stream = nullptr;
@@ -122,6 +125,8 @@ extern "C" int b200rt_create(const b200rt_config * config, b200rt_ctx ** out) {
 	ctx->stream = ctx->own_stream;
 	for (auto & ev : ctx->ev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) return bail("cudaEventCreate", e);
 	for (auto & ev : ctx->staged) if ((e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+	for (auto & ev : ctx->consumed) if ((e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+	if ((e = cudaStreamCreateWithFlags(&ctx->upload_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
 
 	cudaDeviceProp prop;
 	if ((e = cudaGetDeviceProperties(&prop, config->device)) != cudaSuccess) return bail("cudaGetDeviceProperties", e);
@@ -167,12 +172,14 @@ extern "C" void b200rt_destroy(b200rt_ctx * ctx) {
 	if (!ctx) return;
 	cudaSetDevice(ctx->config.device);
 	if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+	if (ctx->upload_stream) cudaStreamSynchronize(ctx->upload_stream);
+	if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
 	for (DeviceBuffer * b : { &ctx->nodes, &ctx->shadow_nodes, &ctx->hot, &ctx->cold, &ctx->materials, &ctx->textures, &ctx->texels, &ctx->sky, &ctx->gamma,
-	                          &ctx->frame_block, &ctx->frame_buffer, &ctx->presented, &ctx->colour_float, &ctx->ids, &ctx->hits, &ctx->counters, &ctx->l2_scratch, &ctx->tile_cost, &ctx->tile_order }) b->release();
+	                          &ctx->frame_block[0], &ctx->frame_block[1], &ctx->frame_buffer, &ctx->presented, &ctx->colour_float, &ctx->ids, &ctx->hits, &ctx->counters, &ctx->l2_scratch, &ctx->tile_cost, &ctx->tile_order }) b->release();
 	for (auto & slot : ctx->slots) {
 		slot.frame_buffer.release(); slot.presented.release(); slot.counters.release();
 		if (slot.pinned_counters) cudaFreeHost(slot.pinned_counters);
-		for (cudaEvent_t e : { slot.begin, slot.render_begin, slot.render_end, slot.fxaa_end, slot.copied }) if (e) cudaEventDestroy(e);
+		for (cudaEvent_t e : { slot.render_end, slot.fxaa_end, slot.copied }) if (e) cudaEventDestroy(e);
 	}
 	if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
 	if (ctx->frame_staging) cudaFreeHost(ctx->frame_staging);
@@ -180,6 +187,8 @@ extern "C" void b200rt_destroy(b200rt_ctx * ctx) {
 	if (ctx->pinned_counters) cudaFreeHost(ctx->pinned_counters);
 	for (auto & ev : ctx->ev) if (ev) cudaEventDestroy(ev);
 	for (auto & ev : ctx->staged) if (ev) cudaEventDestroy(ev);
+	for (auto & ev : ctx->consumed) if (ev) cudaEventDestroy(ev);
+	if (ctx->upload_stream) cudaStreamDestroy(ctx->upload_stream);
 	if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
 	delete ctx;
 }
@@ -464,7 +473,7 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 		CHECK_CUDA(ctx, cudaMallocHost(&ctx->frame_staging, total * 4));
 		ctx->frame_staging_bytes = total * 2;
 	}
-	CHECK_CUDA(ctx, ctx->frame_block.ensure(total));
+	CHECK_CUDA(ctx, ctx->frame_block[ctx->staging_half].ensure(total));
 
 	// Frames may be issued without waiting for the previous one (b200rt_render_frame_device with
 	// stats == NULL): the two staging halves alternate, and a half is rewritten only after the
@@ -510,10 +519,16 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 		lights[i].negdir_outer   = make_float4(l.negative_direction[0], l.negative_direction[1], l.negative_direction[2], l.outer_cutoff);
 	}
 
-	CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->frame_block.ptr, base, total, cudaMemcpyHostToDevice, ctx->stream));
-	CHECK_CUDA(ctx, cudaEventRecord(ctx->staged[half], ctx->stream));
+	// The block travels on its own stream: when frames are pipelined it is in HBM long before the
+	// previous frame's kernels are done, and the compute stream carries kernels only. The device block
+	// is rewritten only after the kernels of the frame that last read it (two frames ago).
+	CHECK_CUDA(ctx, cudaStreamWaitEvent(ctx->upload_stream, ctx->consumed[half], 0));
+	CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->frame_block[half].ptr, base, total, cudaMemcpyHostToDevice, ctx->upload_stream));
+	CHECK_CUDA(ctx, cudaEventRecord(ctx->staged[half], ctx->upload_stream));
+	CHECK_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->staged[half], 0));
+	ctx->block_in_use = half;
 
-	const char * dev = static_cast<const char *>(ctx->frame_block.ptr);
+	const char * dev = static_cast<const char *>(ctx->frame_block[half].ptr);
 	SceneParams & P = ctx->params;
 	P.nodes = static_cast<const float4 *>(ctx->nodes.ptr);
 	P.shadow_nodes = static_cast<const float4 *>(ctx->shadow_nodes.ptr);
@@ -552,8 +567,7 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 // Launches the render kernel over this context's tiles. frame_buffer is a device pointer.
 static int launch_render(b200rt_ctx * ctx, unsigned * frame_buffer, float * colour_float, bool count, void * counters_dev = nullptr) {
 	if (!counters_dev) counters_dev = ctx->counters.ptr;
-	CHECK_CUDA(ctx, cudaMemsetAsync(counters_dev, 0, sizeof(FrameCounters), ctx->stream));
-	CHECK_CUDA(ctx, cudaMemsetAsync(&static_cast<FrameCounters *>(counters_dev)->first_idle_ns, 0xFF, sizeof(unsigned long long), ctx->stream));
+	reset_counters_kernel<<<1, 32, 0, ctx->stream>>>(static_cast<FrameCounters *>(counters_dev));
 	const unsigned total_warps = unsigned(ctx->params.tile_count_mine) * 32u;
 	if (total_warps == 0) return 0;
 	// persistent grid: every SM filled to the occupancy limit, never more warps than units
@@ -568,6 +582,11 @@ static int launch_render(b200rt_ctx * ctx, unsigned * frame_buffer, float * colo
 }
 
 // After the frame (outside the render kernel's timed events): order the tiles for the next one.
+// Called after the last kernel of a frame has been issued: from here on the frame's device block may be rewritten (stage_frame).
+static int release_frame_block(b200rt_ctx * ctx) {
+	CHECK_CUDA(ctx, cudaEventRecord(ctx->consumed[ctx->block_in_use], ctx->stream));
+	return 0;
+}
 static int launch_schedule(b200rt_ctx * ctx) {
 	if (ctx->params.tile_count_mine == 0) return 0;
 	tile_schedule_kernel<<<1, 1024, 0, ctx->stream>>>(static_cast<unsigned *>(ctx->tile_cost.ptr), static_cast<unsigned *>(ctx->tile_order.ptr), ctx->params.tile_count_mine);
@@ -589,7 +608,7 @@ static void fill_stats(b200rt_ctx * ctx, b200rt_stats * stats) {
 	stats->nodes_visited = c.nodes; stats->triangles_tested = c.triangles; stats->texels_fetched = c.texels;
 	stats->hits_accepted = c.accepted; stats->instances_entered = c.instances;
 	stats->device_ms_render = stats->device_ms_fxaa = stats->device_ms_total = 0.0f;
-	stats->device_ms_tail = c.last_done_ns > c.first_idle_ns ? float(double(c.last_done_ns - c.first_idle_ns) * 1e-6) : 0.0f;
+	stats->device_ms_tail = (c.first_idle_ns != 0 && c.last_done_ns > ~c.first_idle_ns) ? float(double(c.last_done_ns - ~c.first_idle_ns) * 1e-6) : 0.0f;
 	cudaEventElapsedTime(&stats->device_ms_render, ctx->ev[1], ctx->ev[2]);
 	cudaEventElapsedTime(&stats->device_ms_fxaa,   ctx->ev[2], ctx->ev[3]);
 }
@@ -627,6 +646,7 @@ extern "C" int b200rt_render_frame(b200rt_ctx * ctx, const b200rt_frame * frame,
 		primary_hits_kernel<<<grid, RT_BLOCK_THREADS, 0, ctx->stream>>>(ctx->params, out->primary_ids ? static_cast<int *>(ctx->ids.ptr) : nullptr, out->primary_hit ? static_cast<float *>(ctx->hits.ptr) : nullptr);
 		CHECK_CUDA(ctx, cudaGetLastError());
 	}
+	if (release_frame_block(ctx)) return -1;
 
 	// device -> pinned host, then one synchronisation
 	// page-locked caller buffers (b200rt_host_alloc, cudaHostRegister, ...) are written by the DMA
@@ -661,13 +681,15 @@ extern "C" int b200rt_render_frame_device(b200rt_ctx * ctx, const b200rt_frame *
 	if (!ctx) return -1;
 	if (!frame_buffer_dev) return fail(ctx, "null device frame buffer");
 	CHECK_CUDA(ctx, cudaSetDevice(ctx->config.device));
-	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
+	// timing events only for the caller who asks for times: each one stalls the stream for ~20 us
+	if (stats) CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
 	if (stage_frame(ctx, frame)) return -1;
-	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+	if (stats) CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
 	if (launch_render(ctx, reinterpret_cast<unsigned *>(uintptr_t(frame_buffer_dev)), nullptr, false)) return -1;
-	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
+	if (stats) CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
 	if (launch_schedule(ctx)) return -1;
-	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));
+	if (stats) CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));
+	if (release_frame_block(ctx)) return -1;
 	if (!stats) return 0; // asynchronous: the caller orders later work on the context's stream
 	CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->pinned_counters, ctx->counters.ptr, sizeof(FrameCounters), cudaMemcpyDeviceToHost, ctx->stream));
 	CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -679,9 +701,9 @@ extern "C" int b200rt_present_device(b200rt_ctx * ctx, uint64_t frame_buffer_dev
 	if (!ctx) return -1;
 	if (!frame_buffer_dev || !presented_dev) return fail(ctx, "null device pointer");
 	CHECK_CUDA(ctx, cudaSetDevice(ctx->config.device));
-	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
+	if (device_ms) CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
 	if (launch_fxaa(ctx, reinterpret_cast<const unsigned *>(uintptr_t(frame_buffer_dev)), reinterpret_cast<unsigned char *>(uintptr_t(presented_dev)))) return -1;
-	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));
+	if (device_ms) CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));
 	if (!device_ms) return 0; // asynchronous
 	CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 	cudaEventElapsedTime(device_ms, ctx->ev[2], ctx->ev[3]);
@@ -727,8 +749,7 @@ static int ensure_slot(b200rt_ctx * ctx, b200rt_ctx::Slot & slot) {
 	CHECK_CUDA(ctx, slot.counters.ensure(sizeof(FrameCounters)));
 	CHECK_CUDA(ctx, cudaMemset(slot.frame_buffer.ptr, 0, pixels * 4));
 	CHECK_CUDA(ctx, cudaMallocHost(reinterpret_cast<void **>(&slot.pinned_counters), sizeof(FrameCounters)));
-	for (cudaEvent_t * e : { &slot.begin, &slot.render_begin, &slot.render_end, &slot.fxaa_end }) CHECK_CUDA(ctx, cudaEventCreate(e));
-	CHECK_CUDA(ctx, cudaEventCreate(&slot.copied));
+	for (cudaEvent_t * e : { &slot.render_end, &slot.fxaa_end, &slot.copied }) CHECK_CUDA(ctx, cudaEventCreateWithFlags(e, cudaEventDisableTiming));
 	if (!ctx->copy_stream) CHECK_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
 	return 0;
 }
@@ -748,14 +769,13 @@ extern "C" int b200rt_submit_frame(b200rt_ctx * ctx, const b200rt_frame * frame,
 	const size_t pixels = size_t(ctx->config.width) * ctx->config.height;
 	unsigned * fb = static_cast<unsigned *>(slot.frame_buffer.ptr);
 
-	CHECK_CUDA(ctx, cudaEventRecord(slot.begin, ctx->stream));
 	if (stage_frame(ctx, frame)) return -1;
-	CHECK_CUDA(ctx, cudaEventRecord(slot.render_begin, ctx->stream));
 	if (launch_render(ctx, fb, nullptr, ctx->config.count_traversal != 0, slot.counters.ptr)) return -1;
 	CHECK_CUDA(ctx, cudaEventRecord(slot.render_end, ctx->stream));
 	if (out->presented_rgb8 && launch_fxaa(ctx, fb, static_cast<unsigned char *>(slot.presented.ptr))) return -1;
 	if (launch_schedule(ctx)) return -1;
 	CHECK_CUDA(ctx, cudaEventRecord(slot.fxaa_end, ctx->stream));
+	if (release_frame_block(ctx)) return -1;
 
 	// the pre-FXAA image can leave as soon as tracing is done, in parallel with the FXAA kernel
 	CHECK_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, slot.render_end, 0));
@@ -785,10 +805,10 @@ extern "C" int b200rt_wait_frame(b200rt_ctx * ctx, b200rt_stats * stats) {
 		stats->nodes_visited = c.nodes; stats->triangles_tested = c.triangles; stats->texels_fetched = c.texels;
 		stats->hits_accepted = c.accepted; stats->instances_entered = c.instances;
 		stats->device_ms_render = stats->device_ms_fxaa = stats->device_ms_total = 0.0f;
-		stats->device_ms_tail = c.last_done_ns > c.first_idle_ns ? float(double(c.last_done_ns - c.first_idle_ns) * 1e-6) : 0.0f;
-		cudaEventElapsedTime(&stats->device_ms_render, slot.render_begin, slot.render_end);
-		cudaEventElapsedTime(&stats->device_ms_fxaa,   slot.render_end, slot.fxaa_end);
-		cudaEventElapsedTime(&stats->device_ms_total,  slot.begin, slot.copied);
+		stats->device_ms_tail = (c.first_idle_ns != 0 && c.last_done_ns > ~c.first_idle_ns) ? float(double(c.last_done_ns - ~c.first_idle_ns) * 1e-6) : 0.0f;
+		// no timing events on this path: the render kernel stamps its own start and end (globaltimer)
+		if (c.first_start_ns != 0 && c.last_done_ns > ~c.first_start_ns) stats->device_ms_render = float(double(c.last_done_ns - ~c.first_start_ns) * 1e-6);
+		stats->device_ms_total = stats->device_ms_render;
 	}
 	return 0;
 }

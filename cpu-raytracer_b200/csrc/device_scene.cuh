@@ -76,7 +76,8 @@ struct FrameCounters {   // accumulated with one atomicAdd per warp
 	unsigned long long nodes, triangles, texels, accepted, instances;
 	unsigned int next_unit;      // work-stealing cursor (WorkerThread.cpp:53-54)
 	unsigned int pad;
-	unsigned long long first_idle_ns, last_done_ns; // globaltimer when the first / the last warp ran out of work: the tail of the launch
+	unsigned long long first_idle_ns, last_done_ns; // globaltimer when the first (stored as ~t) / the last warp ran out of work: the tail of the launch
+	unsigned long long first_start_ns, pad2;        // globaltimer when the first block started (stored as ~t)
 };
 
 } // namespace rt

@@ -24,6 +24,14 @@ __device__ __forceinline__ bool unit_pixel(const SceneParams & P, unsigned unit,
 	return px < P.width && py < P.height; // edge tiles are clipped, WorkerThread.cpp:60-61
 }
 
+// Clears the frame's counter block. A kernel rather than a memset: memsets are served by a copy
+// engine, and with frames pipelined that engine is busy moving the previous frame's images to the
+// host — the memset, and the render kernel behind it, waited 60 us per frame for it.
+__global__ void reset_counters_kernel(FrameCounters * counters) {
+	unsigned long long * words = reinterpret_cast<unsigned long long *>(counters);
+	for (unsigned i = threadIdx.x; i < sizeof(FrameCounters) / sizeof(unsigned long long); i += blockDim.x) words[i] = 0ull;
+}
+
 // Persistent warps pull units off one device-side counter — the GPU form of the reference's
 // InterlockedDecrement tile countdown (WorkerThread.cpp:53-65).
 template<bool COUNT>
@@ -34,6 +42,12 @@ render_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, float *
 
 	Counters cnt = { 0, 0, 0, 0, 0, 0, 0, 0 };
 	unsigned primary = 0;
+
+	if (threadIdx.x == 0) { // when the launch started: with last_done_ns the kernel times itself, and the pipelined frames need no timing events
+		unsigned long long now;
+		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+		atomicMax(&counters->first_start_ns, ~now);
+	}
 
 	for (;;) {
 		unsigned unit = 0;
@@ -59,7 +73,7 @@ render_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, float *
 	if (lane == 0) { // when did this warp run dry? (min / max over warps = how long the launch ran partly empty)
 		unsigned long long now;
 		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-		atomicMin(&counters->first_idle_ns, now);
+		atomicMax(&counters->first_idle_ns, ~now);   // stored complemented: the earliest time wins an atomicMax, and an all-zero block is the initial state
 		atomicMax(&counters->last_done_ns, now);
 	}
 

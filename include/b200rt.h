@@ -156,9 +156,12 @@ typedef struct {
 	uint64_t texels_fetched;       /* texture texels + sky probe texels                        */
 	uint64_t hits_accepted;        /* closest-hit candidates that replaced the running closest hit */
 	uint64_t instances_entered;    /* Mesh::trace / Mesh::intersect calls (TLAS leaf visits)    */
-	float    device_ms_render;     /* CUDA-event time of the ray tracing kernel(s)           */
-	float    device_ms_fxaa;       /* CUDA-event time of the FXAA kernel                     */
-	float    device_ms_total;      /* uploads + kernels + downloads on the context's stream  */
+	float    device_ms_render;     /* CUDA-event time of the ray tracing kernel(s); from b200rt_wait_frame: the
+	                                * kernel's own %globaltimer stamps (pipelined frames carry no timing
+	                                * events: each one stalls the stream for ~20 us)                      */
+	float    device_ms_fxaa;       /* CUDA-event time of the FXAA kernel (0 from b200rt_wait_frame)       */
+	float    device_ms_total;      /* uploads + kernels + downloads on the context's stream
+	                                * (= device_ms_render from b200rt_wait_frame)                         */
 	float    device_ms_tail;       /* part of device_ms_render during which some warps had already run out of work */
 } b200rt_stats;
 
