@@ -204,7 +204,7 @@ def run_reference_arm(args):
         "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    print(json.dumps(line), file=RESULT, flush=True)
     return 0
 
 
@@ -454,13 +454,26 @@ def run_gpu_arm(args):
             "roofline": roofline,
             "cpu_baseline": baseline,
         }
-        print(json.dumps(line))
+        print(json.dumps(line), file=RESULT, flush=True)
     if world > 1:
         dist.destroy_process_group()
     return 0
 
 
+RESULT = sys.stdout
+
+
+def keep_stdout_for_the_result():
+    """The contract is ONE JSON line on stdout; libraries write there too (NCCL prints its version on
+    the first collective). File descriptor 1 is pointed at stderr and the line goes to a private copy."""
+    global RESULT
+    sys.stdout.flush()
+    RESULT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
 def main():
+    keep_stdout_for_the_result()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
