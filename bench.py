@@ -395,18 +395,70 @@ def run_gpu_arm(args):
         ms_render, ms_fxaa, warm_render, warm_fxaa = ms_step, 0.0, None, None
         kernel_ms = None
 
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            step(True)
-        barrier()
-        t = torch.tensor([(time.perf_counter() - t0) * 1e3 / args.steps], device="cuda")
+        # ---- end to end: the frame loop with host buffers. With peer memory it is pipelined like the
+        # single-GPU loop: two shared images alternate, so rank 0 presents and copies out frame n (on a
+        # second stream) while all ranks already trace frame n+1 into the other image. ------------------
+        e2e_pipelined = peer is not None
+        if e2e_pipelined:
+            peers = [peer, PeerFrame(HEIGHT, WIDTH)]
+            if rank == 0:
+                copy_stream = torch.cuda.Stream()
+                presented2 = [presented, torch.empty_like(presented)]
+                host_fb2 = [host_fb, torch.empty(HEIGHT, WIDTH, dtype=torch.int32).pin_memory()]
+                host_rgb2 = [host_rgb, torch.empty(HEIGHT, WIDTH, 3, dtype=torch.uint8).pin_memory()]
+                fxaa_done = [torch.cuda.Event(), torch.cuda.Event()]
+                copied = [torch.cuda.Event(), torch.cuda.Event()]
+
+            def e2e_loop(n):
+                for i in range(n):
+                    b = i & 1
+                    scene.update(0.0, 0)
+                    frame_pack = pack.with_frame(scene.frame_view())
+                    if rank == 0 and i >= 2:
+                        stream.wait_event(copied[b])         # frame i-2 has left image b
+                    peers[b].barrier()                       # ... and every rank knows it
+                    renderer.render_device(frame_pack, peers[b].root_ptr, wait=False)
+                    peers[b].barrier()                       # all tiles of frame i have landed in rank 0's image b
+                    if rank == 0:
+                        renderer.present_device(peers[b].local.data_ptr(), presented2[b].data_ptr(), wait=False)
+                        fxaa_done[b].record(stream)
+                        copy_stream.wait_event(fxaa_done[b])
+                        with torch.cuda.stream(copy_stream):
+                            host_fb2[b].copy_(peers[b].local, non_blocking=True)
+                            host_rgb2[b].copy_(presented2[b], non_blocking=True)
+                            copied[b].record(copy_stream)
+                        if i >= 1:
+                            copied[(i - 1) & 1].synchronize()  # frame i-1 is in host memory
+                if rank == 0:
+                    copied[(n - 1) & 1].synchronize()
+                torch.cuda.synchronize()
+
+            e2e_loop(max(2, args.warmup))
+            barrier()
+            t0 = time.perf_counter()
+            e2e_loop(args.steps)
+            barrier()
+            elapsed = (time.perf_counter() - t0) * 1e3 / args.steps
+            if rank == 0:   # both images of the pipeline must be the single-GPU frame
+                for b in range(2):
+                    ok = np.array_equal(host_fb2[b].numpy().view(np.uint32), expect["frame_buffer"]) and np.array_equal(host_rgb2[b].numpy(), expect["presented"])
+                    gather_verified = bool(gather_verified and ok)
+            e2e_api = "Scene::update + b200rt_render_frame_device per rank into rank 0's image over NVLink (two images alternate) + b200rt_present_device + D2H on rank 0's copy stream, frame n+1 traced while frame n leaves"
+        else:
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                step(True)
+            barrier()
+            elapsed = (time.perf_counter() - t0) * 1e3 / args.steps
+            e2e_api = "Scene::update + b200rt_render_frame_device per rank + NCCL reduce + b200rt_present_device + D2H on rank 0"
+        t = torch.tensor([elapsed], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item())
         h2d = pack.frame_bytes()
         d2h = (pixels * 4 + pixels * 3) if rank == 0 else 0
         launches = (4 if rank == 0 else 3) * args.steps   # reset_counters, render, tile_schedule on every rank (+ fxaa on rank 0); rank 0's count
-        e2e_api, e2e_sync_ms = "Scene::update + b200rt_render_frame_device per rank + NVLink gather + b200rt_present_device + D2H on rank 0", None
+        e2e_sync_ms = None
 
     if rank == 0:
         peak, peak_source = load_peaks()
