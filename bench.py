@@ -310,69 +310,74 @@ def run_gpu_arm(args):
         host_fb = torch.empty(HEIGHT, WIDTH, dtype=torch.int32).pin_memory()
         host_rgb = torch.empty(HEIGHT, WIDTH, 3, dtype=torch.uint8).pin_memory()
 
-        from b200rt.multigpu import FrameGather, PeerFrame
+        from b200rt.multigpu import HALO, BandFrames, FrameGather, SharedHostImage, band_partition
         gather = FrameGather()
-        peer = None
-        if os.environ.get("B200RT_GATHER", "p2p") == "p2p":
+        bands = None
+        partition = band_partition(HEIGHT, world)
+        if os.environ.get("B200RT_GATHER", "bands") == "bands" and partition is not None:
             try:
-                peer = PeerFrame(HEIGHT, WIDTH)
-                if rank == 0:
-                    fb = peer.local                        # rank 0 presents straight out of the shared image
+                # two sets alternate, so no rank has to be told that the previous frame has been consumed:
+                # frame n+2 is written into the images of frame n only after every rank has passed the
+                # barriers of frame n+1, which it reaches after its own FXAA of frame n (stream order)
+                frames = [BandFrames(HEIGHT, WIDTH, world, rank) for _ in range(2)]
+                shown = [BandFrames(HEIGHT, WIDTH, world, rank, dtype=torch.uint8, channels=3) for _ in range(2)]   # rank 0's copy is the presented image
+                bands = partition
             except Exception as e:                         # no symmetric memory on this box: NCCL reduction instead
                 if rank == 0:
-                    print("PeerFrame unavailable (%s): gathering with an NCCL reduce" % (str(e).splitlines() or ["?"])[0], file=sys.stderr)
-                peer = None
+                    print("peer memory unavailable (%s): gathering with an NCCL reduce" % (str(e).splitlines() or ["?"])[0], file=sys.stderr)
+        if bands is not None:
+            band_rows, ranges = bands
+            y0, y1 = ranges[rank]
 
         phase_events = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
         phase_ms = [0.0, 0.0, 0.0]
+        frame_number = [0]
 
-        def step(e2e, phases=False):
-            if e2e:
-                scene.update(0.0, 0)
-                frame_pack = pack.with_frame(scene.frame_view())
-            else:
-                frame_pack = pack
-            if peer is not None:
+        def step(phases=False):
+            """One frame, everything resident: trace this rank's tiles, exchange, FXAA; the presented image ends on rank 0."""
+            if bands is not None:
+                b = frame_number[0] & 1
+                frame_number[0] += 1
+                renderer.set_band_targets(frames[b].ptrs, band_rows, HALO)
                 if phases: phase_events[0].record(stream)
-                peer.barrier()                             # rank 0 has finished reading the previous frame
+                renderer.render_device(pack, frames[b].ptrs[rank], wait=False)   # every pixel is stored into the image of its band's owner over NVLink
                 if phases: phase_events[1].record(stream)
-                renderer.render_device(frame_pack, peer.root_ptr, wait=False)   # pixels are stored into rank 0's image over NVLink
+                frames[b].barrier()                        # all pixels of the frame have landed
                 if phases: phase_events[2].record(stream)
-                peer.barrier()                             # all tiles have landed
+                renderer.present_rows_device(frames[b].ptrs[rank], shown[b].ptrs[0], y0, y1, wait=False)   # this rank's band, filtered into rank 0's presented image
+                shown[b].barrier()                         # rank 0 holds the whole presented image
                 if phases: phase_events[3].record(stream)
             else:
                 fb.zero_()                                 # every rank: only its own tiles may be non-zero going into the SUM
-                renderer.render_device(frame_pack, fb.data_ptr(), wait=False)
+                renderer.render_device(pack, fb.data_ptr(), wait=False)
                 gather(fb)                                 # tiles are disjoint and the rest is zero: SUM == gather (b200rt/multigpu.py)
-            if rank == 0:
-                renderer.present_device(fb.data_ptr(), presented.data_ptr(), wait=False)
-                if e2e:
-                    host_fb.copy_(fb, non_blocking=True)
-                    host_rgb.copy_(presented, non_blocking=True)
-                    torch.cuda.synchronize()
+                if rank == 0:
+                    renderer.present_device(fb.data_ptr(), presented.data_ptr(), wait=False)
 
-        # the gathered frame must be the single-GPU frame, bit for bit (checked once, untimed)
-        step(False)
-        gather_verified = None
-        if rank == 0:
-            whole = Renderer(WIDTH, HEIGHT, BOUNCES, FILTER, device=local_rank)
-            whole.upload_static(pack)
-            expect = whole.render(pack)
-            whole.close()
-            torch.cuda.synchronize()
-            got_fb, got_rgb = fb.cpu().numpy().view(np.uint32), presented.cpu().numpy()
-            gather_verified = bool(np.array_equal(got_fb, expect["frame_buffer"]) and np.array_equal(got_rgb, expect["presented"]))
-            if not gather_verified:
-                from b200rt.multigpu import TILE, tile_grid
-                bad = got_fb != expect["frame_buffer"]
-                tx, _ = tile_grid(WIDTH, HEIGHT)
-                ys, xs = np.nonzero(bad)
-                owners = ((ys // TILE) * tx + xs // TILE) % world
-                print("gather mismatch: %d frame-buffer pixels (by owning rank: %s), %d presented bytes; zero pixels among them: %d"
-                      % (bad.sum(), np.bincount(owners, minlength=world).tolist(), (got_rgb != expect["presented"]).sum(), (got_fb[bad] == 0).sum()), file=sys.stderr)
+        # the exchanged frame must be the single-GPU frame, bit for bit (checked once, untimed): every rank
+        # checks the band (+ halo) it received, rank 0 the presented image
+        step()
+        torch.cuda.synchronize()
+        whole = Renderer(WIDTH, HEIGHT, BOUNCES, FILTER, device=local_rank)
+        whole.upload_static(pack)
+        expect = whole.render(pack)
+        whole.close()
+        if bands is not None:
+            from b200rt.multigpu import band_rows_needed
+            held = band_rows_needed(HEIGHT, y0, y1)
+            ok = np.array_equal(frames[0].local.cpu().numpy().view(np.uint32)[held], expect["frame_buffer"][held])
+            if rank == 0:
+                ok = ok and np.array_equal(shown[0].local.cpu().numpy(), expect["presented"])
+        else:
+            ok = rank != 0 or (np.array_equal(fb.cpu().numpy().view(np.uint32), expect["frame_buffer"]) and np.array_equal(presented.cpu().numpy(), expect["presented"]))
+        if not ok:
+            print("rank %d: the exchanged frame differs from the single-GPU frame" % rank, file=sys.stderr)
+        verdict = torch.tensor([1 if ok else 0], device="cuda")
+        dist.all_reduce(verdict, op=dist.ReduceOp.MIN)
+        gather_verified = bool(verdict.item())
 
         for _ in range(args.warmup):
-            step(False)
+            step()
         barrier()
         with clocks:
             start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -381,11 +386,11 @@ def run_gpu_arm(args):
                 flush.fill_(1)                              # evict L2, outside the timed region
                 barrier()
                 start.record(stream)
-                step(False, phases=peer is not None)
+                step(phases=bands is not None)
                 end.record(stream)
                 torch.cuda.synchronize()
                 total += start.elapsed_time(end)
-                if peer is not None:
+                if bands is not None:
                     for k in range(3):
                         phase_ms[k] += phase_events[k].elapsed_time(phase_events[k + 1]) / args.steps
         barrier()
@@ -395,42 +400,70 @@ def run_gpu_arm(args):
         ms_render, ms_fxaa, warm_render, warm_fxaa = ms_step, 0.0, None, None
         kernel_ms = None
 
-        # ---- end to end: the frame loop with host buffers. With peer memory it is pipelined like the
-        # single-GPU loop: two shared images alternate, so rank 0 presents and copies out frame n (on a
-        # second stream) while all ranks already trace frame n+1 into the other image. ------------------
-        e2e_pipelined = peer is not None
-        if e2e_pipelined:
-            peers = [peer, PeerFrame(HEIGHT, WIDTH)]
+        # ---- end to end: the frame loop with host buffers, pipelined like the single-GPU loop. Every rank
+        # filters its band and sends it (both images) to the host over its OWN PCIe link, into one frame in
+        # shared page-locked memory; frame n leaves on a second stream while frame n+1 is traced. ----------
+        if bands is not None:
+            tag = "b200rt_%s_" % os.environ.get("MASTER_PORT", "0")
+            def shared(name, shape, dtype):
+                if rank == 0:
+                    try:
+                        image = SharedHostImage(tag + name, shape, dtype, create=True)
+                    except FileExistsError:                  # left behind by a run that died
+                        from multiprocessing import shared_memory
+                        stale = shared_memory.SharedMemory(name=tag + name); stale.close(); stale.unlink()
+                        image = SharedHostImage(tag + name, shape, dtype, create=True)
+                    dist.barrier()
+                else:
+                    dist.barrier()
+                    image = SharedHostImage(tag + name, shape, dtype, create=False)
+                dist.barrier()
+                return image
+            host_fb = [shared("fb%d" % b, (HEIGHT, WIDTH), np.int32) for b in range(2)]
+            host_rgb = [shared("rgb%d" % b, (HEIGHT, WIDTH, 3), np.uint8) for b in range(2)]
+            arrived = shared("arrived", (2, world), np.int64)      # arrived[b][r] = number of the last frame whose band rank r has delivered into images b
             if rank == 0:
-                copy_stream = torch.cuda.Stream()
-                presented2 = [presented, torch.empty_like(presented)]
-                host_fb2 = [host_fb, torch.empty(HEIGHT, WIDTH, dtype=torch.int32).pin_memory()]
-                host_rgb2 = [host_rgb, torch.empty(HEIGHT, WIDTH, 3, dtype=torch.uint8).pin_memory()]
-                fxaa_done = [torch.cuda.Event(), torch.cuda.Event()]
-                copied = [torch.cuda.Event(), torch.cuda.Event()]
+                arrived.array[:] = 0
+            dist.barrier()
+            page_locked = all(h.registered and h.tensor.is_pinned() for h in host_fb + host_rgb + [arrived])
+            presented_local = [torch.empty(HEIGHT, WIDTH, 3, dtype=torch.uint8, device="cuda") for _ in range(2)]
+            sequence = [torch.zeros(1, dtype=torch.int64, device="cuda") for _ in range(2)]
+            copy_stream = torch.cuda.Stream()
+            fxaa_done = [torch.cuda.Event(), torch.cuda.Event()]
+            copied = [torch.cuda.Event(), torch.cuda.Event()]
+            delivered = [0]                                # frames of this loop and the ones before it
 
             def e2e_loop(n):
-                for i in range(n):
+                first = delivered[0]
+                for i in range(first, first + n):
                     b = i & 1
                     scene.update(0.0, 0)
                     frame_pack = pack.with_frame(scene.frame_view())
-                    if rank == 0 and i >= 2:
-                        stream.wait_event(copied[b])         # frame i-2 has left image b
-                    peers[b].barrier()                       # ... and every rank knows it
-                    renderer.render_device(frame_pack, peers[b].root_ptr, wait=False)
-                    peers[b].barrier()                       # all tiles of frame i have landed in rank 0's image b
-                    if rank == 0:
-                        renderer.present_device(peers[b].local.data_ptr(), presented2[b].data_ptr(), wait=False)
-                        fxaa_done[b].record(stream)
-                        copy_stream.wait_event(fxaa_done[b])
-                        with torch.cuda.stream(copy_stream):
-                            host_fb2[b].copy_(peers[b].local, non_blocking=True)
-                            host_rgb2[b].copy_(presented2[b], non_blocking=True)
-                            copied[b].record(copy_stream)
-                        if i >= 1:
-                            copied[(i - 1) & 1].synchronize()  # frame i-1 is in host memory
+                    renderer.set_band_targets(frames[b].ptrs, band_rows, HALO)
+                    renderer.render_device(frame_pack, frames[b].ptrs[rank], wait=False)
+                    if i > first:
+                        stream.wait_event(copied[b ^ 1])     # my band of frame i-1 has left images b^1: beyond this barrier the others may trace frame i+1 into them
+                    frames[b].barrier()
+                    renderer.present_rows_device(frames[b].ptrs[rank], presented_local[b].data_ptr(), y0, y1, wait=False)
+                    fxaa_done[b].record(stream)
+                    copy_stream.wait_event(fxaa_done[b])
+                    with torch.cuda.stream(copy_stream):
+                        host_fb[b].tensor[y0:y1].copy_(frames[b].local[y0:y1], non_blocking=True)
+                        host_rgb[b].tensor[y0:y1].copy_(presented_local[b][y0:y1], non_blocking=True)
+                        sequence[b].fill_(i + 1)
+                        arrived.tensor[b, rank:rank + 1].copy_(sequence[b], non_blocking=True)
+                        copied[b].record(copy_stream)
+                    if i > first:
+                        copied[b ^ 1].synchronize()          # frame i-1: this rank's band is in host memory ...
+                        if rank == 0:                        # ... and the consumer waits for everybody's
+                            while int(arrived.array[b ^ 1].min()) < i:
+                                pass
+                last = (first + n - 1) & 1
+                copied[last].synchronize()
                 if rank == 0:
-                    copied[(n - 1) & 1].synchronize()
+                    while int(arrived.array[last].min()) < first + n:
+                        pass
+                delivered[0] = first + n
                 torch.cuda.synchronize()
 
             e2e_loop(max(2, args.warmup))
@@ -439,25 +472,39 @@ def run_gpu_arm(args):
             e2e_loop(args.steps)
             barrier()
             elapsed = (time.perf_counter() - t0) * 1e3 / args.steps
-            if rank == 0:   # both images of the pipeline must be the single-GPU frame
+            if rank == 0:   # both host frames of the pipeline must be the single-GPU frame
                 for b in range(2):
-                    ok = np.array_equal(host_fb2[b].numpy().view(np.uint32), expect["frame_buffer"]) and np.array_equal(host_rgb2[b].numpy(), expect["presented"])
+                    ok = np.array_equal(host_fb[b].array.view(np.uint32), expect["frame_buffer"]) and np.array_equal(host_rgb[b].array, expect["presented"])
                     gather_verified = bool(gather_verified and ok)
-            e2e_api = "Scene::update + b200rt_render_frame_device per rank into rank 0's image over NVLink (two images alternate) + b200rt_present_device + D2H on rank 0's copy stream, frame n+1 traced while frame n leaves"
+            barrier()
+            for h in host_fb + host_rgb + [arrived]:
+                h.close()
+            e2e_api = ("Scene::update + b200rt_render_frame_device per rank (pixels stored into the band owners' images over NVLink) + b200rt_present_rows_device per rank + "
+                       "D2H of every rank's band over its own PCIe link into one frame in shared %s host memory; frame n+1 traced while frame n leaves" % ("page-locked" if page_locked else "PAGEABLE (cudaHostRegister failed)"))
         else:
+            def step_e2e():
+                scene.update(0.0, 0)
+                fb.zero_()
+                renderer.render_device(pack.with_frame(scene.frame_view()), fb.data_ptr(), wait=False)
+                gather(fb)
+                if rank == 0:
+                    renderer.present_device(fb.data_ptr(), presented.data_ptr(), wait=False)
+                    host_fb.copy_(fb, non_blocking=True)
+                    host_rgb.copy_(presented, non_blocking=True)
+                    torch.cuda.synchronize()
             barrier()
             t0 = time.perf_counter()
             for _ in range(args.steps):
-                step(True)
+                step_e2e()
             barrier()
             elapsed = (time.perf_counter() - t0) * 1e3 / args.steps
             e2e_api = "Scene::update + b200rt_render_frame_device per rank + NCCL reduce + b200rt_present_device + D2H on rank 0"
         t = torch.tensor([elapsed], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item())
-        h2d = pack.frame_bytes()
-        d2h = (pixels * 4 + pixels * 3) if rank == 0 else 0
-        launches = (4 if rank == 0 else 3) * args.steps   # reset_counters, render, tile_schedule on every rank (+ fxaa on rank 0); rank 0's count
+        h2d = pack.frame_bytes() * world                  # every rank uploads the frame block
+        d2h = pixels * 4 + pixels * 3 + (8 * world if bands is not None else 0)   # whole job: the bands add up to both images (+ the arrival stamps)
+        launches = 4 * args.steps                          # per rank and frame: reset_counters, render, tile_schedule, fxaa (the NCCL path runs fxaa on rank 0 only)
         e2e_sync_ms = None
 
     if rank == 0:
@@ -500,8 +547,9 @@ def run_gpu_arm(args):
                     "api": e2e_api, "unpipelined_ms_per_step": e2e_sync_ms},
             "gpu_launches": launches,
             "gather_verified": gather_verified if world > 1 else None,
-            "rank0_phases_ms": None if world == 1 or peer is None else {"barrier_before": phase_ms[0], "upload_and_render": phase_ms[1], "barrier_after": phase_ms[2]},
-            "gather": None if world == 1 else ("render kernel stores into rank 0's image over NVLink peer memory + device barrier" if peer is not None else "NCCL reduce(SUM) of disjoint tiles"),
+            "rank0_phases_ms": None if world == 1 or bands is None else {"upload_and_render": phase_ms[0], "barrier_all_pixels_landed": phase_ms[1], "fxaa_band_into_rank0_and_barrier": phase_ms[2]},
+            "gather": None if world == 1 else ("%d bands of %d rows (+%d halo): render kernel stores each pixel into its band owner's image over NVLink peer memory, device barrier, every rank filters its band"
+                                              % (world, bands[0], HALO) if bands is not None else "NCCL reduce(SUM) of disjoint tiles"),
             "clocks": clocks.summary(),
             "roofline": roofline,
             "cpu_baseline": baseline,

@@ -74,6 +74,9 @@ struct b200rt_ctx {
 	cudaStream_t copy_stream = nullptr;
 	unsigned submitted = 0, waited = 0;
 
+	uint64_t band_targets[B200RT_MAX_BANDS] = {};   // b200rt_set_band_targets
+	int band_count = 0, band_rows = 0, band_halo = 0;
+
 	SceneParams params;      // last frame's parameters (for b200rt_time_resident)
 	bool have_frame = false;
 	int  num_sms = 0, blocks_per_sm = 0;
@@ -557,6 +560,8 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 	P.tile_stride = c.tile_stride; P.tile_phase = c.tile_phase;
 	const int tiles = P.tiles_x * P.tiles_y;
 	P.tile_count_mine = tiles > c.tile_phase ? (tiles - c.tile_phase + c.tile_stride - 1) / c.tile_stride : 0;
+	for (int b = 0; b < B200RT_MAX_BANDS; b++) P.band_targets[b] = reinterpret_cast<unsigned *>(uintptr_t(ctx->band_targets[b]));
+	P.band_count = ctx->band_count; P.band_rows = ctx->band_rows; P.band_halo = ctx->band_halo;
 	P.tile_order = static_cast<const unsigned *>(ctx->tile_order.ptr);
 	P.tile_cost  = static_cast<unsigned *>(ctx->tile_cost.ptr);
 
@@ -594,10 +599,12 @@ static int launch_schedule(b200rt_ctx * ctx) {
 	return 0;
 }
 
-static int launch_fxaa(b200rt_ctx * ctx, const unsigned * frame_buffer, unsigned char * presented) {
+static int launch_fxaa(b200rt_ctx * ctx, const unsigned * frame_buffer, unsigned char * presented, int row_begin = 0, int row_end = -1) {
+	if (row_end < 0) row_end = ctx->config.height;
+	if (row_end <= row_begin) return 0;
 	const dim3 block(FXAA_TILE_W, FXAA_TILE_H);
-	const dim3 grid((ctx->config.width + FXAA_TILE_W - 1) / FXAA_TILE_W, (ctx->config.height + FXAA_TILE_H - 1) / FXAA_TILE_H);
-	fxaa_kernel<<<grid, block, 0, ctx->stream>>>(frame_buffer, presented, static_cast<const float *>(ctx->gamma.ptr), ctx->config.width, ctx->config.height, ctx->config.enable_fxaa);
+	const dim3 grid((ctx->config.width + FXAA_TILE_W - 1) / FXAA_TILE_W, (row_end - row_begin + FXAA_TILE_H - 1) / FXAA_TILE_H);
+	fxaa_kernel<<<grid, block, 0, ctx->stream>>>(frame_buffer, presented, static_cast<const float *>(ctx->gamma.ptr), ctx->config.width, ctx->config.height, ctx->config.enable_fxaa, row_begin, row_end);
 	CHECK_CUDA(ctx, cudaGetLastError());
 	return 0;
 }
@@ -707,6 +714,33 @@ extern "C" int b200rt_present_device(b200rt_ctx * ctx, uint64_t frame_buffer_dev
 	if (!device_ms) return 0; // asynchronous
 	CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 	cudaEventElapsedTime(device_ms, ctx->ev[2], ctx->ev[3]);
+	return 0;
+}
+
+extern "C" int b200rt_present_rows_device(b200rt_ctx * ctx, uint64_t frame_buffer_dev, uint64_t presented_dev, int32_t row_begin, int32_t row_end, float * device_ms) {
+	if (!ctx) return -1;
+	if (!frame_buffer_dev || !presented_dev) return fail(ctx, "null device pointer");
+	if (row_begin < 0 || row_end > ctx->config.height || row_begin > row_end) return fail(ctx, "bad row range");
+	CHECK_CUDA(ctx, cudaSetDevice(ctx->config.device));
+	if (device_ms) CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
+	if (launch_fxaa(ctx, reinterpret_cast<const unsigned *>(uintptr_t(frame_buffer_dev)), reinterpret_cast<unsigned char *>(uintptr_t(presented_dev)), row_begin, row_end)) return -1;
+	if (device_ms) CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));
+	if (!device_ms) return 0; // asynchronous
+	CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	cudaEventElapsedTime(device_ms, ctx->ev[2], ctx->ev[3]);
+	return 0;
+}
+
+extern "C" int b200rt_set_band_targets(b200rt_ctx * ctx, const uint64_t * targets, int32_t band_count, int32_t band_rows, int32_t halo_rows) {
+	if (!ctx) return -1;
+	if (band_count == 0) { ctx->band_count = 0; return 0; }
+	if (!targets || band_count < 1 || band_count > B200RT_MAX_BANDS) return fail(ctx, "band_count must be in 0..8");
+	const int height = ctx->config.height;
+	if (halo_rows < 4) return fail(ctx, "halo_rows must be at least 4 (the reach of fragment_fxaa.glsl)");
+	if (band_rows < halo_rows || (band_count - 1) * band_rows >= height || height - (band_count - 1) * band_rows < halo_rows) return fail(ctx, "bands must cover the frame and none may be shorter than halo_rows");
+	for (int b = 0; b < band_count; b++) if (!targets[b]) return fail(ctx, "null band target");
+	for (int b = 0; b < B200RT_MAX_BANDS; b++) ctx->band_targets[b] = b < band_count ? targets[b] : 0;
+	ctx->band_count = band_count; ctx->band_rows = band_rows; ctx->band_halo = halo_rows;
 	return 0;
 }
 

@@ -69,6 +69,10 @@ struct SceneParams {
 	// frame's cost per tile is accumulated for the next frame's order
 	const unsigned * __restrict__ tile_order;
 	unsigned * __restrict__ tile_cost;
+	// multi-GPU exchange fused into the pixel store (b200rt_set_band_targets): band b of the frame
+	// (band_rows rows, the last band takes the rest) belongs to the GPU whose image is band_targets[b]
+	unsigned * band_targets[B200RT_MAX_BANDS];
+	int band_count, band_rows, band_halo;   // band_count 0: one image, the kernel's frame_buffer argument
 };
 
 struct FrameCounters {   // accumulated with one atomicAdd per warp

@@ -24,6 +24,21 @@ __device__ __forceinline__ bool unit_pixel(const SceneParams & P, unsigned unit,
 	return px < P.width && py < P.height; // edge tiles are clipped, WorkerThread.cpp:60-61
 }
 
+// Where a pixel of row py goes when the frame is exchanged in bands (include/b200rt.h:
+// b200rt_set_band_targets): into the image of the GPU that owns the row's band and, within band_halo
+// rows of a band border, into the neighbour's too — cyclically, because the FXAA taps wrap at the
+// frame border (GL_REPEAT, Window.cpp:48-50). Plain stores over NVLink peer memory: the exchange
+// rides on the kernel's last instruction, every link carries 1/N of the frame, nobody gathers.
+__device__ __forceinline__ void store_pixel_banded(const SceneParams & P, size_t p, int py, unsigned value) {
+	const int last = P.band_count - 1;
+	int b = py / P.band_rows;
+	if (b > last) b = last;
+	P.band_targets[b][p] = value;
+	const int begin = b * P.band_rows, end = b == last ? P.height : begin + P.band_rows;
+	if (py - begin < P.band_halo) P.band_targets[b == 0 ? last : b - 1][p] = value;
+	if (end - py <= P.band_halo)  P.band_targets[b == last ? 0 : b + 1][p] = value;
+}
+
 // Clears the frame's counter block. A kernel rather than a memset: memsets are served by a copy
 // engine, and with frames pipelined that engine is busy moving the previous frame's images to the
 // host — the memset, and the render kernel behind it, waited 60 us per frame for it.
@@ -63,7 +78,8 @@ render_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, float *
 			const v3 colour = shade_pixel<COUNT>(P, ray, cnt);
 
 			const size_t p = size_t(px) + size_t(P.width) * py;
-			frame_buffer[p] = plot_colour(colour);
+			if (P.band_count == 0) frame_buffer[p] = plot_colour(colour);
+			else store_pixel_banded(P, p, py, plot_colour(colour));
 			if (colour_float) { colour_float[3 * p] = colour.x; colour_float[3 * p + 1] = colour.y; colour_float[3 * p + 2] = colour.z; }
 		}
 		__syncwarp();
@@ -199,7 +215,7 @@ __device__ __forceinline__ unsigned fxaa_unorm8(float c) {
 }
 
 __global__ void __launch_bounds__(FXAA_TILE_W * FXAA_TILE_H)
-fxaa_kernel(const unsigned * __restrict__ fb, unsigned char * __restrict__ rgb8, const float * __restrict__ gamma_table, int W, int H, int enable_fxaa) {
+fxaa_kernel(const unsigned * __restrict__ fb, unsigned char * __restrict__ rgb8, const float * __restrict__ gamma_table, int W, int H, int enable_fxaa, int row_begin, int row_end) {
 	__shared__ float gamma[256];
 	__shared__ __align__(16) unsigned char staged[FXAA_TILE_H][FXAA_TILE_W * 3];
 
@@ -208,9 +224,9 @@ fxaa_kernel(const unsigned * __restrict__ fb, unsigned char * __restrict__ rgb8,
 	__syncthreads();
 
 	const int px = blockIdx.x * FXAA_TILE_W + threadIdx.x;
-	const int py = blockIdx.y * FXAA_TILE_H + threadIdx.y;
+	const int py = row_begin + blockIdx.y * FXAA_TILE_H + threadIdx.y; // rows [row_begin, row_end): the whole frame, or this GPU's band
 
-	if (px < W && py < H) {
+	if (px < W && py < row_end) {
 		const float cx = float(px) + 0.5f, cy = float(py) + 0.5f;
 		v3 out;
 		if (!enable_fxaa) {
@@ -258,7 +274,7 @@ fxaa_kernel(const unsigned * __restrict__ fb, unsigned char * __restrict__ rgb8,
 
 	// 64 pixels x 3 bytes = 48 aligned 32-bit words per row: coalesced word stores
 	const int row_px0 = blockIdx.x * FXAA_TILE_W;
-	if (py < H && threadIdx.x < 48) {
+	if (py < row_end && threadIdx.x < 48) {
 		const int valid_bytes = min(FXAA_TILE_W, W - row_px0) * 3;
 		const size_t row_base = (size_t(py) * W + row_px0) * 3; // multiple of 4 when W % 4 == 0 or row_px0 * 3 aligned
 		const int b = threadIdx.x * 4;

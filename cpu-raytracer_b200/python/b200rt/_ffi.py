@@ -121,6 +121,8 @@ def device_lib():
         lib.b200rt_render_frame.argtypes = [C.c_void_p, C.POINTER(Frame), C.POINTER(Outputs)]
         lib.b200rt_render_frame_device.argtypes = [C.c_void_p, C.POINTER(Frame), C.c_uint64, C.POINTER(Stats)]
         lib.b200rt_present_device.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_float)]
+        lib.b200rt_set_band_targets.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.c_int32, C.c_int32, C.c_int32]
+        lib.b200rt_present_rows_device.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_int32, C.c_int32, C.POINTER(C.c_float)]
         lib.b200rt_time_resident.argtypes = [C.c_void_p, C.c_int, C.c_uint64, C.POINTER(C.c_float), C.POINTER(C.c_float)]
         lib.b200rt_download_texels.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64]
         lib.b200rt_submit_frame.argtypes = [C.c_void_p, C.POINTER(Frame), C.POINTER(Outputs)]

@@ -129,6 +129,21 @@ class Renderer:
         self._check(self._lib.b200rt_present_device(self._h, C.c_uint64(frame_buffer_ptr), C.c_uint64(presented_ptr), C.byref(ms)))
         return ms.value
 
+    def set_band_targets(self, targets, band_rows, halo_rows):
+        """Multi-GPU exchange fused into the pixel store (b200rt_set_band_targets): targets[b] = device address, in
+        this process, of the uint32 [H][W] image of the GPU that owns band b. An empty list: single target again."""
+        array = (C.c_uint64 * max(len(targets), 1))(*targets)
+        self._check(self._lib.b200rt_set_band_targets(self._h, array, len(targets), band_rows, halo_rows))
+
+    def present_rows_device(self, frame_buffer_ptr, presented_ptr, row_begin, row_end, wait=True):
+        """FXAA + gamma over rows [row_begin, row_end) of a full-size image (this GPU's band)."""
+        if not wait:
+            self._check(self._lib.b200rt_present_rows_device(self._h, C.c_uint64(frame_buffer_ptr), C.c_uint64(presented_ptr), row_begin, row_end, None))
+            return None
+        ms = C.c_float()
+        self._check(self._lib.b200rt_present_rows_device(self._h, C.c_uint64(frame_buffer_ptr), C.c_uint64(presented_ptr), row_begin, row_end, C.byref(ms)))
+        return ms.value
+
     def time_resident(self, repeat=1, flush_l2_bytes=0):
         """Average device time (ms) of render and FXAA kernels over `repeat` launches on resident inputs."""
         a, b = C.c_float(), C.c_float()

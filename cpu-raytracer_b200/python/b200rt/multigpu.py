@@ -54,24 +54,117 @@ class FrameGather:
         return frame_buffer
 
 
-class PeerFrame:
-    """Rank 0's frame buffer mapped into every rank's address space (NVLink peer memory).
+# ------------------------------------------------------------------------------ bands ---
+# The exchange bench.py uses when peer memory is available. Gathering the frame on rank 0 leaves
+# rank 0 with everything that follows tracing: the FXAA pass over the whole image and both images'
+# trip to the host over ONE PCIe link, while the other GPUs wait. Instead the frame is cut into N
+# horizontal bands; every rank's render kernel stores each pixel straight into the image of the
+# rank that owns the pixel's band (b200rt_set_band_targets: NVLink peer stores, 1/N of the frame
+# per link, plus HALO rows either side of a band so that the FXAA taps find their neighbours), and
+# every rank then filters its own band and sends it to the host over its own PCIe link.
 
-    The render kernel of every rank stores its pixels straight into rank 0's image — the gather is
-    fused into the kernel's final store (4 bytes per pixel over NVLink, 8.3 MB per 1080p frame in
-    total), so there is no zero-fill, no send buffer and no reduction; one device-side barrier tells
-    rank 0 that all tiles have landed. Needs CUDA symmetric memory (torch.distributed._symmetric_memory);
-    FrameGather is the transport-agnostic form of the same exchange.
-    """
+HALO = 4  # rows fragment_fxaa.glsl reaches above / below a pixel: |dir| <= 8 px (:46), taps at +-1/2 of it (:52-57), diagonals < 1 px
 
-    def __init__(self, height, width, group=None):
+
+def band_partition(height, world, multiple=4):
+    """(band_rows, [(row_begin, row_end)] per rank): equal bands, a multiple of the FXAA kernel's 4-row
+    blocks; the last band takes the remainder. None when the frame is too short to give every rank a
+    band of at least HALO rows (then: gather on rank 0)."""
+    rows = -(-height // world)
+    rows = -(-rows // multiple) * multiple
+    if rows < HALO or (world - 1) * rows >= height or height - (world - 1) * rows < HALO:
+        return None
+    return rows, [(r * rows, min(height, (r + 1) * rows)) for r in range(world)]
+
+
+def band_rows_needed(height, begin, end, halo=HALO):
+    """Row indices (cyclic: the taps wrap at the frame border) a rank must hold to filter rows [begin, end)."""
+    return [y % height for y in range(begin - halo, end + halo)]
+
+
+def band_destinations(height, world, y, halo=HALO):
+    """Ranks that receive the pixels of row y — what store_pixel_banded (csrc/kernels.cuh) does."""
+    rows, bands = band_partition(height, world)
+    b = min(y // rows, world - 1)
+    begin, end = bands[b]
+    dst = [b]
+    if y - begin < halo:
+        dst.append((b - 1) % world)
+    if end - y <= halo:
+        dst.append((b + 1) % world)
+    return sorted(set(dst))
+
+
+class BandExchangeGeneric:
+    """The band exchange over any torch.distributed backend (gloo in the CPU tests): every rank ends up
+    with the rows of its band + halo, taken from whichever rank traced them. One all_reduce(SUM) of
+    images that are zero outside the sender's tiles — same trick as FrameGather; the GPU path moves
+    only the rows each rank needs (BandFrames)."""
+
+    def __init__(self, group=None):
+        self.group = group
+
+    def __call__(self, frame_buffer):
+        if dist.is_initialized() and dist.get_world_size(self.group) > 1:
+            dist.all_reduce(frame_buffer, op=dist.ReduceOp.SUM, group=self.group)
+        return frame_buffer
+
+
+class BandFrames:
+    """One full-size pre-FXAA image per rank in CUDA symmetric memory, each mapped into every rank.
+
+    ptrs[r] = rank r's image as seen from this process: the list b200rt_set_band_targets wants. Only
+    the rows of a rank's band (+ halo) are ever written in its image."""
+
+    def __init__(self, height, width, world, rank, group=None, dtype=torch.int32, channels=None):
         import torch.distributed._symmetric_memory as symm_mem
         self.group = group if group is not None else dist.group.WORLD
-        self.local = symm_mem.empty((height, width), dtype=torch.int32, device=torch.device("cuda", torch.cuda.current_device()))
+        shape = (height, width) if channels is None else (height, width, channels)
+        self.local = symm_mem.empty(shape, dtype=dtype, device=torch.device("cuda", torch.cuda.current_device()))
         self.local.zero_()
         self.handle = symm_mem.rendezvous(self.local, self.group)
-        self.root_ptr = int(self.handle.buffer_ptrs[0])   # rank 0's buffer, as seen from this rank
+        self.ptrs = [int(self.handle.buffer_ptrs[r]) for r in range(world)]
+        self.rank = rank
 
     def barrier(self):
         """Device-side barrier of all ranks, enqueued on the current stream."""
         self.handle.barrier()
+
+
+class SharedHostImage:
+    """A host image all ranks of the node write their bands into: POSIX shared memory, page-locked in
+    every process (cudaHostRegister), so each GPU's DMA engine delivers its band over its own PCIe
+    link and the consumer (rank 0) reads one contiguous frame."""
+
+    def __init__(self, name, shape, dtype, create):
+        import numpy as np
+        from multiprocessing import shared_memory
+        nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        self.shm = shared_memory.SharedMemory(name=name, create=create, size=nbytes)
+        self.owner = create
+        if not create:   # Python < 3.13 registers attached segments for clean-up too: only the creator unlinks
+            try:
+                from multiprocessing import resource_tracker
+                resource_tracker.unregister(self.shm._name, "shared_memory")
+            except Exception:
+                pass
+        self.array = np.ndarray(shape, dtype=dtype, buffer=self.shm.buf)
+        self.tensor = torch.from_numpy(self.array)
+        self.registered = False
+        rc = torch.cuda.cudart().cudaHostRegister(self.tensor.data_ptr(), nbytes, 0)
+        self.registered = int(rc) == 0
+
+    def close(self):
+        if self.registered:
+            torch.cuda.cudart().cudaHostUnregister(self.tensor.data_ptr())
+            self.registered = False
+        del self.tensor, self.array
+        try:
+            self.shm.close()
+        except BufferError:     # a view of the image is still alive somewhere: the mapping goes with the process
+            pass
+        if self.owner:
+            try:
+                self.shm.unlink()
+            except FileNotFoundError:
+                pass

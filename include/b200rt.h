@@ -222,6 +222,24 @@ int b200rt_render_frame_device(b200rt_ctx * ctx, const b200rt_frame * frame,
  * multi-GPU gather): in uint32 [height][width], out uint8 [height][width][3].              */
 int b200rt_present_device(b200rt_ctx * ctx, uint64_t frame_buffer_dev, uint64_t presented_dev, float * device_ms);
 
+/* Multi-GPU exchange, fused into the render kernel's pixel store. The reference's
+ * worker threads all write one frame_buffer (Window.h:64) that draw_quad then filters (Main.cpp:59);
+ * across GPUs the frame is cut into band_count horizontal bands of band_rows rows (the last band
+ * takes the remainder), band b belonging to the GPU whose image uint32 [height][width] is mapped at
+ * targets[b] in THIS process (peer memory over NVLink). From the next frame on, b200rt_render_frame_device
+ * stores the pixel of row y into the image of band y / band_rows and, within halo_rows of a band
+ * border, into the neighbouring band's image too (cyclically: the FXAA taps wrap at the frame border),
+ * so that every GPU can run b200rt_present_rows_device over its own band: no GPU gathers the frame,
+ * every NVLink carries 1/N of it. fragment_fxaa.glsl reaches 4 rows; halo_rows >= 4, and no band may
+ * be shorter than halo_rows. band_count = 0 restores the single target (frame_buffer_dev).            */
+#define B200RT_MAX_BANDS 8
+int b200rt_set_band_targets(b200rt_ctx * ctx, const uint64_t * targets, int32_t band_count, int32_t band_rows, int32_t halo_rows);
+
+/* b200rt_present_device over rows [row_begin, row_end) only; frame_buffer_dev and presented_dev are
+ * the bases of full-size images (presented_dev may be another GPU's, mapped here).                   */
+int b200rt_present_rows_device(b200rt_ctx * ctx, uint64_t frame_buffer_dev, uint64_t presented_dev,
+                               int32_t row_begin, int32_t row_end, float * device_ms);
+
 /* Re-times the last frame without host<->device traffic: `repeat` launches of the render
  * (+FXAA) kernels on resident inputs, each timed with CUDA events on the context's stream;
  * returns the average per-frame device times. flush_l2_bytes > 0: before every timed launch
