@@ -299,6 +299,7 @@ def run_gpu_arm(args):
         launches = 4 * args.steps      # per frame: reset_counters_kernel, render_kernel, fxaa_kernel, tile_schedule_kernel
         kernel_ms = ms_render
         e2e_api = "Scene::update + b200rt_submit_frame/b200rt_wait_frame (two frames in flight)"
+        band_d2h_ms = None
     else:
         # ---- N GPUs: each rank traces its interleaved tiles, one collective moves the frame to rank 0,
         # rank 0 runs FXAA. Timed on the device with events on the stream everything is issued on. ------
@@ -405,7 +406,7 @@ def run_gpu_arm(args):
         # shared page-locked memory; frame n leaves on a second stream while frame n+1 is traced. ----------
         if bands is not None:
             tag = "b200rt_%s_" % os.environ.get("MASTER_PORT", "0")
-            def shared(name, shape, dtype):
+            def shared(name, shape, dtype, rows=None):
                 if rank == 0:
                     try:
                         image = SharedHostImage(tag + name, shape, dtype, create=True)
@@ -417,13 +418,16 @@ def run_gpu_arm(args):
                 else:
                     dist.barrier()
                     image = SharedHostImage(tag + name, shape, dtype, create=False)
+                if rows is not None:
+                    image.array[rows[0]:rows[1]] = 0         # first touch: this rank's rows live on this rank's NUMA node
+                elif rank == 0:
+                    image.array[:] = 0
                 dist.barrier()
+                image.register()
                 return image
-            host_fb = [shared("fb%d" % b, (HEIGHT, WIDTH), np.int32) for b in range(2)]
-            host_rgb = [shared("rgb%d" % b, (HEIGHT, WIDTH, 3), np.uint8) for b in range(2)]
+            host_fb = [shared("fb%d" % b, (HEIGHT, WIDTH), np.int32, (y0, y1)) for b in range(2)]
+            host_rgb = [shared("rgb%d" % b, (HEIGHT, WIDTH, 3), np.uint8, (y0, y1)) for b in range(2)]
             arrived = shared("arrived", (2, world), np.int64)      # arrived[b][r] = number of the last frame whose band rank r has delivered into images b
-            if rank == 0:
-                arrived.array[:] = 0
             dist.barrier()
             page_locked = all(h.registered and h.tensor.is_pinned() for h in host_fb + host_rgb + [arrived])
             presented_local = [torch.empty(HEIGHT, WIDTH, 3, dtype=torch.uint8, device="cuda") for _ in range(2)]
@@ -477,6 +481,19 @@ def run_gpu_arm(args):
                     ok = np.array_equal(host_fb[b].array.view(np.uint32), expect["frame_buffer"]) and np.array_equal(host_rgb[b].array, expect["presented"])
                     gather_verified = bool(gather_verified and ok)
             barrier()
+            # how long the band's trip to the host takes on its own, all ranks copying at once (diagnostic, untimed part of the run)
+            copy_events = [torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)]
+            with torch.cuda.stream(copy_stream):
+                copy_events[0].record(copy_stream)
+                for _ in range(10):
+                    host_fb[0].tensor[y0:y1].copy_(frames[0].local[y0:y1], non_blocking=True)
+                    host_rgb[0].tensor[y0:y1].copy_(presented_local[0][y0:y1], non_blocking=True)
+                copy_events[1].record(copy_stream)
+            torch.cuda.synchronize()
+            t = torch.tensor([copy_events[0].elapsed_time(copy_events[1]) / 10], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            band_d2h_ms = float(t.item())
+            barrier()
             for h in host_fb + host_rgb + [arrived]:
                 h.close()
             e2e_api = ("Scene::update + b200rt_render_frame_device per rank (pixels stored into the band owners' images over NVLink) + b200rt_present_rows_device per rank + "
@@ -506,6 +523,8 @@ def run_gpu_arm(args):
         d2h = pixels * 4 + pixels * 3 + (8 * world if bands is not None else 0)   # whole job: the bands add up to both images (+ the arrival stamps)
         launches = 4 * args.steps                          # per rank and frame: reset_counters, render, tile_schedule, fxaa (the NCCL path runs fxaa on rank 0 only)
         e2e_sync_ms = None
+        if bands is None:
+            band_d2h_ms = None
 
     if rank == 0:
         peak, peak_source = load_peaks()
@@ -544,7 +563,7 @@ def run_gpu_arm(args):
             "ms_render_kernel": ms_render, "ms_fxaa_kernel": ms_fxaa,
             "warm_l2": None if warm_render is None else {"ms_render_kernel": warm_render, "ms_fxaa_kernel": warm_fxaa, "value": rays / (warm_render + warm_fxaa) / 1e3},
             "e2e": {"value": rays / e2e_ms / 1e3, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "frames_per_s": 1e3 / e2e_ms,
-                    "api": e2e_api, "unpipelined_ms_per_step": e2e_sync_ms},
+                    "api": e2e_api, "unpipelined_ms_per_step": e2e_sync_ms, "band_d2h_ms_alone": band_d2h_ms},
             "gpu_launches": launches,
             "gather_verified": gather_verified if world > 1 else None,
             "rank0_phases_ms": None if world == 1 or bands is None else {"upload_and_render": phase_ms[0], "barrier_all_pixels_landed": phase_ms[1], "fxaa_band_into_rank0_and_barrier": phase_ms[2]},

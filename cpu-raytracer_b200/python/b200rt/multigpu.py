@@ -150,9 +150,15 @@ class SharedHostImage:
                 pass
         self.array = np.ndarray(shape, dtype=dtype, buffer=self.shm.buf)
         self.tensor = torch.from_numpy(self.array)
+        self.nbytes = nbytes
         self.registered = False
-        rc = torch.cuda.cudart().cudaHostRegister(self.tensor.data_ptr(), nbytes, 0)
+
+    def register(self):
+        """Page-locks the mapping in this process. Call after every rank has written its own rows once:
+        registration faults all pages in, and a page lives on the NUMA node of whoever touches it first."""
+        rc = torch.cuda.cudart().cudaHostRegister(self.tensor.data_ptr(), self.nbytes, 0)
         self.registered = int(rc) == 0
+        return self.registered
 
     def close(self):
         if self.registered:
