@@ -136,6 +136,10 @@ extern "C" int b200rt_create(const b200rt_config * config, b200rt_ctx ** out) {
 	ctx->num_sms = prop.multiProcessorCount;
 	if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->blocks_per_sm, render_kernel<false>, RT_BLOCK_THREADS, 0)) != cudaSuccess) return bail("occupancy query (is this an sm_100a device?)", e);
 	if (ctx->blocks_per_sm < 1) ctx->blocks_per_sm = 1;
+#ifdef RT_CARVEOUT_L1   // variant under test: ask for the whole unified cache as L1 (the kernels use at most 2 KB of shared memory)
+	cudaFuncSetAttribute(render_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 0);
+	cudaFuncSetAttribute(render_kernel<true>,  cudaFuncAttributePreferredSharedMemoryCarveout, 0);
+#endif
 
 	// Texture::init (Texture.h:53-62) and the gamma table of get_screen() (fragment_fxaa.glsl:16-18)
 	float ewa[128];

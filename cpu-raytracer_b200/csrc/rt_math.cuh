@@ -19,6 +19,29 @@ namespace rt {
 
 struct v3 { float x, y, z; };
 
+// Loads of the two read-only streams a ray pulls through L1: BVH nodes + triangles (re-used by the
+// neighbouring rays of the warp and of the SM: worth keeping) and texels (streamed: 190 MB of
+// pyramids against 256 KB of L1). RT_NODE_HINT / RT_TEXEL_HINT select the cache policy of each
+// (tools/variant_bench.py times the combinations): 0 = ld.global.nc as the compiler emits it,
+// 1 = L1::evict_last, 2 = L1::evict_first, 3 = L1::no_allocate.
+#ifndef RT_NODE_HINT
+#define RT_NODE_HINT 0
+#endif
+#ifndef RT_TEXEL_HINT
+#define RT_TEXEL_HINT 0
+#endif
+template<int HINT>
+__device__ __forceinline__ float4 load_hinted(const float4 * p) {
+	if (HINT == 0) return __ldg(p);
+	float4 r;
+	if (HINT == 1)      asm("ld.global.nc.L1::evict_last.v4.f32 {%0, %1, %2, %3}, [%4];"  : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+	else if (HINT == 2) asm("ld.global.nc.L1::evict_first.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+	else                asm("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+	return r;
+}
+__device__ __forceinline__ float4 load_node(const float4 * p)  { return load_hinted<RT_NODE_HINT>(p); }
+__device__ __forceinline__ float4 load_texel(const float4 * p) { return load_hinted<RT_TEXEL_HINT>(p); }
+
 __device__ __forceinline__ v3 V(float x, float y, float z) { v3 r; r.x = x; r.y = y; r.z = z; return r; }
 __device__ __forceinline__ v3 V(float4 a) { return V(a.x, a.y, a.z); }
 __device__ __forceinline__ v3 operator+(v3 a, v3 b) { return V(a.x + b.x, a.y + b.y, a.z + b.z); }

@@ -171,7 +171,7 @@ __device__ __forceinline__ v3 fetch_texel(const TexView & tex, int x, int y, int
 	x = positive_mod(x, level_width);
 	y = positive_mod(y, level_height);
 	if (COUNT) cnt.texels++;
-	return V(__ldg(tex.texels + (__ldg(tex.mip_offsets + level) + x + y * level_width)));
+	return V(load_texel(tex.texels + (__ldg(tex.mip_offsets + level) + x + y * level_width)));
 }
 
 // Texture::sample_bilinear, Texture.cpp:156-186

@@ -87,7 +87,7 @@ __device__ __forceinline__ int left_first_bit(int count, unsigned order_mask) {
 // Moller-Trumbore with the reference's operation order; all comparisons strict
 // (BottomLevelBVH.cpp:214-252 / :311-346).
 __device__ __forceinline__ bool triangle_test(const float4 * __restrict__ tri, v3 o, v3 d, float max_t, float & t_out, float & u_out, float & v_out) {
-	const float4 a0 = __ldg(tri), a1 = __ldg(tri + 1), a2 = __ldg(tri + 2);
+	const float4 a0 = load_node(tri), a1 = load_node(tri + 1), a2 = load_node(tri + 2);
 	const v3 p0 = V(a0.x, a0.y, a0.z), edge_1 = V(a0.w, a1.x, a1.y), edge_2 = V(a1.z, a1.w, a2.x);
 
 	v3    h = cross(d, edge_2);
@@ -129,7 +129,7 @@ __device__ __forceinline__ void blas_trace(const float4 * __restrict__ nodes, co
 
 	while (stack_size > 0) {
 		const int index = stack[--stack_size];
-		const float4 n0 = __ldg(nodes + 2 * index), n1 = __ldg(nodes + 2 * index + 1);
+		const float4 n0 = load_node(nodes + 2 * index), n1 = load_node(nodes + 2 * index + 1);
 		if (COUNT) cnt.nodes++;
 
 		if (!aabb_intersect(n0, n1, o, inv_d, best.t, exact)) continue;
@@ -176,7 +176,7 @@ __device__ __forceinline__ bool blas_intersect(const float4 * __restrict__ nodes
 
 	while (stack_size > 0) {
 		const int index = stack[--stack_size];
-		const float4 n0 = __ldg(nodes + 2 * index), n1 = __ldg(nodes + 2 * index + 1);
+		const float4 n0 = load_node(nodes + 2 * index), n1 = load_node(nodes + 2 * index + 1);
 		if (COUNT) cnt.nodes++;
 
 		if (!aabb_intersect(n0, n1, o, inv_d, max_distance, exact)) continue;
@@ -207,7 +207,7 @@ __device__ __forceinline__ bool blas_shadow(const float4 * __restrict__ records,
 
 	int index = 0;
 	while (index >= 0) {
-		const float4 n0 = __ldg(records + 2 * index), n1 = __ldg(records + 2 * index + 1);
+		const float4 n0 = load_node(records + 2 * index), n1 = load_node(records + 2 * index + 1);
 		int next = __float_as_int(n1.z);                       // skip link
 		if (aabb_intersect(n0, n1, o, inv_d, max_distance, exact)) {
 			const int leaf = __float_as_int(n1.w);
