@@ -311,7 +311,7 @@ def run_gpu_arm(args):
         host_fb = torch.empty(HEIGHT, WIDTH, dtype=torch.int32).pin_memory()
         host_rgb = torch.empty(HEIGHT, WIDTH, 3, dtype=torch.uint8).pin_memory()
 
-        from b200rt.multigpu import HALO, BandFrames, FrameGather, SharedHostImage, band_partition
+        from b200rt.multigpu import HALO, BandFrames, FrameGather, PrivateHostImage, SharedHostImage, band_partition, shared_memory_free_bytes
         gather = FrameGather()
         bands = None
         partition = band_partition(HEIGHT, world)
@@ -406,7 +406,14 @@ def run_gpu_arm(args):
         # shared page-locked memory; frame n leaves on a second stream while frame n+1 is traced. ----------
         if bands is not None:
             tag = "b200rt_%s_" % os.environ.get("MASTER_PORT", "0")
+            # one frame for the whole job in POSIX shared memory — if /dev/shm has room for two of them (a container's
+            # default is 64 MiB); else every rank keeps the band it delivered in page-locked memory of its own
+            room = torch.tensor([shared_memory_free_bytes()], dtype=torch.int64, device="cuda")
+            dist.all_reduce(room, op=dist.ReduceOp.MIN)
+            one_frame = int(room.item()) > 2 * pixels * 7 + (64 << 20) and os.environ.get("B200RT_SHARED_FRAME", "1") != "0"
             def shared(name, shape, dtype, rows=None):
+                if not one_frame:
+                    return PrivateHostImage(shape, dtype)
                 if rank == 0:
                     try:
                         image = SharedHostImage(tag + name, shape, dtype, create=True)
@@ -428,6 +435,7 @@ def run_gpu_arm(args):
             host_fb = [shared("fb%d" % b, (HEIGHT, WIDTH), np.int32, (y0, y1)) for b in range(2)]
             host_rgb = [shared("rgb%d" % b, (HEIGHT, WIDTH, 3), np.uint8, (y0, y1)) for b in range(2)]
             arrived = shared("arrived", (2, world), np.int64)      # arrived[b][r] = number of the last frame whose band rank r has delivered into images b
+            arrived.array[:] = 0
             dist.barrier()
             page_locked = all(h.registered and h.tensor.is_pinned() for h in host_fb + host_rgb + [arrived])
             presented_local = [torch.empty(HEIGHT, WIDTH, 3, dtype=torch.uint8, device="cuda") for _ in range(2)]
@@ -459,12 +467,12 @@ def run_gpu_arm(args):
                         copied[b].record(copy_stream)
                     if i > first:
                         copied[b ^ 1].synchronize()          # frame i-1: this rank's band is in host memory ...
-                        if rank == 0:                        # ... and the consumer waits for everybody's
+                        if rank == 0 and one_frame:          # ... and the consumer waits for everybody's
                             while int(arrived.array[b ^ 1].min()) < i:
                                 pass
                 last = (first + n - 1) & 1
                 copied[last].synchronize()
-                if rank == 0:
+                if rank == 0 and one_frame:
                     while int(arrived.array[last].min()) < first + n:
                         pass
                 delivered[0] = first + n
@@ -476,10 +484,13 @@ def run_gpu_arm(args):
             e2e_loop(args.steps)
             barrier()
             elapsed = (time.perf_counter() - t0) * 1e3 / args.steps
-            if rank == 0:   # both host frames of the pipeline must be the single-GPU frame
-                for b in range(2):
-                    ok = np.array_equal(host_fb[b].array.view(np.uint32), expect["frame_buffer"]) and np.array_equal(host_rgb[b].array, expect["presented"])
-                    gather_verified = bool(gather_verified and ok)
+            ok = True       # both host frames of the pipeline must be the single-GPU frame: every rank checks the band it delivered, rank 0 the whole frame
+            for b in range(2):
+                rows = slice(0, HEIGHT) if (rank == 0 and one_frame) else slice(y0, y1)
+                ok = ok and np.array_equal(host_fb[b].array.view(np.uint32)[rows], expect["frame_buffer"][rows]) and np.array_equal(host_rgb[b].array[rows], expect["presented"][rows])
+            verdict = torch.tensor([1 if ok else 0], device="cuda")
+            dist.all_reduce(verdict, op=dist.ReduceOp.MIN)
+            gather_verified = bool(gather_verified and verdict.item())
             barrier()
             # how long the band's trip to the host takes on its own, all ranks copying at once (diagnostic, untimed part of the run)
             copy_events = [torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)]
@@ -497,7 +508,8 @@ def run_gpu_arm(args):
             for h in host_fb + host_rgb + [arrived]:
                 h.close()
             e2e_api = ("Scene::update + b200rt_render_frame_device per rank (pixels stored into the band owners' images over NVLink) + b200rt_present_rows_device per rank + "
-                       "D2H of every rank's band over its own PCIe link into one frame in shared %s host memory; frame n+1 traced while frame n leaves" % ("page-locked" if page_locked else "PAGEABLE (cudaHostRegister failed)"))
+                       "D2H of every rank's band over its own PCIe link into %s %s host memory; frame n+1 traced while frame n leaves"
+                       % ("one frame in shared" if one_frame else "its own (no shared frame: /dev/shm too small, or B200RT_SHARED_FRAME=0)", "page-locked" if page_locked else "PAGEABLE (cudaHostRegister failed)"))
         else:
             def step_e2e():
                 scene.update(0.0, 0)

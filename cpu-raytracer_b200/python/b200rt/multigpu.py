@@ -131,6 +131,32 @@ class BandFrames:
         self.handle.barrier()
 
 
+class PrivateHostImage:
+    """Same face as SharedHostImage, but page-locked memory of this process only: where /dev/shm is too
+    small for the frame, every rank keeps the band it delivered (a distributed frame)."""
+
+    def __init__(self, shape, dtype):
+        import numpy as np
+        self.tensor = torch.empty(tuple(shape), dtype=torch.from_numpy(np.zeros(1, dtype=dtype)).dtype).pin_memory()
+        self.array = self.tensor.numpy()
+        self.registered = True
+
+    def register(self):
+        return True
+
+    def close(self):
+        pass
+
+
+def shared_memory_free_bytes(path="/dev/shm"):
+    import os
+    try:
+        st = os.statvfs(path)
+        return st.f_bavail * st.f_frsize
+    except OSError:
+        return 0
+
+
 class SharedHostImage:
     """A host image all ranks of the node write their bands into: POSIX shared memory, page-locked in
     every process (cudaHostRegister), so each GPU's DMA engine delivers its band over its own PCIe
