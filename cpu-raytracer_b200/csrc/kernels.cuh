@@ -134,7 +134,17 @@ tile_schedule_kernel(unsigned * __restrict__ tile_cost, unsigned * __restrict__ 
 	};
 	for (int t = threadIdx.x; t < tile_count; t += blockDim.x) atomicAdd(&histogram[cost_class(tile_cost[t])], 1u);
 	__syncthreads();
-	if (threadIdx.x == 0) { unsigned sum = 0; for (int i = 0; i < 256; i++) { offset[i] = sum; sum += histogram[i]; } }
+	if (threadIdx.x < 32) { // exclusive prefix sum of the 256 classes by one warp: 8 classes per lane, then a shuffle scan over the lanes
+		unsigned local[8], sum = 0;
+#pragma unroll
+		for (int k = 0; k < 8; k++) { local[k] = sum; sum += histogram[threadIdx.x * 8 + k]; }
+		unsigned before = sum;
+#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) { const unsigned v = __shfl_up_sync(0xffffffffu, before, o); if (int(threadIdx.x) >= o) before += v; }
+		before -= sum;
+#pragma unroll
+		for (int k = 0; k < 8; k++) offset[threadIdx.x * 8 + k] = before + local[k];
+	}
 	__syncthreads();
 	for (int t = threadIdx.x; t < tile_count; t += blockDim.x) tile_order[atomicAdd(&offset[cost_class(tile_cost[t])], 1u)] = unsigned(t);
 	__syncthreads();
@@ -202,8 +212,11 @@ texture_mip_kernel(const float4 * __restrict__ previous, float4 * __restrict__ o
 #define FXAA_TILE_H 4
 
 __device__ __forceinline__ v3 fxaa_screen(const unsigned * __restrict__ fb, const float * gamma, int W, int H, float fx, float fy) {
-	const int x = positive_mod(int(floorf(fx)), W);
-	const int y = positive_mod(int(floorf(fy)), H);
+	// GL_REPEAT. The taps reach a few pixels beyond the frame at most: the integer division of positive_mod
+	// (~20 instructions, 18 of them per pixel) is only paid by the pixels that do wrap
+	int x = int(floorf(fx)), y = int(floorf(fy));
+	if (x < 0 || x >= W) x = positive_mod(x, W);
+	if (y < 0 || y >= H) y = positive_mod(y, H);
 	const unsigned c = __ldg(fb + size_t(x) + size_t(W) * y);
 	return V(gamma[(c >> 16) & 255], gamma[(c >> 8) & 255], gamma[c & 255]);
 }
