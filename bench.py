@@ -9,8 +9,10 @@ refraction recursion, texture filtering) + the FXAA pass. Prints ONE JSON line o
 
   value   whole-job Mrays/s with every input resident in HBM (kernels only, CUDA events on the
           launching stream, L2 flushed between steps), rays = active rays of the frame
-  e2e     the same metric through the public per-frame call b200rt_render_frame: host Scene::update,
-          pinned-host -> device copy of the frame data, kernels, device -> host read of both images
+  e2e     the same metric through the public per-frame calls (b200rt_submit_frame / b200rt_wait_frame; on N
+          GPUs b200rt_render_frame_device + b200rt_present_rows_device per rank): host Scene::update,
+          pinned-host -> device copy of the frame data, kernels, device -> host read of both images (on N
+          GPUs every rank delivers its row band over its own PCIe link into one frame in shared host memory)
   roofline  render kernel: algorithmic bytes of the frame (DESIGN.md "Algorithmic bytes") / its
           CUDA-event duration, against the measured HBM copy peak (MEASURED_PEAKS.json)
   cpu_baseline  the reference's own AVX renderer (oracle/_ref, SIMD_LANE_SIZE 8, all host threads)
