@@ -388,6 +388,10 @@ def run_gpu_arm(args):
             for _ in range(args.steps):
                 flush.fill_(1)                              # evict L2, outside the timed region
                 barrier()
+                if bands is not None:
+                    # the ranks' streams line up on a device-side barrier (untimed): the clock of every rank starts at the same
+                    # moment, with the step already queued behind it, instead of whenever its host got out of the host barrier
+                    frames[frame_number[0] & 1].barrier()
                 start.record(stream)
                 step(phases=bands is not None)
                 end.record(stream)
