@@ -1,0 +1,16 @@
+#!/usr/bin/env python3
+"""A few frames of the bench scene through b200rt_render_frame, for ncu captures of single kernels
+(development tool):  python tools/ncu_frame.py && ncu --set full -k regex:fxaa_kernel -s 2 -c 1 -o out python tools/ncu_frame.py"""
+import os, sys
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(REPO, "cpu-raytracer_b200", "python")); sys.path.insert(0, REPO)
+import bench
+from b200rt.device import Renderer
+_, scene = bench.build_scene()
+pack = scene.pack()
+r = Renderer(bench.WIDTH, bench.HEIGHT, bench.BOUNCES, bench.FILTER)
+r.upload_static(pack)
+for _ in range(4):
+    stats = r.render(pack)["stats"]
+print(stats["device_ms_render"], stats["device_ms_fxaa"])
+r.close()
