@@ -316,7 +316,7 @@ def run_gpu_arm(args):
         from b200rt.multigpu import HALO, BandFrames, FrameGather, PrivateHostImage, SharedHostImage, band_partition, shared_memory_free_bytes
         gather = FrameGather()
         bands = None
-        partition = band_partition(HEIGHT, world)
+        partition = band_partition(HEIGHT, world, width=WIDTH)
         if os.environ.get("B200RT_GATHER", "bands") == "bands" and partition is not None:
             try:
                 # two sets alternate, so no rank has to be told that the previous frame has been consumed:

@@ -740,7 +740,9 @@ extern "C" int b200rt_set_band_targets(b200rt_ctx * ctx, const uint64_t * target
 	if (band_count == 0) { ctx->band_count = 0; return 0; }
 	if (!targets || band_count < 1 || band_count > B200RT_MAX_BANDS) return fail(ctx, "band_count must be in 0..8");
 	const int height = ctx->config.height;
-	if (halo_rows < 4) return fail(ctx, "halo_rows must be at least 4 (the reach of fragment_fxaa.glsl)");
+	// the taps reach 4 rows along the edge direction, and the diagonal taps H/W pixels vertically (fragment_fxaa.glsl:25-28)
+	const int reach = std::max(4, int(0.5f + float(height) / float(ctx->config.width)));
+	if (halo_rows < reach) return fail(ctx, "halo_rows is smaller than the reach of fragment_fxaa.glsl (4 rows, more for a frame over 4.5 times as high as wide)");
 	if (band_rows < halo_rows || (band_count - 1) * band_rows >= height || height - (band_count - 1) * band_rows < halo_rows) return fail(ctx, "bands must cover the frame and none may be shorter than halo_rows");
 	for (int b = 0; b < band_count; b++) if (!targets[b]) return fail(ctx, "null band target");
 	for (int b = 0; b < B200RT_MAX_BANDS; b++) ctx->band_targets[b] = b < band_count ? targets[b] : 0;

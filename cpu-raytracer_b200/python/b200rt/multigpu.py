@@ -66,10 +66,20 @@ class FrameGather:
 HALO = 4  # rows fragment_fxaa.glsl reaches above / below a pixel: |dir| <= 8 px (:46), taps at +-1/2 of it (:52-57), diagonals < 1 px
 
 
-def band_partition(height, world, multiple=4):
+def fxaa_reach(width, height):
+    """Rows the shader reaches above / below a pixel: 4 along the edge direction, and the diagonal taps'
+    vertical offset, which is H/W pixels (the shader adds inv_screen_size.x to both coordinates,
+    fragment_fxaa.glsl:25-28): more than 4 only for a frame over 4.5 times as high as wide."""
+    return max(HALO, int(0.5 + height / width))
+
+
+def band_partition(height, world, multiple=4, width=None):
     """(band_rows, [(row_begin, row_end)] per rank): equal bands, a multiple of the FXAA kernel's 4-row
     blocks; the last band takes the remainder. None when the frame is too short to give every rank a
-    band of at least HALO rows (then: gather on rank 0)."""
+    band of at least HALO rows, or so narrow that the shader reaches further than HALO rows (then:
+    gather on rank 0)."""
+    if width is not None and fxaa_reach(width, height) > HALO:
+        return None
     rows = -(-height // world)
     rows = -(-rows // multiple) * multiple
     if rows < HALO or (world - 1) * rows >= height or height - (world - 1) * rows < HALO:

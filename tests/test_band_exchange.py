@@ -58,6 +58,14 @@ def test_halo_rows_are_all_the_fxaa_pass_needs(name):
             assert np.array_equal(oracle_ffi.present(mine, enable_fxaa=True)[begin:end], whole[begin:end]), (world, begin)
 
 
+def test_tall_narrow_frames_are_gathered_instead():
+    """The diagonal taps' vertical offset is H/W pixels: beyond 4.5 the shader reaches past HALO rows."""
+    assert multigpu.fxaa_reach(1920, 1080) == multigpu.HALO and multigpu.fxaa_reach(1080, 1920) == multigpu.HALO
+    assert multigpu.fxaa_reach(100, 449) == multigpu.HALO and multigpu.fxaa_reach(100, 450) == 5
+    assert multigpu.band_partition(1080, 2, width=1920) is not None
+    assert multigpu.band_partition(4500, 2, width=1000) is None
+
+
 def test_one_row_less_of_halo_is_not_enough():
     """Pins HALO to the shader's reach: with HALO - 1 rows some band of a real frame comes out different."""
     import oracle_ffi
