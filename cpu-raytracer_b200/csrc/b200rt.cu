@@ -110,6 +110,8 @@ extern "C" int b200rt_create(const b200rt_config * config, b200rt_ctx ** out) {
 	if (config->width <= 0 || config->height <= 0) { g_create_error = "bad resolution"; return -1; }
 	if (config->bounces < 0 || config->bounces > RT_MAX_BOUNCES) { g_create_error = "bounces must be in 0..8"; return -1; }
 	if (config->mipmap_filter < 0 || config->mipmap_filter > 2) { g_create_error = "bad mipmap_filter"; return -1; }
+	if (config->texture_sample_mode < 0 || config->texture_sample_mode > 2) { g_create_error = "bad texture_sample_mode"; return -1; }
+	if (config->traversal_naive < 0 || config->traversal_naive > 1) { g_create_error = "bad traversal_naive"; return -1; }
 	if (config->tile_stride < 1 || config->tile_phase < 0 || config->tile_phase >= config->tile_stride) { g_create_error = "bad tile partition"; return -1; }
 
 	int device_count = 0;
@@ -560,6 +562,7 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 	}
 	const b200rt_config & c = ctx->config;
 	P.width = c.width; P.height = c.height; P.bounces = c.bounces; P.mipmap_filter = c.mipmap_filter; P.max_anisotropy = c.max_anisotropy;
+	P.traversal_naive = c.traversal_naive; P.texture_sample_mode = c.texture_sample_mode;
 	P.tiles_x = (c.width + 31) / 32; P.tiles_y = (c.height + 31) / 32; // Window.cpp:11-12
 	P.tile_stride = c.tile_stride; P.tile_phase = c.tile_phase;
 	const int tiles = P.tiles_x * P.tiles_y;

@@ -64,6 +64,7 @@ struct SceneParams {
 	// configuration (Config.h mirror)
 	int width, height, bounces, mipmap_filter;
 	float max_anisotropy;
+	int traversal_naive, texture_sample_mode;   // BVH_TRAVERSAL_STRATEGY, TEXTURE_SAMPLE_MODE
 	int tiles_x, tiles_y, tile_stride, tile_phase, tile_count_mine;
 	// schedule (kernels.cuh, tile_schedule_kernel): this GPU's tiles in hand-out order, and where this
 	// frame's cost per tile is accumulated for the next frame's order

@@ -346,8 +346,10 @@ __device__ __forceinline__ v3 get_albedo(const SceneParams & P, float4 diffuse_t
 	tex.width = __ldg(&dt->width); tex.height = __ldg(&dt->height); tex.mip_levels = __ldg(&dt->mip_levels);
 	tex.mip_offsets = dt->mip_offsets;
 
-	v3 sample;
-	if (!__ldg(&dt->mipmapped))                           sample = sample_bilinear<COUNT>(tex, hit.u, hit.v, 0, cnt);
+	v3 sample;   // TEXTURE_SAMPLE_MODE (Config.h), then MIPMAP_FILTER
+	if (P.texture_sample_mode == B200RT_TEXTURE_NEAREST)  // Texture::sample_nearest, Texture.cpp:149-154
+		sample = fetch_texel<COUNT>(tex, float_to_int(hit.u * float(tex.width)), float_to_int(hit.v * float(tex.height)), 0, cnt);
+	else if (P.texture_sample_mode == B200RT_TEXTURE_BILINEAR || !__ldg(&dt->mipmapped)) sample = sample_bilinear<COUNT>(tex, hit.u, hit.v, 0, cnt);
 	else if (P.mipmap_filter == B200RT_FILTER_TRILINEAR)  sample = sample_trilinear<COUNT>(tex, hit.u, hit.v, hit.ds_dx, hit.ds_dy, hit.dt_dx, hit.dt_dy, cnt);
 	else if (P.mipmap_filter == B200RT_FILTER_EWA)        sample = sample_ewa<COUNT>(tex, P.max_anisotropy, hit.u, hit.v, hit.ds_dx, hit.ds_dy, hit.dt_dx, hit.dt_dy, cnt);
 	else                                                  sample = sample_anisotropic<COUNT>(tex, P.max_anisotropy, hit.u, hit.v, hit.ds_dx, hit.ds_dy, hit.dt_dx, hit.dt_dy, cnt);

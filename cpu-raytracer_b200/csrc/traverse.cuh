@@ -80,6 +80,10 @@ __device__ __forceinline__ bool visit_left_first(int count, v3 d) {
 __device__ __forceinline__ unsigned direction_order_mask(v3 d) {
 	return (d.z > 0.0f ? 9u : 0u) | (d.x > 0.0f ? 2u : 0u) | (d.y > 0.0f ? 4u : 0u);
 }
+// BVH_TRAVERSE_TREE_NAIVE (BVHNode.h:31-32): the left child first, whatever the ray — every bit of the mask set.
+__device__ __forceinline__ unsigned traversal_order_mask(const SceneParams & P, v3 d) {
+	return P.traversal_naive ? 0xffffffffu : direction_order_mask(d);
+}
 __device__ __forceinline__ int left_first_bit(int count, unsigned order_mask) {
 	return int((order_mask >> (unsigned(count) >> 30)) & 1u);
 }
@@ -119,10 +123,9 @@ __device__ __forceinline__ DeviceInstance load_instance_inverse(const DeviceInst
 
 // BottomLevelBVH::trace, BottomLevelBVH.cpp:355-396 (object-space ray, shared t)
 template<bool COUNT>
-__device__ __forceinline__ void blas_trace(const float4 * __restrict__ nodes, const float4 * __restrict__ hot, v3 o, v3 d, int instance, Candidate & best, int * stack, Counters & cnt) {
+__device__ __forceinline__ void blas_trace(const float4 * __restrict__ nodes, const float4 * __restrict__ hot, v3 o, v3 d, int instance, Candidate & best, int * stack, Counters & cnt, unsigned order_mask) {
 	const v3 inv_d = V(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
 	const bool exact = !ray_is_regular(o, inv_d);
-	const unsigned order_mask = direction_order_mask(d);
 
 	int stack_size = 1;
 	stack[0] = 0;
@@ -166,10 +169,9 @@ __device__ __forceinline__ void blas_trace(const float4 * __restrict__ nodes, co
 // 7.13 -> 6.50). The counting instantiation keeps the reference's order, so that nodes_visited
 // stays the reference algorithm's work.
 template<bool COUNT>
-__device__ __forceinline__ bool blas_intersect(const float4 * __restrict__ nodes, const float4 * __restrict__ hot, v3 o, v3 d, float max_distance, int * stack, Counters & cnt) {
+__device__ __forceinline__ bool blas_intersect(const float4 * __restrict__ nodes, const float4 * __restrict__ hot, v3 o, v3 d, float max_distance, int * stack, Counters & cnt, unsigned order_mask) {
 	const v3 inv_d = V(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
 	const bool exact = !ray_is_regular(o, inv_d);
-	const unsigned order_mask = direction_order_mask(d);
 
 	int stack_size = 1;
 	stack[0] = 0;
@@ -306,10 +308,11 @@ __device__ __forceinline__ void trace_closest(const SceneParams & P, v3 o, v3 d,
 				const DeviceInstance inst = load_instance_inverse(P.instances + instance);
 				if (COUNT) cnt.instances++;
 				// Mesh::trace, Mesh.cpp:17-31 (the differentials are transformed in shade.cuh, for the winner only)
+				const v3 local_d = transform_direction(inst.inverse, d);
 				blas_trace<COUNT>(P.nodes + 2 * size_t(inst.node_offset), P.triangles_hot + 3 * size_t(inst.triangle_offset),
-				                  transform_position(inst.inverse, o), transform_direction(inst.inverse, d), instance, best, blas_stack, cnt);
+				                  transform_position(inst.inverse, o), local_d, instance, best, blas_stack, cnt, traversal_order_mask(P, local_d));
 			}
-		} else if (visit_left_first(count, d)) {
+		} else if (P.traversal_naive || visit_left_first(count, d)) {
 			tlas_stack[stack_size++] = left_or_first + 1;
 			tlas_stack[stack_size++] = left_or_first;
 		} else {
@@ -352,10 +355,10 @@ __device__ __forceinline__ bool trace_any(const SceneParams & P, v3 o, v3 d, flo
 				if (COUNT) cnt.instances++;
 				const float4 * hot = P.triangles_hot + 3 * size_t(inst.triangle_offset);
 				const v3 local_o = transform_position(inst.inverse, o), local_d = transform_direction(inst.inverse, d);
-				if (COUNT ? blas_intersect<COUNT>(P.nodes + 2 * size_t(inst.node_offset), hot, local_o, local_d, max_distance, blas_stack, cnt)
+				if (COUNT ? blas_intersect<COUNT>(P.nodes + 2 * size_t(inst.node_offset), hot, local_o, local_d, max_distance, blas_stack, cnt, traversal_order_mask(P, local_d))
 				          : blas_shadow(P.shadow_nodes + 2 * size_t(inst.shadow_node_offset), hot, local_o, local_d, max_distance)) return true;
 			}
-		} else if (visit_left_first(count, d)) {
+		} else if (P.traversal_naive || visit_left_first(count, d)) {
 			tlas_stack[stack_size++] = left_or_first + 1;
 			tlas_stack[stack_size++] = left_or_first;
 		} else {

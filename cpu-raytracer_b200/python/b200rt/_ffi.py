@@ -8,6 +8,8 @@ REPO_ROOT = os.path.dirname(PKG_ROOT)
 MAX_MIP_LEVELS = 16
 FILTER_TRILINEAR, FILTER_ANISOTROPIC, FILTER_EWA = 0, 1, 2
 FILTERS = {"tri": FILTER_TRILINEAR, "aniso": FILTER_ANISOTROPIC, "ewa": FILTER_EWA}
+TRAVERSALS = {"ordered": 0, "naive": 1}                       # BVH_TRAVERSAL_STRATEGY (Config.h)
+TEXTURE_MODES = {"mipmap": 0, "bilinear": 1, "nearest": 2}    # TEXTURE_SAMPLE_MODE (Config.h)
 
 # sizeof of the POD records (checked against the C side by tests/test_abi.py)
 SIZEOF = dict(bvh_node=32, triangle_hot=36, triangle_cold=64, blas=20, material=48, texture=88,
@@ -48,6 +50,7 @@ class Config(C.Structure):
         ("width", C.c_int32), ("height", C.c_int32), ("bounces", C.c_int32), ("mipmap_filter", C.c_int32),
         ("max_anisotropy", C.c_float), ("enable_fxaa", C.c_int32), ("device", C.c_int32),
         ("tile_stride", C.c_int32), ("tile_phase", C.c_int32), ("count_traversal", C.c_int32),
+        ("traversal_naive", C.c_int32), ("texture_sample_mode", C.c_int32),
     ]
 
 
@@ -71,9 +74,10 @@ class Outputs(C.Structure):
 
 
 def make_config(width, height, bounces, mipmap_filter="aniso", max_anisotropy=8.0, enable_fxaa=True, device=0,
-                tile_stride=1, tile_phase=0, count_traversal=False):
+                tile_stride=1, tile_phase=0, count_traversal=False, traversal="ordered", texture_mode="mipmap"):
     f = FILTERS[mipmap_filter] if isinstance(mipmap_filter, str) else int(mipmap_filter)
-    return Config(width, height, bounces, f, max_anisotropy, 1 if enable_fxaa else 0, device, tile_stride, tile_phase, 1 if count_traversal else 0)
+    return Config(width, height, bounces, f, max_anisotropy, 1 if enable_fxaa else 0, device, tile_stride, tile_phase, 1 if count_traversal else 0,
+                  TRAVERSALS[traversal], TEXTURE_MODES[texture_mode])
 
 
 def _load(path):

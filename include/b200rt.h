@@ -145,7 +145,15 @@ typedef struct {
 	/* 1 = also count BVH nodes visited / triangles tested / texels fetched (b200rt_stats), the
 	 * run-time cousin of BVH_VISUALIZE_HEATMAP (Config.h:23). Costs registers: keep 0 when timing. */
 	int32_t count_traversal;
+	/* BVH_TRAVERSAL_STRATEGY (Config.h:27-30, BVHNode.h:30-40): 0 = BVH_TRAVERSE_TREE_ORDERED, the shipped setting (the
+	 * child on the ray's side of the split plane first), 1 = BVH_TRAVERSE_TREE_NAIVE (always the left child first).    */
+	int32_t traversal_naive;
+	/* TEXTURE_SAMPLE_MODE (Config.h:37-42, Texture.h:33-49): B200RT_TEXTURE_*; 0 = the shipped setting.                 */
+	int32_t texture_sample_mode;
 } b200rt_config;
+enum { B200RT_TEXTURE_MIPMAP = 0,   /* TEXTURE_SAMPLE_MODE_MIPMAP: mipmap_filter on mip-mapped textures, bilinear on the others */
+       B200RT_TEXTURE_BILINEAR = 1, /* TEXTURE_SAMPLE_MODE_BILINEAR: Texture::sample_bilinear on level 0, Texture.cpp:156-186   */
+       B200RT_TEXTURE_NEAREST = 2 };/* TEXTURE_SAMPLE_MODE_NEAREST: Texture::sample_nearest, Texture.cpp:149-154              */
 
 /* Counters of one frame. Rays are ACTIVE rays (one per traced ray), which is what the
  * reference's lane-1 build counts (Raytracer.cpp:61,163,180,192,265,320).                  */

@@ -33,11 +33,12 @@ def lib():
 
 
 def render(pack, bounces, mipmap_filter="aniso", width=None, height=None, enable_fxaa=True, threads=None,
-           want_ids=True, want_float=False, tile_stride=1, tile_phase=0, max_anisotropy=8.0):
+           want_ids=True, want_float=False, tile_stride=1, tile_phase=0, max_anisotropy=8.0,
+           traversal="ordered", texture_mode="mipmap"):
     """Render one frame of a ScenePack with the CPU oracle. Returns a dict of numpy arrays + stats."""
     w = width or pack.width
     h = height or pack.height
-    cfg = _ffi.make_config(w, h, bounces, mipmap_filter, max_anisotropy, enable_fxaa, 0, tile_stride, tile_phase)
+    cfg = _ffi.make_config(w, h, bounces, mipmap_filter, max_anisotropy, enable_fxaa, 0, tile_stride, tile_phase, False, traversal, texture_mode)
     static, frame = pack.static_view(), pack.frame_view()
 
     res = {

@@ -119,7 +119,8 @@ static inline int aabb_intersect(const b200rt_bvh_node * n, v3 o, v3 inv_d, floa
 
 /* BVHNode.h:18-40 */
 static inline int node_count(const b200rt_bvh_node * n) { return n->count & 0x3FFFFFFF; }
-static inline int visit_left_first(const b200rt_bvh_node * n, v3 d) {
+static inline int visit_left_first(const ctx_t * ctx, const b200rt_bvh_node * n, v3 d) {
+	if (ctx->c->traversal_naive) return 1; /* BVH_TRAVERSE_TREE_NAIVE, BVHNode.h:31-32 */
 	switch ((uint32_t)n->count >> 30) {
 		case 1:  return d.x > 0.0f;
 		case 2:  return d.y > 0.0f;
@@ -227,7 +228,7 @@ static void blas_trace(const ctx_t * ctx, const b200rt_blas * blas, const ray_t 
 					hit->triangle_id = i;
 				}
 			}
-		} else if (visit_left_first(node, ray->direction)) {
+		} else if (visit_left_first(ctx, node, ray->direction)) {
 			stack[stack_size++] = node->left_or_first + 1;
 			stack[stack_size++] = node->left_or_first;
 		} else {
@@ -260,7 +261,7 @@ static int blas_intersect(const ctx_t * ctx, const b200rt_blas * blas, v3 origin
 				cnt->triangles++;
 				if (triangle_test(&hot[i], origin, direction, max_distance, &t, &u, &v)) return 1;
 			}
-		} else if (visit_left_first(node, direction)) {
+		} else if (visit_left_first(ctx, node, direction)) {
 			stack[stack_size++] = node->left_or_first + 1;
 			stack[stack_size++] = node->left_or_first;
 		} else {
@@ -310,7 +311,7 @@ static void tlas_trace(const ctx_t * ctx, const ray_t * ray, hit_t * hit, counte
 
 		if (node_count(node) > 0) {
 			for (int i = node->left_or_first; i < node->left_or_first + node->count; i++) mesh_trace(ctx, ctx->f->tlas_indices[i], ray, hit, cnt);
-		} else if (visit_left_first(node, ray->direction)) {
+		} else if (visit_left_first(ctx, node, ray->direction)) {
 			stack[stack_size++] = node->left_or_first + 1;
 			stack[stack_size++] = node->left_or_first;
 		} else {
@@ -340,7 +341,7 @@ static int tlas_intersect(const ctx_t * ctx, v3 origin, v3 direction, float max_
 			for (int i = node->left_or_first; i < node->left_or_first + node->count; i++) {
 				if (mesh_intersect(ctx, ctx->f->tlas_indices[i], origin, direction, max_distance, cnt)) return 1;
 			}
-		} else if (visit_left_first(node, direction)) {
+		} else if (visit_left_first(ctx, node, direction)) {
 			stack[stack_size++] = node->left_or_first + 1;
 			stack[stack_size++] = node->left_or_first;
 		} else {
@@ -661,7 +662,9 @@ static v3 get_albedo(const ctx_t * ctx, const b200rt_material * m, const hit_t *
 
 	const b200rt_texture * tex = &ctx->s->textures[m->texture];
 	v3 sample;
-	if (!tex->mipmapped) sample = sample_bilinear(ctx, tex, hit->u, hit->v, 0, cnt);
+	if (ctx->c->texture_sample_mode == B200RT_TEXTURE_NEAREST) /* Texture::sample_nearest, Texture.cpp:149-154 */
+		sample = fetch_texel(ctx, tex, float_to_int(hit->u * (float)tex->width), float_to_int(hit->v * (float)tex->height), 0, cnt);
+	else if (ctx->c->texture_sample_mode == B200RT_TEXTURE_BILINEAR || !tex->mipmapped) sample = sample_bilinear(ctx, tex, hit->u, hit->v, 0, cnt);
 	else switch (ctx->c->mipmap_filter) {
 		case B200RT_FILTER_TRILINEAR: sample = sample_trilinear  (ctx, tex, hit->u, hit->v, hit->ds_dx, hit->ds_dy, hit->dt_dx, hit->dt_dy, cnt); break;
 		case B200RT_FILTER_EWA:       sample = sample_ewa        (ctx, tex, hit->u, hit->v, hit->ds_dx, hit->ds_dy, hit->dt_dx, hit->dt_dy, cnt); break;

@@ -43,6 +43,11 @@ CASES = [
     ("dynamic_b3_aniso_f45", scenes.dynamic, "l8_b3_aniso_dyn_ids", 3, "aniso", 1, 45),
     ("dynamic_b3_tri_f0", scenes.dynamic, "l8_b3_tri_ids", 3, "tri", 0, 0),
     ("dielectrics_b8_ewa", scenes.dielectrics_small, "l8_b8_ewa_ids", 8, "ewa", 0, 0),
+    # the other settings of the reference's hot-path switches (Config.h: BVH_TRAVERSAL_STRATEGY, TEXTURE_SAMPLE_MODE);
+    # "switch_" fixtures are read by tests/test_config_switches.py only
+    ("switch_naive_dynamic_b3_f45", scenes.dynamic, "l8_b3_aniso_naive_dyn_ids", 3, "aniso", 1, 45),
+    ("switch_nearest_monkey_b1", scenes.monkey_plane, "l8_b1_aniso_nearest_ids", 1, "aniso", 0, 0),
+    ("switch_bilinear_monkey_b1", scenes.monkey_plane, "l8_b1_aniso_bilinear_ids", 1, "aniso", 0, 0),
 ]
 DT = 1.0 / 60.0
 
@@ -81,7 +86,10 @@ def main():
 
             arrays = dict(pack.a)
             arrays.update(ref)
+            traversal = "naive" if "_naive" in variant else "ordered"
+            texture_mode = "nearest" if "_nearest" in variant else "bilinear" if "_bilinear" in variant else "mipmap"
             arrays["meta"] = np.frombuffer(json.dumps(dict(name=name, variant=variant, bounces=bounces, filter=filt,
+                                                           traversal=traversal, texture_mode=texture_mode,
                                                            animation=animation, frames=frames, dt=dt, width=W, height=H)).encode(), dtype=np.uint8)
             path = os.path.join(HERE, name + ".npz")
             np.savez_compressed(path, **arrays)
