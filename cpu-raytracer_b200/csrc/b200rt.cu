@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "kernels.cuh"
+#include "threaded_nodes.h"
 
 using namespace rt;
 
@@ -42,7 +43,8 @@ struct b200rt_ctx {
 
 	// static scene in HBM
 	DeviceBuffer nodes, shadow_nodes, hot, cold, materials, textures, texels, sky, gamma;
-	std::vector<int> shadow_node_offset;  // per BLAS: first node of its threaded copy (build_shadow_nodes)
+	std::vector<int> shadow_node_offset;  // per BLAS: first node of its threaded copy (build_threaded_nodes)
+	std::vector<int> records_per_copy;    // per BLAS: records in one threaded copy (RT_OCTANT_THREADED)
 	int sky_size = 0;
 	bool have_static = false;
 	std::vector<b200rt_blas> blas;
@@ -226,76 +228,6 @@ static int upload(b200rt_ctx * ctx, DeviceBuffer & buffer, const void * host, si
 	return 0;
 }
 
-// Threaded copy of one BLAS for the any-hit (shadow ray) traversal, traverse.cuh: blas_intersect.
-// The answer of an any-hit query does not depend on the order the nodes are visited in, so the
-// order is fixed — right child first, the fastest of those measured — which lets the tree be laid
-// out in exactly that order with a skip link per node: "hit an inner node" is "next record",
-// everything else is "follow the link", and the traversal needs no stack at all.
-//   record = BVHNode's 32 bytes: {min[3], max[3], skip, leaf}; skip = record that follows this
-//   node's subtree (-1 = done); leaf = 0 for an inner node, else (first_triangle << 6) | count with
-//   count in 1..63 — a larger leaf becomes a chain of records with the same box.
-// Unreachable records of the reference's array (node 1, reserved pairs) are dropped.
-static const char * build_shadow_nodes(const b200rt_bvh_node * nodes, int node_count, std::vector<b200rt_bvh_node> & out) {
-	const size_t base = out.size();
-	std::vector<int> order;            // node ids in layout order: preorder, right child first
-	{
-		std::vector<int> dfs(1, 0);
-		while (!dfs.empty()) {
-			const int n = dfs.back(); dfs.pop_back();
-			order.push_back(n);
-			if ((nodes[n].count & 0x3FFFFFFF) == 0) {
-				const int left = nodes[n].left_or_first;
-				if (left <= 0 || left + 1 >= node_count) return "BLAS child index out of bounds";
-				dfs.push_back(left); dfs.push_back(left + 1); // left + 1 is popped first
-			}
-			if (order.size() > size_t(node_count)) return "BLAS nodes do not form a tree";
-		}
-	}
-	std::vector<int> first_record(order.size());
-	std::vector<int> position_of;      // node id -> position in `order`
-	{
-		int max_node = 0;
-		for (int n : order) max_node = std::max(max_node, n);
-		position_of.assign(size_t(max_node) + 1, -1);
-		for (size_t i = 0; i < order.size(); i++) position_of[order[i]] = int(i);
-	}
-	int next = 0;
-	for (size_t i = 0; i < order.size(); i++) {
-		const int count = nodes[order[i]].count & 0x3FFFFFFF;
-		first_record[i] = next;
-		next += count > 0 ? (count + 62) / 63 : 1;
-	}
-	const int total = next;
-	// subtree extent: the layout is a preorder, so a subtree is a contiguous run; its end = the end of its last (left) child
-	std::vector<int> subtree_end(order.size());
-	for (size_t i = order.size(); i-- > 0; ) {
-		const b200rt_bvh_node & n = nodes[order[i]];
-		const int count = n.count & 0x3FFFFFFF;
-		subtree_end[i] = count > 0 ? first_record[i] + (count + 62) / 63 : subtree_end[position_of[n.left_or_first]];
-	}
-	out.resize(base + size_t(total));
-	for (size_t i = 0; i < order.size(); i++) {
-		const b200rt_bvh_node & n = nodes[order[i]];
-		const int count = n.count & 0x3FFFFFFF;
-		const int after = subtree_end[i] == total ? -1 : subtree_end[i];
-		if (count == 0) {
-			b200rt_bvh_node r = n;
-			r.left_or_first = after; r.count = 0;
-			out[base + size_t(first_record[i])] = r;
-		} else {
-			if (n.left_or_first < 0 || n.left_or_first >= (1 << 25)) return "BLAS too large for the shadow-ray layout (2^25 triangles per BLAS)";
-			for (int k = 0, done = 0; done < count; k++, done += 63) {
-				b200rt_bvh_node r = n;
-				const int part = std::min(63, count - done);
-				r.left_or_first = done + part < count ? first_record[i] + k + 1 : after;
-				r.count = ((n.left_or_first + done) << 6) | part;
-				out[base + size_t(first_record[i] + k)] = r;
-			}
-		}
-	}
-	return nullptr;
-}
-
 extern "C" int b200rt_upload_static(b200rt_ctx * ctx, const b200rt_static_scene * s) {
 	if (!ctx) return -1;
 	if (!s) return fail(ctx, "null scene");
@@ -339,9 +271,15 @@ extern "C" int b200rt_upload_static(b200rt_ctx * ctx, const b200rt_static_scene 
 		std::vector<b200rt_bvh_node> threaded;
 		threaded.reserve(size_t(s->node_count));
 		ctx->shadow_node_offset.assign(s->blas_count, 0);
+		ctx->records_per_copy.assign(s->blas_count, 0);
 		for (int b = 0; b < s->blas_count; b++) {
 			ctx->shadow_node_offset[b] = int(threaded.size());
-			if (const char * problem = build_shadow_nodes(s->nodes + s->blas[b].node_offset, s->blas[b].node_count, threaded)) return fail(ctx, problem);
+			if (const char * problem = build_threaded_nodes(s->nodes + s->blas[b].node_offset, s->blas[b].node_count, threaded)) return fail(ctx, problem);
+#ifdef RT_OCTANT_THREADED
+			ctx->records_per_copy[b] = int(threaded.size()) - ctx->shadow_node_offset[b];
+			for (int octant = 0; octant < 8; octant++) // copy `octant` lies at shadow_node_offset + (1 + octant) * records_per_copy
+				if (const char * problem = build_threaded_nodes(s->nodes + s->blas[b].node_offset, s->blas[b].node_count, threaded, octant)) return fail(ctx, problem);
+#endif
 		}
 		if (upload(ctx, ctx->shadow_nodes, threaded.data(), threaded.size() * sizeof(b200rt_bvh_node))) return -1;
 	}
@@ -506,6 +444,7 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 		instances[i].node_offset = blas.node_offset; instances[i].triangle_offset = blas.triangle_offset;
 		instances[i].material_offset = blas.material_offset; instances[i].shadow_node_offset = ctx->shadow_node_offset[in.blas];
 		memset(instances[i].reserved, 0, sizeof(instances[i].reserved));
+		instances[i].reserved[0] = ctx->records_per_copy[in.blas];
 	}
 	DeviceSphere * spheres = reinterpret_cast<DeviceSphere *>(base + off_spheres);
 	for (int i = 0; i < f->sphere_count; i++) {

@@ -43,7 +43,7 @@ struct DeviceLight  { float4 colour_kind; float4 position_inner; float4 negdir_o
 struct SceneParams {
 	// static (uploaded once)
 	const float4 * __restrict__ nodes;          // all BLAS, concatenated
-	const float4 * __restrict__ shadow_nodes;   // the same trees threaded for the any-hit traversal (b200rt.cu: build_shadow_nodes)
+	const float4 * __restrict__ shadow_nodes;   // the same trees threaded for the any-hit traversal (threaded_nodes.h: build_threaded_nodes)
 	const float4 * __restrict__ triangles_hot;
 	const float4 * __restrict__ triangles_cold;
 	const DeviceMaterial * __restrict__ materials;

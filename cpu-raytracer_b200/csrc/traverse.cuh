@@ -200,7 +200,7 @@ __device__ __forceinline__ bool blas_intersect(const float4 * __restrict__ nodes
 	return false;
 }
 
-// The same query on the threaded copy of the tree (b200rt.cu: build_shadow_nodes): records lie in
+// The same query on the threaded copy of the tree (threaded_nodes.h: build_threaded_nodes): records lie in
 // the order they are visited (right child first), so a hit inner node continues with the next
 // record and everything else follows the record's skip link — no stack, no push, no pop.
 __device__ __forceinline__ bool blas_shadow(const float4 * __restrict__ records, const float4 * __restrict__ hot, v3 o, v3 d, float max_distance) {
@@ -227,6 +227,37 @@ __device__ __forceinline__ bool blas_shadow(const float4 * __restrict__ records,
 	}
 	return false;
 }
+
+#ifdef RT_OCTANT_THREADED
+// Experiment (off by default): closest hit on the copy of the tree threaded in this ray's visiting order
+// (threaded_nodes.h: build_threaded_nodes with an octant). The records come in the sequence the stack traversal pops
+// the nodes in, each tested against the running best.t: same tests, same order, no stack.
+__device__ __forceinline__ void blas_trace_threaded(const float4 * __restrict__ records, const float4 * __restrict__ hot, v3 o, v3 d, int instance, Candidate & best) {
+	const v3 inv_d = V(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+	const bool exact = !ray_is_regular(o, inv_d);
+
+	int index = 0;
+	while (index >= 0) {
+		const float4 n0 = load_node(records + 2 * index), n1 = load_node(records + 2 * index + 1);
+		int next = __float_as_int(n1.z);                       // skip link
+		const int leaf = __float_as_int(n1.w);                 // bit 31: continuation of a long leaf, no box test
+		if (leaf < 0 || aabb_intersect(n0, n1, o, inv_d, best.t, exact)) {
+			if (leaf != 0) {
+				const int first = (leaf & 0x7FFFFFFF) >> 6, count = leaf & 63;
+				for (int i = first; i < first + count; i++) {
+					float t, u, v;
+					if (triangle_test(hot + 3 * size_t(i), o, d, best.t, t, u, v)) {
+						best.t = t; best.u = u; best.v = v; best.instance = instance; best.primitive = i;
+					}
+				}
+			} else {
+				next = index + 1;
+			}
+		}
+		index = next;
+	}
+}
+#endif
 
 // Sphere::trace, Sphere.cpp:9-40 — t only; the record is built in shade.cuh
 __device__ __forceinline__ bool sphere_test(const DeviceSphere * __restrict__ sphere, v3 o, v3 d, float max_t, float & t_out) {
@@ -309,6 +340,14 @@ __device__ __forceinline__ void trace_closest(const SceneParams & P, v3 o, v3 d,
 				if (COUNT) cnt.instances++;
 				// Mesh::trace, Mesh.cpp:17-31 (the differentials are transformed in shade.cuh, for the winner only)
 				const v3 local_d = transform_direction(inst.inverse, d);
+#ifdef RT_OCTANT_THREADED
+				if (!COUNT) { // BVH_TRAVERSE_TREE_NAIVE, the left child first at every node, is the order of octant 7
+					const int octant = P.traversal_naive ? 7 : (local_d.x > 0.0f ? 1 : 0) | (local_d.y > 0.0f ? 2 : 0) | (local_d.z > 0.0f ? 4 : 0);
+					const int records_per_copy = __ldg(&P.instances[instance].reserved[0]);
+					blas_trace_threaded(P.shadow_nodes + 2 * (size_t(inst.shadow_node_offset) + size_t(1 + octant) * size_t(records_per_copy)),
+					                    P.triangles_hot + 3 * size_t(inst.triangle_offset), transform_position(inst.inverse, o), local_d, instance, best);
+				} else
+#endif
 				blas_trace<COUNT>(P.nodes + 2 * size_t(inst.node_offset), P.triangles_hot + 3 * size_t(inst.triangle_offset),
 				                  transform_position(inst.inverse, o), local_d, instance, best, blas_stack, cnt, traversal_order_mask(P, local_d));
 			}

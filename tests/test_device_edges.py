@@ -164,7 +164,7 @@ def test_frame_before_static_scene_is_refused(dynamic):
 
 def test_leaves_larger_than_a_shadow_record(dynamic):
     """The shadow rays walk a threaded copy of every BLAS whose leaf records hold at most 63
-    triangles (b200rt.cu: build_shadow_nodes); a larger leaf becomes a chain of records. Collapse
+    triangles (threaded_nodes.h: build_threaded_nodes); a larger leaf becomes a chain of records. Collapse
     two BLAS of the scene into a single root leaf each (514 and 24+ triangles) and compare with
     the oracle, which walks the reference's own node array."""
     import oracle_ffi
