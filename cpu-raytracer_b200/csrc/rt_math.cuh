@@ -41,6 +41,15 @@ __device__ __forceinline__ float4 load_hinted(const float4 * p) {
 }
 __device__ __forceinline__ float4 load_node(const float4 * p)  { return load_hinted<RT_NODE_HINT>(p); }
 __device__ __forceinline__ float4 load_texel(const float4 * p) { return load_hinted<RT_TEXEL_HINT>(p); }
+// -DRT_PREFETCH_SKIP (experiment, off by default): a threaded record's skip target is known as soon as the record
+// is; asking for its line while the box test runs takes the load off the path of a ray that misses the box.
+__device__ __forceinline__ void prefetch_record(const float4 * p) {
+#ifdef RT_PREFETCH_SKIP
+	asm volatile("prefetch.global.L1 [%0];" : : "l"(p));
+#else
+	(void) p;
+#endif
+}
 
 __device__ __forceinline__ v3 V(float x, float y, float z) { v3 r; r.x = x; r.y = y; r.z = z; return r; }
 __device__ __forceinline__ v3 V(float4 a) { return V(a.x, a.y, a.z); }

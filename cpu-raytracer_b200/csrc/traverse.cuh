@@ -211,6 +211,7 @@ __device__ __forceinline__ bool blas_shadow(const float4 * __restrict__ records,
 	while (index >= 0) {
 		const float4 n0 = load_node(records + 2 * index), n1 = load_node(records + 2 * index + 1);
 		int next = __float_as_int(n1.z);                       // skip link
+		if (next >= 0) prefetch_record(records + 2 * next);
 		if (aabb_intersect(n0, n1, o, inv_d, max_distance, exact)) {
 			const int leaf = __float_as_int(n1.w);
 			if (leaf != 0) {
@@ -240,6 +241,7 @@ __device__ __forceinline__ void blas_trace_threaded(const float4 * __restrict__ 
 	while (index >= 0) {
 		const float4 n0 = load_node(records + 2 * index), n1 = load_node(records + 2 * index + 1);
 		int next = __float_as_int(n1.z);                       // skip link
+		if (next >= 0) prefetch_record(records + 2 * next);
 		const int leaf = __float_as_int(n1.w);                 // bit 31: continuation of a long leaf, no box test
 		if (leaf < 0 || aabb_intersect(n0, n1, o, inv_d, best.t, exact)) {
 			if (leaf != 0) {
