@@ -4,7 +4,8 @@ reference AS SHIPPED (8-ray packets through a shared stack, release build with c
 tests/golden/stock_frames.npz (made by tests/golden/make_golden_stock.py from the reference's own binaries):
 
 * packet mode without contraction: frame buffer, primary-hit ids and primary-hit distances are the per-ray
-  ones, bit for bit — SIMD_LANE_SIZE changes the packet width, not one pixel, id or distance. (Given the same
+  ones, bit for bit — the packet width changes not one pixel, id or distance (SIMD_LANE_SIZE 4 likewise;
+  SIMD_LANE_SIZE 1 is scalar arithmetic through libm, 68 dB away, and not what BASELINE quotes). (Given the same
   <obj>.bvh caches: ids index the leaves of the tree in use, and the release build's SBVH builder, with the SAH
   arithmetic contracted, writes a different, equally valid tree.)
 * the stock build (contraction on): north_star's bar, PSNR >= 50 dB, with a wide margin — fewer than one pixel
