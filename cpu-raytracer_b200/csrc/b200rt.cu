@@ -2,22 +2,20 @@
 //
 // There is no CPU fallback in this library: every entry point either runs the CUDA path or
 // returns an error.
-#include <cuda_runtime.h>
-
 #include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <string>
 #include <vector>
 
-#include "kernels.cuh"
+#include "kernel_table.h"      // rt_types.h (cuda_runtime.h, include/b200rt.h) + the launchers of the kernel units
 #include "threaded_nodes.h"
 
 using namespace rt;
 
 namespace {
 
-std::string g_create_error;
+thread_local std::string g_create_error;   // errors of calls that have no context to keep them in (b200rt_create, b200rt_host_alloc)
 
 struct DeviceBuffer {
 	void * ptr = nullptr; size_t bytes = 0;
@@ -39,12 +37,15 @@ struct b200rt_ctx {
 	std::string   error;
 	cudaStream_t  stream = nullptr;      // stream in use (the context's own, or a caller's: b200rt_set_stream)
 	cudaStream_t  own_stream = nullptr;
-	cudaEvent_t   ev[4] = { nullptr, nullptr, nullptr, nullptr }; // total begin, render begin, render end / fxaa begin, fxaa end
+	cudaEvent_t   ev[5] = { nullptr, nullptr, nullptr, nullptr, nullptr }; // total begin, render begin, render end / fxaa begin, fxaa end, total end
+	const KernelTable * kernels = nullptr;   // the kernel unit of config.arithmetic
 
 	// static scene in HBM
 	DeviceBuffer nodes, shadow_nodes, hot, cold, materials, textures, texels, sky, gamma;
 	std::vector<int> shadow_node_offset;  // per BLAS: first node of its threaded copy (build_threaded_nodes)
 	std::vector<int> records_per_copy;    // per BLAS: records in one threaded copy (RT_OCTANT_THREADED)
+	std::vector<int> wide_node_offset;    // per BLAS: first record of its four-wide copy, -1 if it has none (RT_WIDE_SHADOW)
+	DeviceBuffer wide_nodes;
 	int sky_size = 0;
 	bool have_static = false;
 	std::vector<b200rt_blas> blas;
@@ -60,6 +61,14 @@ struct b200rt_ctx {
 
 	// outputs
 	DeviceBuffer frame_buffer, presented, colour_float, ids, hits, counters, l2_scratch;
+	// `counters` is a ring of COUNTER_BLOCKS FrameCounters: frame k counts in block k % 4 and its last kernel
+	// (tile_schedule_kernel) clears block (k + 1) % 4 — no memset, no extra launch, and a block is cleared three frames
+	// after the frame that used it, when its copy to the host (at most two frames are in flight) is long done
+	unsigned frame_number = 0;
+	// deep-pixel queue (render.cuh): pools, allocated on first use
+	DeviceBuffer q_nodes, q_bounce, q_shadow, q_bounce_ready, q_shadow_ready;
+	int queue_inline_below = 0;
+	int blas_stack_entries = 1;
 	DeviceBuffer tile_cost, tile_order; // schedule of the render kernel (kernels.cuh: tile_schedule_kernel)
 	int tile_count_mine = 0;
 	void * pinned_out = nullptr; size_t pinned_out_bytes = 0;
@@ -68,7 +77,7 @@ struct b200rt_ctx {
 	// pipelined frames (b200rt_submit_frame / b200rt_wait_frame): two slots, each with its own images
 	// and counters, so that frame n+1 renders while frame n is still on its way to the host
 	struct Slot {
-		DeviceBuffer frame_buffer, presented, counters;
+		DeviceBuffer frame_buffer, presented;
 		FrameCounters * pinned_counters = nullptr;
 		cudaEvent_t render_end = nullptr, fxaa_end = nullptr, copied = nullptr; // ordering only, no timestamps: a timing event costs the stream ~20 us, four of them 7 % of a pipelined frame
 		bool busy = false;
@@ -81,8 +90,12 @@ struct b200rt_ctx {
 
 	SceneParams params;      // last frame's parameters (for b200rt_time_resident)
 	bool have_frame = false;
-	int  num_sms = 0, blocks_per_sm = 0;
+	int  num_sms = 0, blocks_per_sm[2][2] = { { 0, 0 }, { 0, 0 } };   // resident blocks per SM of the render kernel, [counting][queue]
+	unsigned launch_serial = 0;   // SceneParams::frame_serial of the last queue launch
 };
+
+enum { COUNTER_BLOCKS = 4 };
+static FrameCounters * counter_block(b200rt_ctx * ctx, unsigned frame) { return static_cast<FrameCounters *>(ctx->counters.ptr) + frame % COUNTER_BLOCKS; }
 
 #define CHECK_CUDA(ctx, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { (ctx)->error = std::string(#call) + ": " + cudaGetErrorString(e_); return -1; } } while (0)
 
@@ -115,6 +128,11 @@ extern "C" int b200rt_create(const b200rt_config * config, b200rt_ctx ** out) {
 	if (config->texture_sample_mode < 0 || config->texture_sample_mode > 2) { g_create_error = "bad texture_sample_mode"; return -1; }
 	if (config->traversal_naive < 0 || config->traversal_naive > 1) { g_create_error = "bad traversal_naive"; return -1; }
 	if (config->tile_stride < 1 || config->tile_phase < 0 || config->tile_phase >= config->tile_stride) { g_create_error = "bad tile partition"; return -1; }
+	if (config->arithmetic < 0 || config->arithmetic > 1) { g_create_error = "bad arithmetic mode"; return -1; }
+	if (config->deep_queue < 0 || config->deep_queue > 2) { g_create_error = "bad deep_queue"; return -1; }
+#ifndef RT_HAVE_FAST
+	if (config->arithmetic == B200RT_ARITHMETIC_FAST) { g_create_error = "this build of the library carries no FAST kernels"; return -1; }
+#endif
 
 	int device_count = 0;
 	cudaError_t e = cudaGetDeviceCount(&device_count);
@@ -125,6 +143,12 @@ extern "C" int b200rt_create(const b200rt_config * config, b200rt_ctx ** out) {
 	b200rt_ctx * ctx = new b200rt_ctx();
 	ctx->config = *config;
 	memset(&ctx->params, 0, sizeof(ctx->params));
+#ifdef RT_HAVE_FAST
+	ctx->kernels = config->arithmetic == B200RT_ARITHMETIC_FAST ? &kernels_fast() : &kernels_exact();
+#else
+	ctx->kernels = &kernels_exact();
+#endif
+	if (const char * text = getenv("B200RT_QUEUE_INLINE_BELOW")) ctx->queue_inline_below = atoi(text);   // tuning knob (tools/): see SceneParams::queue_inline_below
 
 	auto bail = [&](const char * what, cudaError_t err) { g_create_error = std::string(what) + ": " + cudaGetErrorString(err); b200rt_destroy(ctx); return -1; };
 
@@ -138,12 +162,6 @@ extern "C" int b200rt_create(const b200rt_config * config, b200rt_ctx ** out) {
 	cudaDeviceProp prop;
 	if ((e = cudaGetDeviceProperties(&prop, config->device)) != cudaSuccess) return bail("cudaGetDeviceProperties", e);
 	ctx->num_sms = prop.multiProcessorCount;
-	if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->blocks_per_sm, render_kernel<false>, RT_BLOCK_THREADS, 0)) != cudaSuccess) return bail("occupancy query (is this an sm_100a device?)", e);
-	if (ctx->blocks_per_sm < 1) ctx->blocks_per_sm = 1;
-#ifdef RT_CARVEOUT_L1   // variant under test: ask for the whole unified cache as L1 (the kernels use at most 2 KB of shared memory)
-	cudaFuncSetAttribute(render_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 0);
-	cudaFuncSetAttribute(render_kernel<true>,  cudaFuncAttributePreferredSharedMemoryCarveout, 0);
-#endif
 
 	// Texture::init (Texture.h:53-62) and the gamma table of get_screen() (fragment_fxaa.glsl:16-18)
 	float ewa[128];
@@ -151,7 +169,7 @@ extern "C" int b200rt_create(const b200rt_config * config, b200rt_ctx ** out) {
 		const float alpha = 2.0f, denom = 1.0f / 127.0f, exp_neg_alpha = expf(-alpha);
 		for (int i = 0; i < 128; i++) ewa[i] = expf(-alpha * (float(i) * denom)) - exp_neg_alpha;
 	}
-	if ((e = cudaMemcpyToSymbol(c_ewa_weight_table, ewa, sizeof(ewa))) != cudaSuccess) return bail("cudaMemcpyToSymbol", e);
+	if ((e = ctx->kernels->init(ewa)) != cudaSuccess) return bail("kernel tables (is this an sm_100a device?)", e);
 
 	float gamma[256];
 	for (int i = 0; i < 256; i++) gamma[i] = powf(float(i) / 255.0f, 1.0f / 2.2f);
@@ -161,7 +179,7 @@ extern "C" int b200rt_create(const b200rt_config * config, b200rt_ctx ** out) {
 	const size_t pixels = size_t(config->width) * config->height;
 	if ((e = ctx->frame_buffer.ensure(pixels * 4)) != cudaSuccess) return bail("cudaMalloc", e);
 	if ((e = ctx->presented.ensure(pixels * 3 + 16)) != cudaSuccess) return bail("cudaMalloc", e);
-	if ((e = ctx->counters.ensure(sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMalloc", e);
+	if ((e = ctx->counters.ensure(COUNTER_BLOCKS * sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMalloc", e);
 	if ((e = cudaMemset(ctx->frame_buffer.ptr, 0, pixels * 4)) != cudaSuccess) return bail("cudaMemset", e);
 	if ((e = cudaMallocHost(reinterpret_cast<void **>(&ctx->pinned_counters), sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMallocHost", e);
 	{ // schedule buffers; the first frame has no cost history: tiles in index order
@@ -173,6 +191,11 @@ extern "C" int b200rt_create(const b200rt_config * config, b200rt_ctx ** out) {
 		if ((e = ctx->tile_cost.ensure(size_t(mine) * 4)) != cudaSuccess || (e = ctx->tile_order.ensure(size_t(mine) * 4)) != cudaSuccess) return bail("cudaMalloc", e);
 		if ((e = cudaMemset(ctx->tile_cost.ptr, 0, size_t(mine) * 4)) != cudaSuccess) return bail("cudaMemset", e);
 		if ((e = cudaMemcpy(ctx->tile_order.ptr, identity.data(), size_t(mine) * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return bail("cudaMemcpy", e);
+		// the counter ring starts cleared and armed, as tile_schedule_kernel leaves the next frame's block
+		std::vector<FrameCounters> blocks(COUNTER_BLOCKS);
+		memset(blocks.data(), 0, blocks.size() * sizeof(FrameCounters));
+		for (FrameCounters & b : blocks) b.q_outstanding = ctx->tile_count_mine * 32;
+		if ((e = cudaMemcpy(ctx->counters.ptr, blocks.data(), blocks.size() * sizeof(FrameCounters), cudaMemcpyHostToDevice)) != cudaSuccess) return bail("cudaMemcpy", e);
 	}
 
 	*out = ctx;
@@ -186,9 +209,10 @@ extern "C" void b200rt_destroy(b200rt_ctx * ctx) {
 	if (ctx->upload_stream) cudaStreamSynchronize(ctx->upload_stream);
 	if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
 	for (DeviceBuffer * b : { &ctx->nodes, &ctx->shadow_nodes, &ctx->hot, &ctx->cold, &ctx->materials, &ctx->textures, &ctx->texels, &ctx->sky, &ctx->gamma,
-	                          &ctx->frame_block[0], &ctx->frame_block[1], &ctx->frame_buffer, &ctx->presented, &ctx->colour_float, &ctx->ids, &ctx->hits, &ctx->counters, &ctx->l2_scratch, &ctx->tile_cost, &ctx->tile_order }) b->release();
+	                          &ctx->frame_block[0], &ctx->frame_block[1], &ctx->frame_buffer, &ctx->presented, &ctx->colour_float, &ctx->ids, &ctx->hits, &ctx->counters, &ctx->l2_scratch, &ctx->tile_cost, &ctx->tile_order,
+	                          &ctx->q_nodes, &ctx->q_bounce, &ctx->q_shadow, &ctx->q_bounce_ready, &ctx->q_shadow_ready, &ctx->wide_nodes }) b->release();
 	for (auto & slot : ctx->slots) {
-		slot.frame_buffer.release(); slot.presented.release(); slot.counters.release();
+		slot.frame_buffer.release(); slot.presented.release();
 		if (slot.pinned_counters) cudaFreeHost(slot.pinned_counters);
 		for (cudaEvent_t e : { slot.render_end, slot.fxaa_end, slot.copied }) if (e) cudaEventDestroy(e);
 	}
@@ -241,16 +265,14 @@ extern "C" int b200rt_upload_static(b200rt_ctx * ctx, const b200rt_static_scene 
 	if (gpu_ingest && !s->gamma_lut) return fail(ctx, "texels_rgb8 needs gamma_lut");
 
 	// validate indices: the kernels trust them
+	int blas_depth = 0;
 	for (int b = 0; b < s->blas_count; b++) {
 		const b200rt_blas & d = s->blas[b];
 		if (d.node_offset < 0 || d.node_count <= 0 || d.node_offset + d.node_count > s->node_count || d.triangle_offset < 0 || d.triangle_count < 0 || d.triangle_offset + d.triangle_count > s->triangle_count) return fail(ctx, "BLAS range out of bounds");
-		for (int n = 0; n < d.node_count; n++) {
-			if (n == 1) continue; // never written by the reference's builders (BottomLevelBVH.cpp:92,132): unreachable, may hold garbage
-			const b200rt_bvh_node & node = s->nodes[d.node_offset + n];
-			const int count = node.count & 0x3FFFFFFF;
-			if (count > 0) { if (node.left_or_first < 0 || node.left_or_first + count > d.triangle_count) return fail(ctx, "BLAS leaf range out of bounds"); }
-			else if ((unsigned(node.count) >> 30) != 0 && (node.left_or_first < 0 || node.left_or_first + 1 >= d.node_count)) return fail(ctx, "BLAS child index out of bounds");
-		}
+		int depth = 0;
+		if (const char * problem = check_tree(s->nodes + d.node_offset, d.node_count, d.triangle_count, &depth)) return fail(ctx, std::string("BLAS ") + std::to_string(b) + ": " + problem);
+		blas_depth = std::max(blas_depth, depth);
+		if (depth + 1 > 64) return fail(ctx, "a BLAS is deeper than BVH_TRAVERSAL_STACK_SIZE allows (Config.h:25: 64 entries)");
 		for (int t = 0; t < d.triangle_count; t++) {
 			const int m = d.material_offset + s->triangles_cold[d.triangle_offset + t].material_id;
 			if (m < 0 || m >= s->material_count) return fail(ctx, "triangle material id out of range");
@@ -282,6 +304,18 @@ extern "C" int b200rt_upload_static(b200rt_ctx * ctx, const b200rt_static_scene 
 #endif
 		}
 		if (upload(ctx, ctx->shadow_nodes, threaded.data(), threaded.size() * sizeof(b200rt_bvh_node))) return -1;
+		ctx->wide_node_offset.assign(s->blas_count, -1);
+#ifdef RT_WIDE_SHADOW
+		std::vector<float> wide;
+		for (int b = 0; b < s->blas_count; b++) {
+			const size_t first = wide.size() / 32;
+			int entries = 0;
+			const char * problem = build_wide_nodes(s->nodes + s->blas[b].node_offset, s->blas[b].node_count, wide, &entries);
+			if (problem || entries > 48) wide.resize(first * 32);     // RT_WIDE_STACK; this tree keeps the binary walk
+			else ctx->wide_node_offset[b] = int(first);
+		}
+		if (upload(ctx, ctx->wide_nodes, wide.data(), std::max<size_t>(wide.size(), 32) * sizeof(float))) return -1;
+#endif
 	}
 
 	{ // TriangleHot 36 B -> 48 B (three aligned float4)
@@ -343,15 +377,14 @@ extern "C" int b200rt_upload_static(b200rt_ctx * ctx, const b200rt_static_scene 
 				const b200rt_texture & tex = s->textures[t];
 				float4 * pool = static_cast<float4 *>(ctx->texels.ptr) + tex.texel_offset;
 				const long long n = (long long)tex.width * tex.height;
-				texture_level0_kernel<<<unsigned(std::min<long long>((n + 255) / 256, 148 * 8)), 256, 0, ctx->stream>>>(static_cast<const unsigned char *>(bytes.ptr) + source * 3, static_cast<const float *>(lut.ptr), pool, n);
+				e = ctx->kernels->texture_level0(static_cast<const unsigned char *>(bytes.ptr) + source * 3, static_cast<const float *>(lut.ptr), pool, n, ctx->stream);
 				source += size_t(n);
 				int previous_width = tex.width;
-				for (int level = 1; level < tex.mip_levels && tex.mipmapped; level++) {
+				for (int level = 1; level < tex.mip_levels && tex.mipmapped && e == cudaSuccess; level++) {
 					const int w = tex.width >> level, h = tex.height >> level;
-					texture_mip_kernel<<<dim3((w + 31) / 32, (h + 7) / 8), 256, 0, ctx->stream>>>(pool + tex.mip_offsets[level - 1], pool + tex.mip_offsets[level], w, h, previous_width);
+					e = ctx->kernels->texture_mip(pool + tex.mip_offsets[level - 1], pool + tex.mip_offsets[level], w, h, previous_width, ctx->stream);
 					previous_width = w;
 				}
-				e = cudaGetLastError();
 			}
 			if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
 			bytes.release(); lut.release();
@@ -360,6 +393,7 @@ extern "C" int b200rt_upload_static(b200rt_ctx * ctx, const b200rt_static_scene 
 		if (upload_rgb(ctx->sky, s->sky, size_t(s->sky_size) * s->sky_size + 1)) return -1; // + the pad texel (Sky.cpp:45)
 	}
 	ctx->sky_size = s->sky_size;
+	ctx->blas_stack_entries = blas_depth + 1;
 	ctx->blas.assign(s->blas, s->blas + s->blas_count);
 	ctx->have_static = true;
 	ctx->have_frame = false;
@@ -391,13 +425,10 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 		if (f->instances[i].blas < 0 || f->instances[i].blas >= int(ctx->blas.size())) return fail(ctx, "instance BLAS index out of range");
 		if (f->tlas_indices[i] < 0 || f->tlas_indices[i] >= f->instance_count) return fail(ctx, "TLAS primitive index out of range");
 	}
-	for (int n = 0; n < f->tlas_node_count; n++) {
-		if (n == 1) continue; // unused slot, as in the BLAS
-		const b200rt_bvh_node & node = f->tlas_nodes[n];
-		const int count = node.count & 0x3FFFFFFF;
-		if (count > 0) { if (node.left_or_first < 0 || node.left_or_first + count > f->instance_count) return fail(ctx, "TLAS leaf range out of bounds"); }
-		else if ((unsigned(node.count) >> 30) != 0 && (node.left_or_first < 0 || node.left_or_first + 1 >= f->tlas_node_count)) return fail(ctx, "TLAS child index out of bounds");
-	}
+	int tlas_depth = 0;
+	if (const char * problem = check_tree(f->tlas_nodes, f->tlas_node_count, f->instance_count, &tlas_depth)) return fail(ctx, std::string("TLAS: ") + problem);
+	if (tlas_depth + 1 > RT_TLAS_STACK_SIZE) return fail(ctx, "TLAS deeper than the traversal stack (RT_TLAS_STACK_SIZE)");
+	if ((f->sphere_count > 0 && !f->spheres) || (f->plane_count > 0 && !f->planes) || (f->light_count > 0 && !f->lights)) return fail(ctx, "a count is positive but its array is NULL");
 	for (int i = 0; i < f->sphere_count; i++) if (f->spheres[i].material_id < 0 || f->spheres[i].material_id >= material_count) return fail(ctx, "sphere material id out of range");
 	for (int i = 0; i < f->plane_count;  i++) if (f->planes[i].material_id  < 0 || f->planes[i].material_id  >= material_count) return fail(ctx, "plane material id out of range");
 	for (int i = 0; i < f->light_count; i++) {
@@ -445,6 +476,7 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 		instances[i].material_offset = blas.material_offset; instances[i].shadow_node_offset = ctx->shadow_node_offset[in.blas];
 		memset(instances[i].reserved, 0, sizeof(instances[i].reserved));
 		instances[i].reserved[0] = ctx->records_per_copy[in.blas];
+		instances[i].reserved[1] = ctx->wide_node_offset[in.blas];
 	}
 	DeviceSphere * spheres = reinterpret_cast<DeviceSphere *>(base + off_spheres);
 	for (int i = 0; i < f->sphere_count; i++) {
@@ -480,6 +512,7 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 	SceneParams & P = ctx->params;
 	P.nodes = static_cast<const float4 *>(ctx->nodes.ptr);
 	P.shadow_nodes = static_cast<const float4 *>(ctx->shadow_nodes.ptr);
+	P.wide_nodes = static_cast<const float4 *>(ctx->wide_nodes.ptr);
 	P.triangles_hot = static_cast<const float4 *>(ctx->hot.ptr);
 	P.triangles_cold = static_cast<const float4 *>(ctx->cold.ptr);
 	P.materials = static_cast<const DeviceMaterial *>(ctx->materials.ptr);
@@ -515,53 +548,88 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 	return 0;
 }
 
-// Launches the render kernel over this context's tiles. frame_buffer is a device pointer.
-static int launch_render(b200rt_ctx * ctx, unsigned * frame_buffer, float * colour_float, bool count, void * counters_dev = nullptr) {
-	if (!counters_dev) counters_dev = ctx->counters.ptr;
-	reset_counters_kernel<<<1, 32, 0, ctx->stream>>>(static_cast<FrameCounters *>(counters_dev));
-	const unsigned total_warps = unsigned(ctx->params.tile_count_mine) * 32u;
-	if (total_warps == 0) return 0;
-	// persistent grid: every SM filled to the occupancy limit, never more warps than units
-	unsigned blocks = unsigned(ctx->num_sms) * unsigned(ctx->blocks_per_sm);
-	const unsigned needed = (total_warps + RT_BLOCK_THREADS / 32 - 1) / (RT_BLOCK_THREADS / 32);
-	if (blocks > needed) blocks = needed;
-	FrameCounters * counters = static_cast<FrameCounters *>(counters_dev);
-	if (count) render_kernel<true ><<<blocks, RT_BLOCK_THREADS, 0, ctx->stream>>>(ctx->params, frame_buffer, colour_float, counters);
-	else       render_kernel<false><<<blocks, RT_BLOCK_THREADS, 0, ctx->stream>>>(ctx->params, frame_buffer, colour_float, counters);
-	CHECK_CUDA(ctx, cudaGetLastError());
+// Pools of the deep-pixel queue (render.cuh), sized by this context's share of the frame; allocated on first use.
+// A pool that runs out costs nothing but speed: the producer walks that subtree depth-first (FrameCounters::q_fallbacks).
+static int ensure_queue(b200rt_ctx * ctx, SceneParams & P) {
+	const size_t pixels = size_t(std::max(ctx->tile_count_mine, 1)) * 1024;
+	const size_t nodes = std::min<size_t>(4 * pixels, (size_t(1) << 26) - 1), bounce = 4 * pixels, shadow = 8 * pixels;
+	if (!ctx->q_nodes.ptr) {
+		CHECK_CUDA(ctx, ctx->q_nodes.ensure(nodes * 6 * sizeof(float4)));
+		CHECK_CUDA(ctx, ctx->q_bounce.ensure(bounce * 5 * sizeof(float4)));
+		CHECK_CUDA(ctx, ctx->q_shadow.ensure(shadow * 2 * sizeof(float4)));
+		CHECK_CUDA(ctx, ctx->q_bounce_ready.ensure(bounce * sizeof(unsigned)));
+		CHECK_CUDA(ctx, ctx->q_shadow_ready.ensure(shadow * sizeof(unsigned)));
+		// "ready" means "holds this launch's serial number": the arrays must not start with a previous owner's
+		CHECK_CUDA(ctx, cudaMemset(ctx->q_bounce_ready.ptr, 0, bounce * sizeof(unsigned)));
+		CHECK_CUDA(ctx, cudaMemset(ctx->q_shadow_ready.ptr, 0, shadow * sizeof(unsigned)));
+	}
+	P.q_nodes = static_cast<float4 *>(ctx->q_nodes.ptr); P.q_bounce = static_cast<float4 *>(ctx->q_bounce.ptr); P.q_shadow = static_cast<float4 *>(ctx->q_shadow.ptr);
+	P.q_bounce_ready = static_cast<unsigned *>(ctx->q_bounce_ready.ptr); P.q_shadow_ready = static_cast<unsigned *>(ctx->q_shadow_ready.ptr);
+	P.q_node_capacity = unsigned(nodes); P.q_bounce_capacity = unsigned(bounce); P.q_shadow_capacity = unsigned(shadow);
 	return 0;
 }
 
-// After the frame (outside the render kernel's timed events): order the tiles for the next one.
+// Launches the render kernel over this context's tiles; the frame counts in the ring's current block. frame_buffer is
+// a device pointer. banded: store through the band targets (b200rt_set_band_targets) — b200rt_render_frame_device
+// only; every other entry point renders into the one image it was given.
+static int launch_render(b200rt_ctx * ctx, unsigned * frame_buffer, float * colour_float, bool count, bool banded = false) {
+	const unsigned total_warps = unsigned(ctx->params.tile_count_mine) * 32u;
+	if (total_warps == 0) return 0;
+	SceneParams P = ctx->params;
+	if (!banded) P.band_count = 0;
+	P.blas_stack_entries = ctx->blas_stack_entries;
+	P.queue_mode = (count || P.light_count > 24 || P.bounces == 0) ? 0 : ctx->config.deep_queue;   // RT_QUEUE_MAX_LIGHTS: a node record keeps one bit per light
+	P.queue_inline_below = ctx->queue_inline_below;
+	if (P.queue_mode != 0) {
+		if (ensure_queue(ctx, P)) return -1;
+		if (++ctx->launch_serial == 0) ctx->launch_serial = 1;
+		P.frame_serial = ctx->launch_serial;
+	}
+	// persistent grid: every SM filled to the occupancy limit, never more warps than units
+	int & per_sm = ctx->blocks_per_sm[count ? 1 : 0][P.queue_mode != 0 ? 1 : 0];
+	if (per_sm == 0) {
+		CHECK_CUDA(ctx, ctx->kernels->render_occupancy(P, count, &per_sm));
+		if (per_sm < 1) per_sm = 1;
+	}
+	unsigned blocks = unsigned(ctx->num_sms) * unsigned(per_sm);
+	const unsigned needed = (total_warps + 7) / 8;   // 8 warps per 256-thread block
+	if (blocks > needed) blocks = needed;
+	CHECK_CUDA(ctx, ctx->kernels->render(P, frame_buffer, colour_float, counter_block(ctx, ctx->frame_number), count ? 1 : 0, blocks, ctx->stream));
+	return 0;
+}
+
 // Called after the last kernel of a frame has been issued: from here on the frame's device block may be rewritten (stage_frame).
 static int release_frame_block(b200rt_ctx * ctx) {
 	CHECK_CUDA(ctx, cudaEventRecord(ctx->consumed[ctx->block_in_use], ctx->stream));
 	return 0;
 }
-static int launch_schedule(b200rt_ctx * ctx) {
-	if (ctx->params.tile_count_mine == 0) return 0;
-	tile_schedule_kernel<<<1, 1024, 0, ctx->stream>>>(static_cast<unsigned *>(ctx->tile_cost.ptr), static_cast<unsigned *>(ctx->tile_order.ptr), ctx->params.tile_count_mine);
-	CHECK_CUDA(ctx, cudaGetLastError());
+// The last kernel of every frame: orders the tiles for the next one by what they cost in this one, and clears the
+// next frame's counter block. Returns this frame's block (for the copy to the host) through *counted.
+static int launch_schedule(b200rt_ctx * ctx, FrameCounters ** counted = nullptr) {
+	if (counted) *counted = counter_block(ctx, ctx->frame_number);
+	CHECK_CUDA(ctx, ctx->kernels->schedule(static_cast<unsigned *>(ctx->tile_cost.ptr), static_cast<unsigned *>(ctx->tile_order.ptr), ctx->params.tile_count_mine, counter_block(ctx, ctx->frame_number + 1), ctx->stream));
+	ctx->frame_number++;
 	return 0;
 }
 
 static int launch_fxaa(b200rt_ctx * ctx, const unsigned * frame_buffer, unsigned char * presented, int row_begin = 0, int row_end = -1) {
 	if (row_end < 0) row_end = ctx->config.height;
 	if (row_end <= row_begin) return 0;
-	const dim3 block(FXAA_TILE_W, FXAA_TILE_H);
-	const dim3 grid((ctx->config.width + FXAA_TILE_W - 1) / FXAA_TILE_W, (row_end - row_begin + FXAA_TILE_H - 1) / FXAA_TILE_H);
-	fxaa_kernel<<<grid, block, 0, ctx->stream>>>(frame_buffer, presented, static_cast<const float *>(ctx->gamma.ptr), ctx->config.width, ctx->config.height, ctx->config.enable_fxaa, row_begin, row_end);
-	CHECK_CUDA(ctx, cudaGetLastError());
+	CHECK_CUDA(ctx, ctx->kernels->fxaa(frame_buffer, presented, static_cast<const float *>(ctx->gamma.ptr), ctx->config.width, ctx->config.height, ctx->config.enable_fxaa, row_begin, row_end, ctx->stream));
 	return 0;
 }
 
-static void fill_stats(b200rt_ctx * ctx, b200rt_stats * stats) {
-	const FrameCounters & c = *ctx->pinned_counters;
+static void counters_to_stats(const FrameCounters & c, b200rt_stats * stats) {
 	stats->primary_rays = c.primary; stats->shadow_rays = c.shadow; stats->reflection_rays = c.reflection; stats->refraction_rays = c.refraction;
 	stats->nodes_visited = c.nodes; stats->triangles_tested = c.triangles; stats->texels_fetched = c.texels;
 	stats->hits_accepted = c.accepted; stats->instances_entered = c.instances;
 	stats->device_ms_render = stats->device_ms_fxaa = stats->device_ms_total = 0.0f;
 	stats->device_ms_tail = (c.first_idle_ns != 0 && c.last_done_ns > ~c.first_idle_ns) ? float(double(c.last_done_ns - ~c.first_idle_ns) * 1e-6) : 0.0f;
+	stats->queue_nodes = c.q_node_reserved; stats->queue_bounce_items = c.q_bounce_reserved; stats->queue_shadow_items = c.q_shadow_reserved; stats->queue_fallbacks = c.q_fallbacks;
+}
+
+static void fill_stats(b200rt_ctx * ctx, b200rt_stats * stats) {
+	counters_to_stats(*ctx->pinned_counters, stats);
 	cudaEventElapsedTime(&stats->device_ms_render, ctx->ev[1], ctx->ev[2]);
 	cudaEventElapsedTime(&stats->device_ms_fxaa,   ctx->ev[2], ctx->ev[3]);
 }
@@ -591,14 +659,12 @@ extern "C" int b200rt_render_frame(b200rt_ctx * ctx, const b200rt_frame * frame,
 	if (launch_render(ctx, fb, out->colour_float ? static_cast<float *>(ctx->colour_float.ptr) : nullptr, ctx->config.count_traversal != 0)) return -1;
 	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
 	if (out->presented_rgb8 && launch_fxaa(ctx, fb, static_cast<unsigned char *>(ctx->presented.ptr))) return -1;
-	if (launch_schedule(ctx)) return -1;
+	FrameCounters * counted = nullptr;
+	if (launch_schedule(ctx, &counted)) return -1;
 	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));
 
-	if (out->primary_ids || out->primary_hit) {
-		const dim3 grid((ctx->config.width + 31) / 32, (ctx->config.height + 7) / 8);
-		primary_hits_kernel<<<grid, RT_BLOCK_THREADS, 0, ctx->stream>>>(ctx->params, out->primary_ids ? static_cast<int *>(ctx->ids.ptr) : nullptr, out->primary_hit ? static_cast<float *>(ctx->hits.ptr) : nullptr);
-		CHECK_CUDA(ctx, cudaGetLastError());
-	}
+	if (out->primary_ids || out->primary_hit)
+		CHECK_CUDA(ctx, ctx->kernels->primary_hits(ctx->params, out->primary_ids ? static_cast<int *>(ctx->ids.ptr) : nullptr, out->primary_hit ? static_cast<float *>(ctx->hits.ptr) : nullptr, ctx->stream));
 	if (release_frame_block(ctx)) return -1;
 
 	// device -> pinned host, then one synchronisation
@@ -609,24 +675,20 @@ extern "C" int b200rt_render_frame(b200rt_ctx * ctx, const b200rt_frame * frame,
 	const bool direct_rgb = out->presented_rgb8 && is_page_locked(out->presented_rgb8);
 	if (out->frame_buffer)   CHECK_CUDA(ctx, cudaMemcpyAsync(direct_fb  ? static_cast<void *>(out->frame_buffer)   : pinned + off_fb,  fb, pixels * 4, cudaMemcpyDeviceToHost, ctx->stream));
 	if (out->presented_rgb8) CHECK_CUDA(ctx, cudaMemcpyAsync(direct_rgb ? static_cast<void *>(out->presented_rgb8) : pinned + off_rgb, ctx->presented.ptr, pixels * 3, cudaMemcpyDeviceToHost, ctx->stream));
-	CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->pinned_counters, ctx->counters.ptr, sizeof(FrameCounters), cudaMemcpyDeviceToHost, ctx->stream));
+	CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->pinned_counters, counted, sizeof(FrameCounters), cudaMemcpyDeviceToHost, ctx->stream));
 	if (out->colour_float) CHECK_CUDA(ctx, cudaMemcpyAsync(out->colour_float, ctx->colour_float.ptr, pixels * 12, cudaMemcpyDeviceToHost, ctx->stream));
 	if (out->primary_ids)  CHECK_CUDA(ctx, cudaMemcpyAsync(out->primary_ids, ctx->ids.ptr, pixels * 8, cudaMemcpyDeviceToHost, ctx->stream));
 	if (out->primary_hit)  CHECK_CUDA(ctx, cudaMemcpyAsync(out->primary_hit, ctx->hits.ptr, pixels * 16, cudaMemcpyDeviceToHost, ctx->stream));
-	cudaEvent_t end = ctx->ev[0]; // reuse: total = ev[0] .. now, measured with a fresh record on a temp event
-	cudaEvent_t total_end;
-	CHECK_CUDA(ctx, cudaEventCreate(&total_end));
-	CHECK_CUDA(ctx, cudaEventRecord(total_end, ctx->stream));
+	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[4], ctx->stream));
 	cudaError_t sync = cudaStreamSynchronize(ctx->stream);
-	if (sync != cudaSuccess) { cudaEventDestroy(total_end); ctx->error = std::string("render failed: ") + cudaGetErrorString(sync); return -1; }
+	if (sync != cudaSuccess) { ctx->error = std::string("render failed: ") + cudaGetErrorString(sync); return -1; }
 
 	if (out->frame_buffer   && !direct_fb)  memcpy(out->frame_buffer,   pinned + off_fb,  pixels * 4);
 	if (out->presented_rgb8 && !direct_rgb) memcpy(out->presented_rgb8, pinned + off_rgb, pixels * 3);
 	if (out->stats) {
 		fill_stats(ctx, out->stats);
-		cudaEventElapsedTime(&out->stats->device_ms_total, end, total_end);
+		cudaEventElapsedTime(&out->stats->device_ms_total, ctx->ev[0], ctx->ev[4]);
 	}
-	cudaEventDestroy(total_end);
 	return 0;
 }
 
@@ -638,13 +700,14 @@ extern "C" int b200rt_render_frame_device(b200rt_ctx * ctx, const b200rt_frame *
 	if (stats) CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
 	if (stage_frame(ctx, frame)) return -1;
 	if (stats) CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
-	if (launch_render(ctx, reinterpret_cast<unsigned *>(uintptr_t(frame_buffer_dev)), nullptr, false)) return -1;
+	if (launch_render(ctx, reinterpret_cast<unsigned *>(uintptr_t(frame_buffer_dev)), nullptr, false, true)) return -1;   // the one entry point that stores through the band targets
 	if (stats) CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
-	if (launch_schedule(ctx)) return -1;
+	FrameCounters * counted = nullptr;
+	if (launch_schedule(ctx, &counted)) return -1;
 	if (stats) CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));
 	if (release_frame_block(ctx)) return -1;
 	if (!stats) return 0; // asynchronous: the caller orders later work on the context's stream
-	CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->pinned_counters, ctx->counters.ptr, sizeof(FrameCounters), cudaMemcpyDeviceToHost, ctx->stream));
+	CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->pinned_counters, counted, sizeof(FrameCounters), cudaMemcpyDeviceToHost, ctx->stream));
 	CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 	fill_stats(ctx, stats); cudaEventElapsedTime(&stats->device_ms_total, ctx->ev[0], ctx->ev[3]);
 	return 0;
@@ -728,7 +791,6 @@ static int ensure_slot(b200rt_ctx * ctx, b200rt_ctx::Slot & slot) {
 	if (slot.copied) return 0;
 	CHECK_CUDA(ctx, slot.frame_buffer.ensure(pixels * 4));
 	CHECK_CUDA(ctx, slot.presented.ensure(pixels * 3 + 16));
-	CHECK_CUDA(ctx, slot.counters.ensure(sizeof(FrameCounters)));
 	CHECK_CUDA(ctx, cudaMemset(slot.frame_buffer.ptr, 0, pixels * 4));
 	CHECK_CUDA(ctx, cudaMallocHost(reinterpret_cast<void **>(&slot.pinned_counters), sizeof(FrameCounters)));
 	for (cudaEvent_t * e : { &slot.render_end, &slot.fxaa_end, &slot.copied }) CHECK_CUDA(ctx, cudaEventCreateWithFlags(e, cudaEventDisableTiming));
@@ -752,17 +814,18 @@ extern "C" int b200rt_submit_frame(b200rt_ctx * ctx, const b200rt_frame * frame,
 	unsigned * fb = static_cast<unsigned *>(slot.frame_buffer.ptr);
 
 	if (stage_frame(ctx, frame)) return -1;
-	if (launch_render(ctx, fb, nullptr, ctx->config.count_traversal != 0, slot.counters.ptr)) return -1;
+	if (launch_render(ctx, fb, nullptr, ctx->config.count_traversal != 0)) return -1;
 	CHECK_CUDA(ctx, cudaEventRecord(slot.render_end, ctx->stream));
 	if (out->presented_rgb8 && launch_fxaa(ctx, fb, static_cast<unsigned char *>(slot.presented.ptr))) return -1;
-	if (launch_schedule(ctx)) return -1;
+	FrameCounters * counted = nullptr;
+	if (launch_schedule(ctx, &counted)) return -1;
 	CHECK_CUDA(ctx, cudaEventRecord(slot.fxaa_end, ctx->stream));
 	if (release_frame_block(ctx)) return -1;
 
 	// the pre-FXAA image can leave as soon as tracing is done, in parallel with the FXAA kernel
 	CHECK_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, slot.render_end, 0));
 	if (out->frame_buffer) CHECK_CUDA(ctx, cudaMemcpyAsync(out->frame_buffer, fb, pixels * 4, cudaMemcpyDeviceToHost, ctx->copy_stream));
-	CHECK_CUDA(ctx, cudaMemcpyAsync(slot.pinned_counters, slot.counters.ptr, sizeof(FrameCounters), cudaMemcpyDeviceToHost, ctx->copy_stream));
+	CHECK_CUDA(ctx, cudaMemcpyAsync(slot.pinned_counters, counted, sizeof(FrameCounters), cudaMemcpyDeviceToHost, ctx->copy_stream));   // this block is cleared three frames from now
 	CHECK_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, slot.fxaa_end, 0));
 	if (out->presented_rgb8) CHECK_CUDA(ctx, cudaMemcpyAsync(out->presented_rgb8, slot.presented.ptr, pixels * 3, cudaMemcpyDeviceToHost, ctx->copy_stream));
 	CHECK_CUDA(ctx, cudaEventRecord(slot.copied, ctx->copy_stream));
@@ -783,11 +846,7 @@ extern "C" int b200rt_wait_frame(b200rt_ctx * ctx, b200rt_stats * stats) {
 	if (e != cudaSuccess) { ctx->error = std::string("frame failed: ") + cudaGetErrorString(e); return -1; }
 	if (stats) {
 		const FrameCounters & c = *slot.pinned_counters;
-		stats->primary_rays = c.primary; stats->shadow_rays = c.shadow; stats->reflection_rays = c.reflection; stats->refraction_rays = c.refraction;
-		stats->nodes_visited = c.nodes; stats->triangles_tested = c.triangles; stats->texels_fetched = c.texels;
-		stats->hits_accepted = c.accepted; stats->instances_entered = c.instances;
-		stats->device_ms_render = stats->device_ms_fxaa = stats->device_ms_total = 0.0f;
-		stats->device_ms_tail = (c.first_idle_ns != 0 && c.last_done_ns > ~c.first_idle_ns) ? float(double(c.last_done_ns - ~c.first_idle_ns) * 1e-6) : 0.0f;
+		counters_to_stats(c, stats);
 		// no timing events on this path: the render kernel stamps its own start and end (globaltimer)
 		if (c.first_start_ns != 0 && c.last_done_ns > ~c.first_start_ns) stats->device_ms_render = float(double(c.last_done_ns - ~c.first_start_ns) * 1e-6);
 		stats->device_ms_total = stats->device_ms_render;

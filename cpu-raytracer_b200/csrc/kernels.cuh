@@ -2,7 +2,7 @@
 #pragma once
 #include "render.cuh"
 
-namespace rt {
+namespace RT_NAMESPACE {
 
 __device__ __forceinline__ unsigned warp_sum(unsigned v) {
 #pragma unroll
@@ -24,75 +24,17 @@ __device__ __forceinline__ bool unit_pixel(const SceneParams & P, unsigned unit,
 	return px < P.width && py < P.height; // edge tiles are clipped, WorkerThread.cpp:60-61
 }
 
-// Where a pixel of row py goes when the frame is exchanged in bands (include/b200rt.h:
-// b200rt_set_band_targets): into the image of the GPU that owns the row's band and, within band_halo
-// rows of a band border, into the neighbour's too — cyclically, because the FXAA taps wrap at the
-// frame border (GL_REPEAT, Window.cpp:48-50). Plain stores over NVLink peer memory: the exchange
-// rides on the kernel's last instruction, every link carries 1/N of the frame, nobody gathers.
-__device__ __forceinline__ void store_pixel_banded(const SceneParams & P, size_t p, int py, unsigned value) {
-	const int last = P.band_count - 1;
-	int b = py / P.band_rows;
-	if (b > last) b = last;
-	P.band_targets[b][p] = value;
-	const int begin = b * P.band_rows, end = b == last ? P.height : begin + P.band_rows;
-	if (py - begin < P.band_halo) P.band_targets[b == 0 ? last : b - 1][p] = value;
-	if (end - py <= P.band_halo)  P.band_targets[b == last ? 0 : b + 1][p] = value;
-}
-
-// Clears the frame's counter block. A kernel rather than a memset: memsets are served by a copy
-// engine, and with frames pipelined that engine is busy moving the previous frame's images to the
-// host — the memset, and the render kernel behind it, waited 60 us per frame for it.
-__global__ void reset_counters_kernel(FrameCounters * counters) {
+// Clears the NEXT frame's counter block (the context keeps a ring of four: b200rt.cu) and arms its count of
+// outstanding work. Runs inside tile_schedule_kernel, the last kernel of every frame, so a frame costs no launch for it.
+__device__ __forceinline__ void reset_counters(FrameCounters * counters, unsigned total_units) {
 	unsigned long long * words = reinterpret_cast<unsigned long long *>(counters);
 	for (unsigned i = threadIdx.x; i < sizeof(FrameCounters) / sizeof(unsigned long long); i += blockDim.x) words[i] = 0ull;
+	__syncthreads();
+	if (threadIdx.x == 0) counters->q_outstanding = int(total_units);
 }
 
-// Persistent warps pull units off one device-side counter — the GPU form of the reference's
-// InterlockedDecrement tile countdown (WorkerThread.cpp:53-65).
-template<bool COUNT>
-__global__ void __launch_bounds__(RT_BLOCK_THREADS, RT_MIN_BLOCKS)
-render_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, float * __restrict__ colour_float, FrameCounters * __restrict__ counters) {
+__device__ __forceinline__ void flush_ray_counters(FrameCounters * __restrict__ counters, const Counters & cnt, unsigned primary, bool count) {
 	const int lane = threadIdx.x & 31;
-	const unsigned total_units = unsigned(P.tile_count_mine) * 32u;
-
-	Counters cnt = { 0, 0, 0, 0, 0, 0, 0, 0 };
-	unsigned primary = 0;
-
-	if (threadIdx.x == 0) { // when the launch started: with last_done_ns the kernel times itself, and the pipelined frames need no timing events
-		unsigned long long now;
-		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-		atomicMax(&counters->first_start_ns, ~now);
-	}
-
-	for (;;) {
-		unsigned unit = 0;
-		if (lane == 0) unit = atomicAdd(&counters->next_unit, 1u);
-		unit = __shfl_sync(0xffffffffu, unit, 0);
-		if (unit >= total_units) break;
-
-		const long long unit_begin = clock64();
-		int local_tile, px, py;
-		if (unit_pixel(P, unit, lane, local_tile, px, py)) {
-			const Ray ray = primary_ray(P, px, py);
-			primary++;
-			const v3 colour = shade_pixel<COUNT>(P, ray, cnt);
-
-			const size_t p = size_t(px) + size_t(P.width) * py;
-			if (P.band_count == 0) frame_buffer[p] = plot_colour(colour);
-			else store_pixel_banded(P, p, py, plot_colour(colour));
-			if (colour_float) { colour_float[3 * p] = colour.x; colour_float[3 * p + 1] = colour.y; colour_float[3 * p + 2] = colour.z; }
-		}
-		__syncwarp();
-		if (lane == 0) atomicAdd(P.tile_cost + local_tile, unsigned((clock64() - unit_begin) >> 6)); // what this tile cost, for the next frame's order
-	}
-
-	if (lane == 0) { // when did this warp run dry? (min / max over warps = how long the launch ran partly empty)
-		unsigned long long now;
-		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-		atomicMax(&counters->first_idle_ns, ~now);   // stored complemented: the earliest time wins an atomicMax, and an all-zero block is the initial state
-		atomicMax(&counters->last_done_ns, now);
-	}
-
 	// one atomic per warp and counter
 	const unsigned s_primary = warp_sum(primary), s_shadow = warp_sum(cnt.shadow), s_refl = warp_sum(cnt.reflection), s_refr = warp_sum(cnt.refraction);
 	if (lane == 0) {
@@ -101,7 +43,7 @@ render_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, float *
 		atomicAdd(&counters->reflection, (unsigned long long)s_refl);
 		atomicAdd(&counters->refraction, (unsigned long long)s_refr);
 	}
-	if (COUNT) {
+	if (count) {
 		const unsigned s_nodes = warp_sum(cnt.nodes), s_tris = warp_sum(cnt.triangles), s_texels = warp_sum(cnt.texels);
 		const unsigned s_accepted = warp_sum(cnt.accepted), s_instances = warp_sum(cnt.instances);
 		if (lane == 0) {
@@ -114,17 +56,151 @@ render_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, float *
 	}
 }
 
+// Persistent warps pull units off one device-side counter — the GPU form of the reference's
+// InterlockedDecrement tile countdown (WorkerThread.cpp:53-65). One thread walks a pixel's whole ray tree.
+template<bool COUNT, int MAXB, int BSTACK>
+__global__ void __launch_bounds__(RT_BLOCK_THREADS, RT_MIN_BLOCKS)
+render_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, float * __restrict__ colour_float, FrameCounters * __restrict__ counters) {
+	const int lane = threadIdx.x & 31;
+	const unsigned total_units = unsigned(P.tile_count_mine) * 32u;
+	const PixelOut out = { frame_buffer, colour_float };
+
+	Counters cnt = { 0, 0, 0, 0, 0, 0, 0, 0 };
+	unsigned primary = 0;
+
+	if (threadIdx.x == 0) atomicMax(&counters->first_start_ns, ~global_timer_ns()); // when the launch started: with last_done_ns the kernel times itself, and the pipelined frames need no timing events
+
+	for (;;) {
+		unsigned unit = 0;
+		if (lane == 0) unit = atomicAdd(&counters->next_unit, 1u);
+		unit = __shfl_sync(0xffffffffu, unit, 0);
+		if (unit >= total_units) break;
+
+		const long long unit_begin = clock64();
+		int local_tile, px, py;
+		if (unit_pixel(P, unit, lane, local_tile, px, py)) {
+			const Ray ray = primary_ray(P, px, py);
+			primary++;
+			float distance;
+			write_pixel(P, out, px, py, shade_subtree<COUNT, MAXB, BSTACK>(P, ray, P.bounces, cnt, distance));
+		}
+		__syncwarp();
+		if (lane == 0) atomicAdd(P.tile_cost + local_tile, unsigned((clock64() - unit_begin) >> 6)); // what this tile cost, for the next frame's order
+	}
+
+	if (lane == 0) { // when did this warp run dry? (min / max over warps = how long the launch ran partly empty)
+		const unsigned long long now = global_timer_ns();
+		atomicMax(&counters->first_idle_ns, ~now);   // stored complemented: the earliest time wins an atomicMax, and an all-zero block is the initial state
+		atomicMax(&counters->last_done_ns, now);
+	}
+	flush_ray_counters(counters, cnt, primary, COUNT);
+}
+
+// The same frame with the deep-pixel queue (render.cuh): a warp takes, in this order of preference, 32 bounce items,
+// 32 shadow items, a tile unit, whatever items are left — and leaves when the frame's count of outstanding work
+// (units not finished + items not finished) is zero. Items first: the rays of the deep pixels are the frame's
+// critical path, and popping them as soon as a full warp's worth exists keeps the queues (and their L2 footprint) short.
+template<int MAXB, int BSTACK>
+__global__ void __launch_bounds__(RT_BLOCK_THREADS, RT_MIN_BLOCKS)
+render_queue_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, float * __restrict__ colour_float, FrameCounters * counters) {
+	const int lane = threadIdx.x & 31;
+	const unsigned total_units = unsigned(P.tile_count_mine) * 32u;
+	const PixelOut out = { frame_buffer, colour_float };
+	enum { WORK_NONE = 0, WORK_UNIT = 1, WORK_BOUNCE = 2, WORK_SHADOW = 3, WORK_WAIT = 4 };
+
+	Counters cnt = { 0, 0, 0, 0, 0, 0, 0, 0 };
+	unsigned primary = 0;
+	bool was_idle = false;
+
+	if (threadIdx.x == 0) atomicMax(&counters->first_start_ns, ~global_timer_ns());
+
+	for (;;) {
+		// ---- lane 0 chooses the warp's next piece of work ------------------------------------------------
+		int kind = WORK_NONE; unsigned first = 0, n = 0;
+		if (lane == 0) {
+			for (int attempt = 0; attempt < 8 && kind == WORK_NONE; attempt++) {
+				const unsigned hb = peek(&counters->q_bounce_head), rb = min(peek(&counters->q_bounce_reserved), P.q_bounce_capacity), ab = rb > hb ? rb - hb : 0u;
+				const unsigned hs = peek(&counters->q_shadow_head), rs = min(peek(&counters->q_shadow_reserved), P.q_shadow_capacity), as = rs > hs ? rs - hs : 0u;
+				const bool units_left = peek(&counters->next_unit) < total_units;
+				if (ab >= 32u || (ab > 0u && !units_left && as < 32u)) {
+					n = min(ab, 32u);
+					if (atomicCAS(&counters->q_bounce_head, hb, hb + n) == hb) { kind = WORK_BOUNCE; first = hb; }
+				} else if (as >= 32u || (as > 0u && !units_left)) {
+					n = min(as, 32u);
+					if (atomicCAS(&counters->q_shadow_head, hs, hs + n) == hs) { kind = WORK_SHADOW; first = hs; }
+				} else if (units_left) {
+					first = atomicAdd(&counters->next_unit, 1u);
+					if (first < total_units) kind = WORK_UNIT;
+				} else break;
+			}
+			if (kind == WORK_NONE && peek(&counters->q_outstanding) > 0) kind = WORK_WAIT;   // nothing to take, or every race lost: look again
+		}
+		kind = __shfl_sync(0xffffffffu, kind, 0); first = __shfl_sync(0xffffffffu, first, 0); n = __shfl_sync(0xffffffffu, n, 0);
+		if (kind == WORK_NONE) break;
+		if (kind == WORK_WAIT) {
+			if (lane == 0 && !was_idle) atomicMax(&counters->first_idle_ns, ~global_timer_ns());
+			was_idle = true;
+			__nanosleep(200);
+			continue;
+		}
+
+		int settled = 0;   // items (or the tile unit) this lane finishes: comes off the frame's outstanding work
+		if (kind == WORK_UNIT) {
+			const long long unit_begin = clock64();
+			int local_tile, px, py;
+			const bool inside = unit_pixel(P, first, lane, local_tile, px, py);
+			Ray ray;
+			if (inside) { ray = primary_ray(P, px, py); primary++; }
+			process_bounce<MAXB, BSTACK>(P, out, counters, inside, ray, P.bounces, -(px + P.width * py + 1), 0, cnt);
+			__syncwarp();
+			if (lane == 0) { atomicAdd(P.tile_cost + local_tile, unsigned((clock64() - unit_begin) >> 6)); settled = 1; }   // the unit itself
+		} else if (kind == WORK_BOUNCE) {
+			bool active = unsigned(lane) < n;
+			Ray ray; int parent = 0, which = 0, bounces_left = 0;
+			if (active) {
+				const unsigned slot = first + unsigned(lane);
+				while (__ldcg(P.q_bounce_ready + slot) != P.frame_serial) __nanosleep(20);   // reserved before it was written: a moment
+				__threadfence();
+				read_bounce_item(P, slot, ray, parent, which, bounces_left);
+				if (parent == QUEUE_NULL_ITEM) active = false; else settled = 1;
+			}
+			process_bounce<MAXB, BSTACK>(P, out, counters, active, ray, bounces_left, parent, which, cnt);
+		} else { // WORK_SHADOW
+			if (unsigned(lane) < n) {
+				const unsigned slot = first + unsigned(lane);
+				while (__ldcg(P.q_shadow_ready + slot) != P.frame_serial) __nanosleep(20);
+				__threadfence();
+				const float4 a = __ldcg(P.q_shadow + 2 * size_t(slot)), b = __ldcg(P.q_shadow + 2 * size_t(slot) + 1);
+				const int word = as_i(b.w);
+				if (word != QUEUE_NULL_ITEM) {
+					deliver_shadow(P, out, word >> 5, word & 31, trace_any<false, BSTACK>(P, V(a), V(b), a.w, cnt));
+					settled = 1;
+				}
+			}
+		}
+		warp_add(&counters->q_outstanding, -settled);   // what this warp queued was added before it became visible (process_bounce)
+	}
+
+	if (lane == 0) {
+		const unsigned long long now = global_timer_ns();
+		if (!was_idle) atomicMax(&counters->first_idle_ns, ~now);
+		atomicMax(&counters->last_done_ns, now);
+	}
+	flush_ray_counters(counters, cnt, primary, false);
+}
+
 // Next frame's hand-out order from this frame's measured tile costs: most expensive first (counting
 // sort over 256 logarithmic cost classes, one block), so that the launch does not end with a few
 // warps inside a costly tile and the rest of the GPU idle. Any order gives the same image; the
-// reference's countdown uses index order (WorkerThread.cpp:53-58). Resets the costs.
+// reference's countdown uses index order (WorkerThread.cpp:53-58). Resets the costs, and the NEXT frame's counter block.
 // Measured (tools/tail_probe.py, bench frame): time with some warps already out of work 0.17 -> 0.08
 // ms on one GPU's share of the frame. Splitting expensive tiles into 8-pixel items as well was tried
 // and dropped: what bounds a costly unit is the serial recursion of its most expensive PIXEL
 // (~0.3 ms), so narrower warps only multiplied the warp-time.
 __global__ void __launch_bounds__(1024)
-tile_schedule_kernel(unsigned * __restrict__ tile_cost, unsigned * __restrict__ tile_order, int tile_count) {
+tile_schedule_kernel(unsigned * __restrict__ tile_cost, unsigned * __restrict__ tile_order, int tile_count, FrameCounters * __restrict__ next_counters) {
 	__shared__ unsigned histogram[256];
+	reset_counters(next_counters, unsigned(tile_count) * 32u);
 	__shared__ unsigned offset[256];
 	for (int i = threadIdx.x; i < 256; i += blockDim.x) histogram[i] = 0;
 	__syncthreads();
@@ -162,7 +238,7 @@ primary_hits_kernel(const SceneParams P, int * __restrict__ ids, float * __restr
 	const Ray ray = primary_ray(P, px, py);
 	Counters cnt = { 0, 0, 0, 0, 0, 0, 0, 0 };
 	Candidate best;
-	trace_closest<false>(P, ray.origin, ray.direction, best, cnt);
+	trace_closest<false, 64>(P, ray.origin, ray.direction, best, cnt);
 
 	const size_t p = size_t(px) + size_t(P.width) * py;
 	const bool is_hit = best.instance != HIT_NONE;
@@ -299,4 +375,4 @@ fxaa_kernel(const unsigned * __restrict__ fb, unsigned char * __restrict__ rgb8,
 	}
 }
 
-} // namespace rt
+} // namespace RT_NAMESPACE

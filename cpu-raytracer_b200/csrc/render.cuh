@@ -1,20 +1,23 @@
-// render.cuh — the frame kernels: Whitted ray tracing over all tiles, primary-hit dump, FXAA.
+// render.cuh — Raytracer::bounce for one ray per thread, in two forms that produce the same bits:
+//   shade_subtree   the whole ray tree of one call of bounce() walked depth-first by ONE thread with an explicit
+//                   frame stack (what every pixel used in round 1);
+//   process_bounce  ONE call of bounce() as a work item: closest hit, hit record, albedo, then the node's children
+//                   (reflection / refraction rays) and its shadow rays go to device-side queues as items of their
+//                   own, and the node's value is assembled bottom-up when the last of them has reported (the
+//                   deep-pixel queue; kernels.cuh has the loop that feeds persistent warps from the queues).
 //
-// Reference: Raytracer::render_tile (Raytracer.cpp:3-85), Raytracer::bounce (:87-400),
-// WorkerThreads tile hand-out (WorkerThread.cpp:49-69), Window::plot (Window.h:56-65),
-// Data/Shaders/fragment_fxaa.glsl.
+// Reference: Raytracer::render_tile (Raytracer.cpp:3-85), Raytracer::bounce (:87-400), Window::plot (Window.h:56-65).
 #pragma once
 #include "shade.cuh"
 
-namespace rt {
+namespace RT_NAMESPACE {
 
-#define RT_MAX_BOUNCES 8
 #ifndef RT_BLOCK_THREADS
 #define RT_BLOCK_THREADS 256
 #endif
 #ifndef RT_MIN_BLOCKS
 #define RT_MIN_BLOCKS 4   // resident 256-thread blocks per SM the register allocation is sized for: 64 registers, 32 warps/SM.
-                          // Measured on the bench frame (gpurun_out/r1_variants_*.log): 2 -> 1.87 ms, 3 -> 1.53, 4 -> 1.46, 5 -> 1.48, 6 -> 1.57, 8 -> 1.69
+                          // Measured on the bench frame (profiles/r01_variants_traversal.log): 2 -> 1.87 ms, 3 -> 1.53, 4 -> 1.46, 5 -> 1.48, 6 -> 1.57, 8 -> 1.69
 #endif
 
 // Raytracer::render_tile, Raytracer.cpp:45-59: primary ray + its differentials for pixel (i, j)
@@ -56,6 +59,134 @@ __device__ __forceinline__ unsigned plot_colour(v3 colour) {
 	return (q[0] << 16) | (q[1] << 8) | q[2];
 }
 
+// Where a pixel of row py goes when the frame is exchanged in bands (include/b200rt.h:
+// b200rt_set_band_targets): into the image of the GPU that owns the row's band and, within band_halo
+// rows of a band border, into the neighbour's too — cyclically, because the FXAA taps wrap at the
+// frame border (GL_REPEAT, Window.cpp:48-50). Plain stores over NVLink peer memory: the exchange
+// rides on the kernel's last instruction, every link carries 1/N of the frame, nobody gathers.
+__device__ __forceinline__ void store_pixel_banded(const SceneParams & P, size_t p, int py, unsigned value) {
+	const int last = P.band_count - 1;
+	int b = py / P.band_rows;
+	if (b > last) b = last;
+	P.band_targets[b][p] = value;
+	const int begin = b * P.band_rows, end = b == last ? P.height : begin + P.band_rows;
+	if (py - begin < P.band_halo) P.band_targets[b == 0 ? last : b - 1][p] = value;
+	if (end - py <= P.band_halo)  P.band_targets[b == last ? 0 : b + 1][p] = value;
+}
+
+// The one place a finished pixel is written (by the thread that traced it, or by whichever thread completed
+// the root node of a queued pixel).
+struct PixelOut { unsigned * frame_buffer; float * colour_float; };
+__device__ __forceinline__ void write_pixel(const SceneParams & P, const PixelOut & out, int px, int py, v3 colour) {
+	const size_t p = size_t(px) + size_t(P.width) * py;
+	if (P.band_count == 0) out.frame_buffer[p] = plot_colour(colour);
+	else store_pixel_banded(P, p, py, plot_colour(colour));
+	if (out.colour_float) { out.colour_float[3 * p] = colour.x; out.colour_float[3 * p + 1] = colour.y; out.colour_float[3 * p + 2] = colour.z; }
+}
+
+// ---------------------------------------------------------------- pieces of bounce() both forms share ---
+enum { FRAME_AFTER_REFLECTION = 1, FRAME_AFTER_REFRACTION = 2, FRAME_HAS_REFRACTION = 4, FRAME_TIR = 8, FRAME_ENTERING = 16, FRAME_HAS_REFLECTION = 32 };
+
+// One light seen from a hit point: direction and length of the shadow ray (Raytracer.cpp:155-198; DirectionalLight.h:9-11)
+struct LightSample { float4 l0, l1, l2; v3 to_light; float distance, distance_squared; int kind; };
+__device__ __forceinline__ void light_sample(const SceneParams & P, int i, v3 point, LightSample & s) {
+	s.l0 = __ldg(&P.lights[i].colour_kind); s.l1 = __ldg(&P.lights[i].position_inner); s.l2 = __ldg(&P.lights[i].negdir_outer);
+	s.kind = __float_as_int(s.l0.w);
+	s.distance = CUDART_INF_F; s.distance_squared = 0.0f;
+	if (s.kind == 2) {
+		s.to_light = V(s.l2);
+	} else {
+		s.to_light = V(s.l1) - point;
+		s.distance_squared = dot(s.to_light, s.to_light);
+		s.distance         = sqrtf(s.distance_squared);
+		s.to_light = divf(s.to_light, s.distance);
+	}
+}
+// diffuse + what an unoccluded light adds (PointLight.h:9-11, SpotLight.h:17-33, DirectionalLight.h:9-11)
+__device__ __forceinline__ v3 light_add(v3 diffuse, const LightSample & s, v3 normal, v3 to_camera) {
+	if (s.kind == 2) return diffuse + light_base(V(s.l0), normal, s.to_light, to_camera);
+	v3 lighting = divf(light_base(V(s.l0), normal, s.to_light, to_camera), s.distance_squared);
+	if (s.kind == 1) {
+		const float d = dot(s.to_light, V(s.l2));
+		if (!(d > s.l2.w)) lighting = V(0.0f, 0.0f, 0.0f);
+		else {
+			float radial_falloff = (d - s.l2.w) / (s.l1.w - s.l2.w);
+			if (radial_falloff > 1.0f) radial_falloff = 1.0f;
+			lighting = lighting * radial_falloff;
+		}
+	}
+	return diffuse + lighting;
+}
+__device__ __forceinline__ v3 lit_result(v3 diffuse, v3 material_diffuse) { // result = madd(diffuse, material_diffuse, result = 0), :200
+	return V(__fmaf_rn(diffuse.x, material_diffuse.x, 0.0f), __fmaf_rn(diffuse.y, material_diffuse.y, 0.0f), __fmaf_rn(diffuse.z, material_diffuse.z, 0.0f));
+}
+
+// Everything about the refraction branch that only depends on this hit (Raytracer.cpp:273-342, Schlick :379-391).
+// Returns the FRAME_* flags of the branch; `refracted` and F_r are filled unless the hit reflects totally.
+__device__ __forceinline__ int refraction_setup(const Ray & ray, const HitRecord & hit, float ior, float d_dot_n, float dDN_dx, float dDN_dy, Ray & refracted, float & F_r) {
+	int flags = FRAME_HAS_REFRACTION;
+	const bool entering = d_dot_n < 0.0f;
+	if (entering) flags |= FRAME_ENTERING;
+
+	const float n_1 = entering ? 1.0f : ior;
+	const float n_2 = entering ? ior : 1.0f;
+
+	float    cos_theta = entering ? 0.0f - d_dot_n : d_dot_n;
+	const v3 normal    = entering ? hit.normal : neg(hit.normal);
+
+	const float eta = n_1 / n_2;
+	const float k   = 1.0f - (eta * eta * (1.0f - (cos_theta * cos_theta)));
+
+	if (k < 0.0f) return flags | FRAME_TIR; // :310-314
+
+	refracted.origin    = hit.point;
+	refracted.direction = ray.direction * eta + normal * ((eta * cos_theta) - sqrtf(k)); // Math::refract, Math.h:34-36
+	refracted.dO_dx = hit.dO_dx;
+	refracted.dO_dy = hit.dO_dy;
+
+	const float D_dot_N      = 0.0f - cos_theta;
+	const float Dprime_dot_N = 0.0f - sqrtf(k);
+	const float mu = 0.0f - (eta * cos_theta + Dprime_dot_N);
+
+	// :341-342, float + vector broadcast and all
+	refracted.dD_dx = ray.dD_dx * eta - addf(hit.dN_dx * hit.normal, mu * D_dot_N) * dDN_dx;
+	refracted.dD_dy = ray.dD_dy * eta - addf(hit.dN_dy * hit.normal, mu * D_dot_N) * dDN_dy;
+
+	float r_0 = (n_1 - n_2) / (n_1 + n_2);
+	r_0 = r_0 * r_0;
+	if (n_1 > n_2) cos_theta = 0.0f - dot(refracted.direction, normal);
+
+	const float one_minus_cos         = 1.0f - cos_theta;
+	const float one_minus_cos_squared = one_minus_cos * one_minus_cos;
+	F_r = r_0 + ((1.0f - r_0) * one_minus_cos_squared) * (one_minus_cos_squared * one_minus_cos);
+	return flags;
+}
+// :249-271
+__device__ __forceinline__ Ray reflection_ray(const Ray & ray, const HitRecord & hit, float d_dot_n, float dDN_dx, float dDN_dy) {
+	Ray reflected;
+	reflected.origin    = hit.point;
+	reflected.direction = ray.direction - hit.normal * (2.0f * d_dot_n); // Math::reflect, Math.h:28-31
+	reflected.dO_dx = hit.dO_dx;
+	reflected.dO_dy = hit.dO_dy;
+	reflected.dD_dx = ray.dD_dx - (hit.dN_dx * d_dot_n + hit.normal * dDN_dx) * 2.0f;
+	reflected.dD_dy = ray.dD_dy - (hit.dN_dy * d_dot_n + hit.normal * dDN_dy) * 2.0f;
+	return reflected;
+}
+// The refraction child returned: Beer's law with the child's hit distance (:350-376), Fresnel blend (:393-395)
+__device__ __forceinline__ v3 refraction_blend(const SceneParams & P, int material_id, int flags, float F_r, v3 result, v3 colour_reflection, v3 returned, float returned_distance) {
+	v3 colour_refraction = returned;
+	if (flags & FRAME_ENTERING) {
+		const float4 m2 = __ldg(reinterpret_cast<const float4 *>(P.materials + material_id) + 2);
+		colour_refraction.x = colour_refraction.x * expf((m2.x - 1.0f) * returned_distance);
+		colour_refraction.y = colour_refraction.y * expf((m2.y - 1.0f) * returned_distance);
+		colour_refraction.z = colour_refraction.z * expf((m2.z - 1.0f) * returned_distance);
+	}
+	const float F_t = 1.0f - F_r;
+	const v3 blend = colour_reflection * F_r + colour_refraction * F_t; // :393
+	return result + blend;                                               // :395
+}
+
+// ------------------------------------------------------------------------- depth-first, one thread ---
 // One pending level of Raytracer::bounce's recursion (:204-397), kept in local memory. The
 // recursion is binary (reflection, then refraction) and is unrolled depth-first with the same
 // association of every sum as the reference, so the colour is bit-identical to the recursive form.
@@ -68,14 +199,14 @@ struct BounceFrame {
 	int   material_id;
 	int   flags;             // see FRAME_*
 };
-enum { FRAME_AFTER_REFLECTION = 1, FRAME_AFTER_REFRACTION = 2, FRAME_HAS_REFRACTION = 4, FRAME_TIR = 8, FRAME_ENTERING = 16 };
 
-// Raytracer::bounce for one primary ray, iteratively. Returns the pixel colour.
-template<bool COUNT>
-__device__ v3 shade_pixel(const SceneParams & P, Ray ray, Counters & cnt) {
-	BounceFrame frames[RT_MAX_BOUNCES];
+// bounce(ray, bounces_left), iteratively: returns the colour; distance_out = the hit distance bounce() hands to its
+// caller (Beer's law one level up). MAXB = frames reserved (>= bounces_left). first_hit: the closest hit of `ray`
+// when the caller has traced it already.
+template<bool COUNT, int MAXB, int BSTACK>
+__device__ __forceinline__ v3 shade_subtree_body(const SceneParams & P, Ray ray, int bounces_left, Counters & cnt, float & distance_out, const Candidate * first_hit) {
+	BounceFrame frames[MAXB];
 	int depth = 0;                // number of pending frames = recursion depth of the current ray
-	int bounces_left = P.bounces;
 
 	v3    returned;               // value of the bounce() call that just finished
 	float returned_distance;
@@ -83,7 +214,8 @@ __device__ v3 shade_pixel(const SceneParams & P, Ray ray, Counters & cnt) {
 	for (;;) {
 		// ---- bounce(ray, bounces_left): Raytracer.cpp:87-201 ---------------------------------
 		Candidate best;
-		trace_closest<COUNT>(P, ray.origin, ray.direction, best, cnt);
+		if (first_hit) { best = *first_hit; first_hit = nullptr; }
+		else trace_closest<COUNT, BSTACK>(P, ray.origin, ray.direction, best, cnt);
 
 		bool descend = false;
 
@@ -104,39 +236,14 @@ __device__ v3 shade_pixel(const SceneParams & P, Ray ray, Counters & cnt) {
 				const v3 to_camera = normalize(V(P.cam_position[0], P.cam_position[1], P.cam_position[2]) - hit.point);
 
 				for (int i = 0; i < P.light_count; i++) { // point, then spot, then directional (:155-198)
-					const float4 l0 = __ldg(&P.lights[i].colour_kind), l1 = __ldg(&P.lights[i].position_inner), l2 = __ldg(&P.lights[i].negdir_outer);
-					const int kind = __float_as_int(l0.w);
+					LightSample s;
+					light_sample(P, i, hit.point, s);
 					cnt.shadow++;
-
 					// one shadow query for all three kinds (a single inlined copy of the traversal)
-					v3 to_light; float distance_to_light = CUDART_INF_F, distance_to_light_squared = 0.0f;
-					if (kind == 2) { // DirectionalLight.h:9-11
-						to_light = V(l2);
-					} else {
-						to_light = V(l1) - hit.point;
-						distance_to_light_squared = dot(to_light, to_light);
-						distance_to_light         = sqrtf(distance_to_light_squared);
-						to_light = divf(to_light, distance_to_light);
-					}
-					if (trace_any<COUNT>(P, hit.point, to_light, distance_to_light, cnt)) continue;
-
-					if (kind == 2) {
-						diffuse = diffuse + light_base(V(l0), hit.normal, to_light, to_camera);
-					} else {
-						v3 lighting = divf(light_base(V(l0), hit.normal, to_light, to_camera), distance_to_light_squared); // PointLight.h:9-11
-						if (kind == 1) { // SpotLight.h:17-33
-							const float d = dot(to_light, V(l2));
-							if (!(d > l2.w)) lighting = V(0.0f, 0.0f, 0.0f);
-							else {
-								float radial_falloff = (d - l2.w) / (l1.w - l2.w);
-								if (radial_falloff > 1.0f) radial_falloff = 1.0f;
-								lighting = lighting * radial_falloff;
-							}
-						}
-						diffuse = diffuse + lighting;
-					}
+					if (trace_any<COUNT, BSTACK>(P, hit.point, s.to_light, s.distance, cnt)) continue;
+					diffuse = light_add(diffuse, s, hit.normal, to_camera);
 				}
-				result = V(__fmaf_rn(diffuse.x, material_diffuse.x, result.x), __fmaf_rn(diffuse.y, material_diffuse.y, result.y), __fmaf_rn(diffuse.z, material_diffuse.z, result.z)); // :200
+				result = lit_result(diffuse, material_diffuse); // :200
 			}
 
 			returned = result;
@@ -161,57 +268,10 @@ __device__ v3 shade_pixel(const SceneParams & P, Ray ray, Counters & cnt) {
 					const float dDN_dx = dot(ray.dD_dx, hit.normal) + dot(ray.direction, hit.dN_dx);
 					const float dDN_dy = dot(ray.dD_dy, hit.normal) + dot(ray.direction, hit.dN_dy);
 
-					if (refraction_mask) { // :273-342 — everything that only depends on this hit
-						flags |= FRAME_HAS_REFRACTION;
-						const bool entering = d_dot_n < 0.0f;
-						if (entering) flags |= FRAME_ENTERING;
-
-						const float ior = m1.w;
-						const float n_1 = entering ? 1.0f : ior;
-						const float n_2 = entering ? ior : 1.0f;
-
-						float    cos_theta = entering ? 0.0f - d_dot_n : d_dot_n;
-						const v3 normal    = entering ? hit.normal : neg(hit.normal);
-
-						const float eta = n_1 / n_2;
-						const float k   = 1.0f - (eta * eta * (1.0f - (cos_theta * cos_theta)));
-
-						if (k < 0.0f) flags |= FRAME_TIR; // :310-314
-						else {
-							Ray & refracted = frame.refracted;
-							refracted.origin    = hit.point;
-							refracted.direction = ray.direction * eta + normal * ((eta * cos_theta) - sqrtf(k)); // Math::refract, Math.h:34-36
-							refracted.dO_dx = hit.dO_dx;
-							refracted.dO_dy = hit.dO_dy;
-
-							const float D_dot_N      = 0.0f - cos_theta;
-							const float Dprime_dot_N = 0.0f - sqrtf(k);
-							const float mu = 0.0f - (eta * cos_theta + Dprime_dot_N);
-
-							// :341-342, float + vector broadcast and all
-							refracted.dD_dx = ray.dD_dx * eta - addf(hit.dN_dx * hit.normal, mu * D_dot_N) * dDN_dx;
-							refracted.dD_dy = ray.dD_dy * eta - addf(hit.dN_dy * hit.normal, mu * D_dot_N) * dDN_dy;
-
-							// Schlick, :379-391
-							float r_0 = (n_1 - n_2) / (n_1 + n_2);
-							r_0 = r_0 * r_0;
-							if (n_1 > n_2) cos_theta = 0.0f - dot(refracted.direction, normal);
-
-							const float one_minus_cos         = 1.0f - cos_theta;
-							const float one_minus_cos_squared = one_minus_cos * one_minus_cos;
-							frame.F_r = r_0 + ((1.0f - r_0) * one_minus_cos_squared) * (one_minus_cos_squared * one_minus_cos);
-						}
-					}
+					if (refraction_mask) flags |= refraction_setup(ray, hit, m1.w, d_dot_n, dDN_dx, dDN_dy, frame.refracted, frame.F_r);
 
 					if (reflection_mask) { // :249-271
-						Ray reflected;
-						reflected.origin    = hit.point;
-						reflected.direction = ray.direction - hit.normal * (2.0f * d_dot_n); // Math::reflect, Math.h:28-31
-						reflected.dO_dx = hit.dO_dx;
-						reflected.dO_dy = hit.dO_dy;
-						reflected.dD_dx = ray.dD_dx - (hit.dN_dx * d_dot_n + hit.normal * dDN_dx) * 2.0f;
-						reflected.dD_dy = ray.dD_dy - (hit.dN_dy * d_dot_n + hit.normal * dDN_dy) * 2.0f;
-
+						const Ray reflected = reflection_ray(ray, hit, d_dot_n, dDN_dx, dDN_dy);
 						cnt.reflection++;
 						frame.flags = flags | FRAME_AFTER_REFLECTION;
 						ray = reflected;
@@ -257,23 +317,293 @@ __device__ v3 shade_pixel(const SceneParams & P, Ray ray, Counters & cnt) {
 					break;
 				}
 			} else { // FRAME_AFTER_REFRACTION
-				v3 colour_refraction = returned;
-				if (frame.flags & FRAME_ENTERING) { // Beer's law with the child's hit distance, :350-376
-					const float4 m2 = __ldg(reinterpret_cast<const float4 *>(P.materials + frame.material_id) + 2);
-					colour_refraction.x = colour_refraction.x * expf((m2.x - 1.0f) * returned_distance);
-					colour_refraction.y = colour_refraction.y * expf((m2.y - 1.0f) * returned_distance);
-					colour_refraction.z = colour_refraction.z * expf((m2.z - 1.0f) * returned_distance);
-				}
-				const float F_r = frame.F_r, F_t = 1.0f - F_r;
-				const v3 blend = frame.colour_reflection * F_r + colour_refraction * F_t; // :393
-				returned = frame.result + blend;                                          // :395
+				returned = refraction_blend(P, frame.material_id, frame.flags, frame.F_r, frame.result, frame.colour_reflection, returned, returned_distance);
 				returned_distance = frame.distance;
 				depth--; bounces_left++;
 			}
 		}
 		if (!descend) break;
 	}
+	distance_out = returned_distance;
 	return returned;
 }
+// inlined into the kernel that does nothing else (no queue: the code of round 1) ...
+template<bool COUNT, int MAXB, int BSTACK>
+__device__ __forceinline__ v3 shade_subtree(const SceneParams & P, const Ray & ray, int bounces_left, Counters & cnt, float & distance_out) {
+	return shade_subtree_body<COUNT, MAXB, BSTACK>(P, ray, bounces_left, cnt, distance_out, nullptr);
+}
+// ... and ONE out-of-line copy for the queue kernel, which reaches it from four places (instruction fetch had shown
+// up with two inlined copies of the traversal in round 1: DESIGN.md 4)
+template<int MAXB, int BSTACK>
+__device__ __noinline__ v3 shade_subtree_call(const SceneParams & P, const Ray & ray, int bounces_left, Counters & cnt, float & distance_out, const Candidate * first_hit) {
+	return shade_subtree_body<false, MAXB, BSTACK>(P, ray, bounces_left, cnt, distance_out, first_hit);
+}
 
-} // namespace rt
+// ------------------------------------------------------------------------------ deep-pixel queue ---
+// North_star's "wavefront traversal with ray compaction", restricted to where it pays: a pixel whose primary ray hits
+// glass is not walked by one thread. Every call of bounce() in its ray tree becomes a NODE RECORD in HBM and every ray
+// an ITEM in one of two device-side queues (bounce rays: closest hit + shading; shadow rays: any hit), which all
+// persistent warps pop 32 at a time (kernels.cuh) — so a warp always holds 32 rays of ONE kind (the compaction), the
+// shadow rays leave the pixel's critical chain (which rays are spawned never depends on a shadow ray's answer), and
+// the sibling subtrees of a fan-out run side by side on whatever warps are idle. A node's value is assembled when the
+// last of its shadow rays and children has reported (a countdown in the record), by the reporting thread, with the
+// reference's sums in the reference's order: the same bits as the recursive form.
+//
+//   node record  6 x float4   {parent, flags | which << 8, pending, material id} {point, distance} {normal, F_r}
+//                             {albedo, occluded-light bits} {reflection child's colour, -} {refraction child's colour, its distance}
+//   bounce item  5 x float4   the Ray (18 floats), parent node, which | bounces_left << 1     (parent = QUEUE_NULL_ITEM: skip)
+//   shadow item  2 x float4   {origin, max distance} {direction, node << 5 | light}           (word = QUEUE_NULL_ITEM: skip)
+// An item is visible to consumers once its word in the queue's `ready` array holds the frame's serial number (written
+// after a __threadfence()). Records and items are bump-allocated per frame; when a pool is exhausted the producer
+// walks the subtree itself (shade_subtree): always correct, never blocked. Records and items are read and written
+// with .cg accesses (L2 only): another SM's L1 may hold a stale copy of the line.
+#define RT_QUEUE_MAX_LIGHTS 24
+#define QUEUE_NULL_ITEM int(0x80000000u)
+
+__device__ __forceinline__ float as_f(int v) { return __int_as_float(v); }
+__device__ __forceinline__ int   as_i(float v) { return __float_as_int(v); }
+
+// Value of a node whose shadow rays and children have all reported (the record is complete and no longer written).
+__device__ __forceinline__ v3 node_value(const SceneParams & P, const float4 * rec, float & distance_out, int & parent, int & which) {
+	const float4 r0 = __ldcg(rec), r1 = __ldcg(rec + 1), r2 = __ldcg(rec + 2), r3 = __ldcg(rec + 3);
+	parent = as_i(r0.x);
+	const int flags = as_i(r0.y) & 0xff; which = (as_i(r0.y) >> 8) & 1;
+	const int material_id = as_i(r0.w);
+	const v3 point = V(r1), normal = V(r2), material_diffuse = V(r3);
+	const unsigned occluded = unsigned(as_i(r3.w));
+	distance_out = r1.w;
+
+	v3 result = V(0.0f, 0.0f, 0.0f);
+	if (dot(material_diffuse, material_diffuse) > 0.0f) {
+		v3 diffuse = V(P.ambient[0], P.ambient[1], P.ambient[2]);
+		const v3 to_camera = normalize(V(P.cam_position[0], P.cam_position[1], P.cam_position[2]) - point);
+		for (int i = 0; i < P.light_count; i++) {
+			if ((occluded >> i) & 1u) continue;
+			LightSample s;
+			light_sample(P, i, point, s);
+			diffuse = light_add(diffuse, s, normal, to_camera);
+		}
+		result = lit_result(diffuse, material_diffuse);
+	}
+	v3 colour_reflection = V(0.0f, 0.0f, 0.0f);
+	if (flags & FRAME_HAS_REFLECTION) {
+		const float4 m1 = __ldg(reinterpret_cast<const float4 *>(P.materials + material_id) + 1);
+		colour_reflection = V(m1) * V(__ldcg(rec + 4));
+		result = result + colour_reflection;
+		if (!(flags & FRAME_HAS_REFRACTION)) return result;
+		if (flags & FRAME_TIR) return result + colour_reflection;
+	} else if (!(flags & FRAME_HAS_REFRACTION) || (flags & FRAME_TIR)) {
+		return result;
+	}
+	const float4 r5 = __ldcg(rec + 5);
+	return refraction_blend(P, material_id, flags, r2.w, result, colour_reflection, V(r5), r5.w);
+}
+
+// A child's colour (and hit distance) goes into its parent's record; whoever brings a record's countdown to zero
+// computes the node's value and carries it one level up — up to the pixel.
+__device__ __noinline__ void deliver(const SceneParams & P, const PixelOut & out, int parent, int which, v3 value, float distance) {
+	for (;;) {
+		if (parent < 0) { // the root's parent is the pixel
+			const int p = -(parent + 1);
+			write_pixel(P, out, p % P.width, p / P.width, value);
+			return;
+		}
+		float4 * rec = P.q_nodes + 6 * size_t(parent);
+		__stcg(rec + 4 + which, make_float4(value.x, value.y, value.z, distance));
+		__threadfence();
+		if (atomicSub(reinterpret_cast<int *>(rec) + 2, 1) != 1) return;
+		__threadfence();
+		value = node_value(P, rec, distance, parent, which);
+	}
+}
+__device__ __forceinline__ void deliver_shadow(const SceneParams & P, const PixelOut & out, int node, int light, bool occluded) {
+	float4 * rec = P.q_nodes + 6 * size_t(node);
+	if (occluded) atomicOr(reinterpret_cast<unsigned *>(rec) + 15, 1u << light);
+	__threadfence();
+	if (atomicSub(reinterpret_cast<int *>(rec) + 2, 1) != 1) return;
+	__threadfence();
+	float distance; int parent, which;
+	const v3 value = node_value(P, rec, distance, parent, which);
+	deliver(P, out, parent, which, value, distance);
+}
+
+// Warp-collective reservation of n slots per lane in a bump-allocated pool: one atomicAdd per warp.
+// Returns the first slot of this lane; slots at or beyond the pool's capacity do not exist (the caller falls back).
+__device__ __forceinline__ unsigned warp_reserve(unsigned * counter, unsigned n) {
+	const int lane = threadIdx.x & 31;
+	unsigned before = n;
+#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) { const unsigned v = __shfl_up_sync(0xffffffffu, before, o); if (lane >= o) before += v; }
+	const unsigned total = __shfl_sync(0xffffffffu, before, 31);
+	unsigned base = 0;
+	if (lane == 0 && total) base = atomicAdd(counter, total);
+	base = __shfl_sync(0xffffffffu, base, 0);
+	return base + before - n;
+}
+
+// Warp-collective counter update: one atomicAdd per warp.
+__device__ __forceinline__ void warp_add(int * counter, int n) {
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+	if ((threadIdx.x & 31) == 0 && n != 0) atomicAdd(counter, n);
+}
+__device__ __forceinline__ unsigned peek(const unsigned * p) { return *reinterpret_cast<const volatile unsigned *>(p); }   // a fresh value, not this SM's L1 copy
+__device__ __forceinline__ int      peek(const int * p)      { return *reinterpret_cast<const volatile int *>(p); }
+
+__device__ __forceinline__ void publish(unsigned * ready, unsigned slot, unsigned serial) {
+	__threadfence();
+	__stcg(ready + slot, serial);
+}
+__device__ __forceinline__ void write_bounce_item(const SceneParams & P, unsigned slot, const Ray & r, int parent, int which, int bounces_left) {
+	float4 * item = P.q_bounce + 5 * size_t(slot);
+	__stcg(item,     make_float4(r.origin.x, r.origin.y, r.origin.z, r.direction.x));
+	__stcg(item + 1, make_float4(r.direction.y, r.direction.z, r.dO_dx.x, r.dO_dx.y));
+	__stcg(item + 2, make_float4(r.dO_dx.z, r.dO_dy.x, r.dO_dy.y, r.dO_dy.z));
+	__stcg(item + 3, make_float4(r.dD_dx.x, r.dD_dx.y, r.dD_dx.z, r.dD_dy.x));
+	__stcg(item + 4, make_float4(r.dD_dy.y, r.dD_dy.z, as_f(parent), as_f(which | (bounces_left << 1))));
+	publish(P.q_bounce_ready, slot, P.frame_serial);
+}
+__device__ __forceinline__ void read_bounce_item(const SceneParams & P, unsigned slot, Ray & r, int & parent, int & which, int & bounces_left) {
+	const float4 * item = P.q_bounce + 5 * size_t(slot);
+	const float4 a = __ldcg(item), b = __ldcg(item + 1), c = __ldcg(item + 2), d = __ldcg(item + 3), e = __ldcg(item + 4);
+	r.origin = V(a.x, a.y, a.z); r.direction = V(a.w, b.x, b.y);
+	r.dO_dx = V(b.z, b.w, c.x); r.dO_dy = V(c.y, c.z, c.w);
+	r.dD_dx = V(d.x, d.y, d.z); r.dD_dy = V(d.w, e.x, e.y);
+	parent = as_i(e.z); which = as_i(e.w) & 1; bounces_left = as_i(e.w) >> 1;
+}
+__device__ __forceinline__ void write_null_bounce_item(const SceneParams & P, unsigned slot) {
+	__stcg(P.q_bounce + 5 * size_t(slot) + 4, make_float4(0.0f, 0.0f, as_f(QUEUE_NULL_ITEM), 0.0f));
+	publish(P.q_bounce_ready, slot, P.frame_serial);
+}
+__device__ __forceinline__ void write_shadow_item(const SceneParams & P, unsigned slot, v3 origin, v3 direction, float max_distance, int word) {
+	float4 * item = P.q_shadow + 2 * size_t(slot);
+	__stcg(item,     make_float4(origin.x, origin.y, origin.z, max_distance));
+	__stcg(item + 1, make_float4(direction.x, direction.y, direction.z, as_f(word)));
+	publish(P.q_shadow_ready, slot, P.frame_serial);
+}
+
+// One call of bounce() as a work item. WARP-COLLECTIVE: all 32 lanes call it; `active` lanes carry a ray.
+// parent < 0: the ray is the primary ray of pixel -(parent + 1). The items it queues are added to the frame's count of
+// outstanding work (FrameCounters::q_outstanding) BEFORE they become visible, so the count never runs low; the caller
+// subtracts the item (or tile unit) this call finishes (kernels.cuh).
+template<int MAXB, int BSTACK>
+__device__ __forceinline__ void process_bounce(const SceneParams & P, const PixelOut & out, FrameCounters * counters, bool active, const Ray & ray, int bounces_left, int parent, int which, Counters & cnt) {
+	// ---- closest hit, hit record, albedo, which rays this node spawns -------------------------------
+	Candidate best;
+	HitRecord hit;
+	v3 material_diffuse = V(0.0f, 0.0f, 0.0f);
+	int flags = 0;
+	float F_r = 0.0f;
+	bool want_node = false;
+	Ray reflected, refracted;
+
+	best.t = 0.0f; best.instance = HIT_NONE;
+	if (active) {
+		trace_closest<false, BSTACK>(P, ray.origin, ray.direction, best, cnt);
+		if (best.instance == HIT_NONE) {
+			deliver(P, out, parent, which, sky_sample<false>(P, ray.direction, cnt), CUDART_INF_F);
+			active = false;
+		}
+	}
+	if (active) {
+		build_record(P, ray, best, hit);
+		const float4 * mp = reinterpret_cast<const float4 *>(P.materials + hit.material_id);
+		material_diffuse = get_albedo<false>(P, __ldg(mp), hit, cnt);
+
+		bool reflection_mask = false, refraction_mask = false;
+		float4 m1 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+		if (bounces_left > 0) {
+			m1 = __ldg(mp + 1);
+			const float4 m2 = __ldg(mp + 2);
+			reflection_mask = dot(V(m1), V(m1)) > 0.0f;
+			refraction_mask = dot(V(m2), V(m2)) > 0.0f;
+		}
+		// Who is queued: a primary ray that hits glass (queue_mode 1) or anything with children (queue_mode 2); every ray
+		// below a queued node down to queue_inline_below bounces left. The rest is walked depth-first right here.
+		const bool queued = parent >= 0 ? bounces_left > P.queue_inline_below
+		                                : (P.queue_mode == 2 ? (reflection_mask || refraction_mask) : refraction_mask);
+		if (!queued) {
+			float distance;
+			const v3 value = shade_subtree_call<MAXB, BSTACK>(P, ray, bounces_left, cnt, distance, &best);
+			deliver(P, out, parent, which, value, distance);
+		} else {
+			if (reflection_mask || refraction_mask) {
+				const float d_dot_n = dot(ray.direction, hit.normal);
+				const float dDN_dx = dot(ray.dD_dx, hit.normal) + dot(ray.direction, hit.dN_dx);
+				const float dDN_dy = dot(ray.dD_dy, hit.normal) + dot(ray.direction, hit.dN_dy);
+				if (refraction_mask) flags |= refraction_setup(ray, hit, m1.w, d_dot_n, dDN_dx, dDN_dy, refracted, F_r);
+				if (reflection_mask) { flags |= FRAME_HAS_REFLECTION; reflected = reflection_ray(ray, hit, d_dot_n, dDN_dx, dDN_dy); }
+			}
+			want_node = true;
+		}
+	}
+
+	// ---- node record + items: three pool reservations per warp ----------------------------------------
+	const bool lit = want_node && dot(material_diffuse, material_diffuse) > 0.0f;
+	const int n_children = !want_node ? 0 : ((flags & FRAME_HAS_REFLECTION) ? 1 : 0) + (((flags & FRAME_HAS_REFRACTION) && !(flags & FRAME_TIR)) ? 1 : 0);
+	const int n_shadow   = lit ? P.light_count : 0;
+	if (want_node && n_children + n_shadow == 0) { // nothing to wait for: result = 0 (:141), or ambient * albedo with no lights (:144,:200)
+		v3 result = V(0.0f, 0.0f, 0.0f);
+		if (lit) result = lit_result(V(P.ambient[0], P.ambient[1], P.ambient[2]), material_diffuse);
+		deliver(P, out, parent, which, result, best.t);
+		want_node = false;
+	}
+	const unsigned node_slot   = warp_reserve(&counters->q_node_reserved,   want_node ? 1u : 0u);
+	const unsigned bounce_slot = warp_reserve(&counters->q_bounce_reserved, want_node ? unsigned(n_children) : 0u);
+	const unsigned shadow_slot = warp_reserve(&counters->q_shadow_reserved, want_node ? unsigned(n_shadow) : 0u);
+	warp_add(&counters->q_outstanding, want_node ? n_children + n_shadow : 0);
+	if (!want_node) return;
+
+	if (node_slot >= P.q_node_capacity) { // no record to be had: walk the subtree here; the item slots reserved above are published empty
+		for (int k = 0; k < n_children; k++) if (bounce_slot + k < P.q_bounce_capacity) write_null_bounce_item(P, bounce_slot + k);
+		for (int i = 0; i < n_shadow; i++)   if (shadow_slot + i < P.q_shadow_capacity) write_shadow_item(P, shadow_slot + i, hit.point, hit.normal, 0.0f, QUEUE_NULL_ITEM);
+		float distance;
+		const v3 value = shade_subtree_call<MAXB, BSTACK>(P, ray, bounces_left, cnt, distance, &best);
+		deliver(P, out, parent, which, value, distance);
+		atomicAdd(&counters->q_fallbacks, 1u);
+		atomicSub(&counters->q_outstanding, n_children + n_shadow);
+		return;
+	}
+
+	const int node = int(node_slot);
+	float4 * rec = P.q_nodes + 6 * size_t(node);
+	__stcg(rec,     make_float4(as_f(parent), as_f(flags | (which << 8)), as_f(n_children + n_shadow), as_f(hit.material_id)));
+	__stcg(rec + 1, make_float4(hit.point.x, hit.point.y, hit.point.z, best.t));
+	__stcg(rec + 2, make_float4(hit.normal.x, hit.normal.y, hit.normal.z, F_r));
+	__stcg(rec + 3, make_float4(material_diffuse.x, material_diffuse.y, material_diffuse.z, as_f(0)));
+	// (every item is published behind a __threadfence(): the record is in L2 before an item that names it can be seen)
+
+	unsigned slot = bounce_slot;
+	for (int k = 0; k < 2; k++) { // children (Raytracer.cpp:249-271, :316-342); a child without a slot is walked here
+		const bool present = k == 0 ? (flags & FRAME_HAS_REFLECTION) != 0 : ((flags & FRAME_HAS_REFRACTION) && !(flags & FRAME_TIR));
+		if (!present) continue;
+		if (k == 0) cnt.reflection++; else cnt.refraction++;
+		const Ray & child = k == 0 ? reflected : refracted;
+		if (slot < P.q_bounce_capacity) {
+			write_bounce_item(P, slot, child, node, k, bounces_left - 1);
+		} else {
+			__threadfence();
+			float distance;
+			const v3 value = shade_subtree_call<MAXB, BSTACK>(P, child, bounces_left - 1, cnt, distance, nullptr);
+			deliver(P, out, node, k, value, distance);
+			atomicAdd(&counters->q_fallbacks, 1u);
+			atomicSub(&counters->q_outstanding, 1);
+		}
+		slot++;
+	}
+	for (int i = 0; i < n_shadow; i++) { // shadow rays (:155-198)
+		LightSample s;
+		light_sample(P, i, hit.point, s);
+		cnt.shadow++;
+		if (shadow_slot + i < P.q_shadow_capacity) {
+			write_shadow_item(P, shadow_slot + i, hit.point, s.to_light, s.distance, (node << 5) | i);
+		} else {
+			__threadfence();
+			deliver_shadow(P, out, node, i, trace_any<false, BSTACK>(P, hit.point, s.to_light, s.distance, cnt));
+			atomicAdd(&counters->q_fallbacks, 1u);
+			atomicSub(&counters->q_outstanding, 1);
+		}
+	}
+}
+
+} // namespace RT_NAMESPACE

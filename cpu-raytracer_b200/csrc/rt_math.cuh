@@ -7,11 +7,19 @@
 // is compiled with -fmad=false and spells every fused operation as __fmaf_rn. Division and
 // square root are IEEE (nvcc defaults -prec-div=true -prec-sqrt=true; no --use_fast_math).
 #pragma once
-#include <cuda_runtime.h>
+#include "rt_types.h"
+#ifndef RT_EMULATE
 #include <math_constants.h>
-#include <stdint.h>
+#endif
 
-namespace rt {
+// The kernels are compiled once per arithmetic mode (kernels_tu.cu): rt_exact with -fmad=false, rt_fast with
+// -fmad=true -DRT_FAST. Same source, two namespaces, so both sets of kernels live in one library.
+#ifndef RT_NAMESPACE
+#define RT_NAMESPACE rt_exact
+#endif
+
+namespace RT_NAMESPACE {
+using namespace rt;
 
 #define RT_EPSILON 0.005f               // Ray::EPSILON, Ray.h:5
 #define RT_ONE_OVER_PI     0.31830988618f // Util.h:9
@@ -19,35 +27,28 @@ namespace rt {
 
 struct v3 { float x, y, z; };
 
-// Loads of the two read-only streams a ray pulls through L1: BVH nodes + triangles (re-used by the
-// neighbouring rays of the warp and of the SM: worth keeping) and texels (streamed: 190 MB of
-// pyramids against 256 KB of L1). RT_NODE_HINT / RT_TEXEL_HINT select the cache policy of each
-// (tools/variant_bench.py times the combinations): 0 = ld.global.nc as the compiler emits it,
-// 1 = L1::evict_last, 2 = L1::evict_first, 3 = L1::no_allocate.
-#ifndef RT_NODE_HINT
-#define RT_NODE_HINT 0
-#endif
-#ifndef RT_TEXEL_HINT
-#define RT_TEXEL_HINT 0
-#endif
-template<int HINT>
-__device__ __forceinline__ float4 load_hinted(const float4 * p) {
-	if (HINT == 0) return __ldg(p);
-	float4 r;
-	if (HINT == 1)      asm("ld.global.nc.L1::evict_last.v4.f32 {%0, %1, %2, %3}, [%4];"  : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
-	else if (HINT == 2) asm("ld.global.nc.L1::evict_first.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
-	else                asm("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
-	return r;
-}
-__device__ __forceinline__ float4 load_node(const float4 * p)  { return load_hinted<RT_NODE_HINT>(p); }
-__device__ __forceinline__ float4 load_texel(const float4 * p) { return load_hinted<RT_TEXEL_HINT>(p); }
+// Loads of the two read-only streams a ray pulls through L1: BVH nodes + triangles and texels, both ld.global.nc.
+// (Cache-policy hints — L1::evict_last / evict_first / no_allocate on either stream — were timed in round 1 and
+// changed nothing beyond noise: profiles/r01_variants_cache_hints.log.)
+__device__ __forceinline__ float4 load_node(const float4 * p)  { return __ldg(p); }
+__device__ __forceinline__ float4 load_texel(const float4 * p) { return __ldg(p); }
 // -DRT_PREFETCH_SKIP (experiment, off by default): a threaded record's skip target is known as soon as the record
 // is; asking for its line while the box test runs takes the load off the path of a ray that misses the box.
 __device__ __forceinline__ void prefetch_record(const float4 * p) {
-#ifdef RT_PREFETCH_SKIP
+#if defined(RT_PREFETCH_SKIP) && !defined(RT_EMULATE)
 	asm volatile("prefetch.global.L1 [%0];" : : "l"(p));
 #else
 	(void) p;
+#endif
+}
+// %globaltimer: nanoseconds, one clock for the whole GPU (the kernels time themselves with it)
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+#ifdef RT_EMULATE
+	return emu::global_timer_ns();
+#else
+	unsigned long long now;
+	asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+	return now;
 #endif
 }
 
@@ -88,11 +89,6 @@ __device__ __forceinline__ int positive_mod(int value, int modulus) { // Math::m
 	return r < 0 ? r + modulus : r;
 }
 
-// Row-major 3x4 affine matrix (three float4 rows): row i = (m(0,i), m(1,i), m(2,i), m(3,i)) of the
-// reference's column-major Matrix4, so the nested fused multiply-adds of Matrix4.h:39-85 read
-// x' = fma(r.x, p.x, fma(r.y, p.y, fma(r.z, p.z, r.w))).
-struct Affine { float4 r0, r1, r2; };
-
 __device__ __forceinline__ v3 transform_position(const Affine & m, v3 p) {
 	return V(__fmaf_rn(m.r0.x, p.x, __fmaf_rn(m.r0.y, p.y, __fmaf_rn(m.r0.z, p.z, m.r0.w))),
 	         __fmaf_rn(m.r1.x, p.x, __fmaf_rn(m.r1.y, p.y, __fmaf_rn(m.r1.z, p.z, m.r1.w))),
@@ -104,4 +100,4 @@ __device__ __forceinline__ v3 transform_direction(const Affine & m, v3 d) {
 	         __fmaf_rn(m.r2.x, d.x, __fmaf_rn(m.r2.y, d.y, m.r2.z * d.z)));
 }
 
-} // namespace rt
+} // namespace RT_NAMESPACE

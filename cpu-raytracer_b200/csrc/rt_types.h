@@ -1,4 +1,5 @@
-// device_scene.cuh — how the scene lies in HBM.
+// rt_types.h — how the scene lies in HBM: the plain records shared by the C ABI layer (b200rt.cu) and by the kernel
+// translation units (kernels_tu.cu, compiled once per arithmetic mode). No device code in this file.
 //
 // Everything a ray touches is stored as 16-byte aligned records read with LDG.128:
 //   BVH node      32 B = 2 x float4   {min.xyz, max.x} {max.yz, left_or_first, count}   (BVHNode.h:10-16, same bytes)
@@ -9,16 +10,29 @@
 // The child pair of an inner node (left, left + 1) is one aligned 64-byte line, as in the
 // reference (root 0, node 1 unused, BottomLevelBVH.cpp:92,132).
 #pragma once
-#include "rt_math.cuh"
+#ifdef RT_EMULATE
+#include "cuda_emu.h"              // tests/emu: the kernels' source run on the host, fibre per CUDA thread (test infrastructure)
+#else
+#include <cuda_runtime.h>
+#endif
+#include <stdint.h>
 #include "../../include/b200rt.h"
 
 namespace rt {
+
+// Row-major 3x4 affine matrix (three float4 rows): row i = (m(0,i), m(1,i), m(2,i), m(3,i)) of the
+// reference's column-major Matrix4, so the nested fused multiply-adds of Matrix4.h:39-85 read
+// x' = fma(r.x, p.x, fma(r.y, p.y, fma(r.z, p.z, r.w))).
+struct Affine { float4 r0, r1, r2; };
+
+#define RT_TLAS_STACK_SIZE 32   // entries of the TLAS traversal stack; b200rt.cu rejects a frame whose TLAS is deeper
+#define RT_MAX_BOUNCES 8        // NUMBER_OF_BOUNCES the kernels are instantiated up to
 
 struct DeviceInstance {
 	Affine inverse;   // Mesh::transform_inv
 	Affine world;     // Transform::world_matrix
 	int node_offset, triangle_offset, material_offset, shadow_node_offset;
-	int reserved[4];    // keeps the record at 128 bytes (one L2 line)
+	int reserved[4];    // [0] records per octant copy (RT_OCTANT_THREADED), [1] first wide record or -1 (RT_WIDE_SHADOW); keeps the record at 128 bytes (one L2 line)
 };
 static_assert(sizeof(DeviceInstance) == 128, "instance record is 128 bytes");
 
@@ -44,6 +58,7 @@ struct SceneParams {
 	// static (uploaded once)
 	const float4 * __restrict__ nodes;          // all BLAS, concatenated
 	const float4 * __restrict__ shadow_nodes;   // the same trees threaded for the any-hit traversal (threaded_nodes.h: build_threaded_nodes)
+	const float4 * __restrict__ wide_nodes;     // -DRT_WIDE_SHADOW: the same trees, four children per record (threaded_nodes.h: build_wide_nodes)
 	const float4 * __restrict__ triangles_hot;
 	const float4 * __restrict__ triangles_cold;
 	const DeviceMaterial * __restrict__ materials;
@@ -74,6 +89,17 @@ struct SceneParams {
 	// (band_rows rows, the last band takes the rest) belongs to the GPU whose image is band_targets[b]
 	unsigned * band_targets[B200RT_MAX_BANDS];
 	int band_count, band_rows, band_halo;   // band_count 0: one image, the kernel's frame_buffer argument
+	// deep-pixel queue (render.cuh): pools in HBM, bump-allocated per frame through FrameCounters::q_*
+	float4   * q_nodes;          // 6 float4 per node record
+	float4   * q_bounce;         // 5 float4 per bounce item
+	float4   * q_shadow;         // 2 float4 per shadow item
+	unsigned * q_bounce_ready;   // item i is readable once ready[i] == frame_serial
+	unsigned * q_shadow_ready;
+	unsigned q_node_capacity, q_bounce_capacity, q_shadow_capacity;
+	unsigned frame_serial;       // never 0, different for every launch of a context
+	int queue_mode;              // 0 off; 1: pixels whose primary ray hits a transmissive material; 2: every pixel whose primary hit spawns rays
+	int queue_inline_below;      // a queued ray with at most this many bounces left is walked depth-first by the thread that popped it (-1: never)
+	int blas_stack_entries;      // deepest BLAS + 1: what a push-both-pop-one traversal can hold
 };
 
 struct FrameCounters {   // accumulated with one atomicAdd per warp
@@ -82,7 +108,14 @@ struct FrameCounters {   // accumulated with one atomicAdd per warp
 	unsigned int next_unit;      // work-stealing cursor (WorkerThread.cpp:53-54)
 	unsigned int pad;
 	unsigned long long first_idle_ns, last_done_ns; // globaltimer when the first (stored as ~t) / the last warp ran out of work: the tail of the launch
-	unsigned long long first_start_ns, pad2;        // globaltimer when the first block started (stored as ~t)
+	unsigned long long first_start_ns, pad2[3];     // globaltimer when the first block started (stored as ~t)
+	// deep-pixel queue, on a 128-byte line of its own: pool cursors, and the frame's outstanding work
+	// (tile units not finished + items not finished; the queue kernel's warps leave when it is zero)
+	unsigned int q_node_reserved, q_bounce_reserved, q_shadow_reserved, q_fallbacks;
+	unsigned int q_bounce_head, q_shadow_head;
+	int q_outstanding;
+	unsigned int q_pad[25];
 };
+static_assert(sizeof(FrameCounters) == 256, "two 128-byte lines");
 
 } // namespace rt

@@ -8,7 +8,7 @@
 #pragma once
 #include "traverse.cuh"
 
-namespace rt {
+namespace RT_NAMESPACE {
 
 struct HitRecord {         // RayHit.h:4-22
 	v3    point, normal;
@@ -395,4 +395,4 @@ __device__ __forceinline__ v3 light_base(v3 colour, v3 normal, v3 to_light, v3 t
 	return colour * intensity;
 }
 
-} // namespace rt
+} // namespace RT_NAMESPACE

@@ -14,11 +14,15 @@
 // (shade.cuh) — the reference recomputes it on every accepted candidate
 // (BottomLevelBVH.cpp:254-308), a pure function of the same inputs.
 #pragma once
-#include "device_scene.cuh"
+#include "rt_math.cuh"
 
-namespace rt {
+namespace RT_NAMESPACE {
 
-#define RT_STACK_SIZE 64   // BVH_TRAVERSAL_STACK_SIZE, Config.h:25
+// BVH_TRAVERSAL_STACK_SIZE (Config.h:25) is 64 — a capacity, not semantics: a traversal that pushes both children
+// and pops one holds at most depth + 1 entries. The host measures every tree's depth (threaded_nodes.h: check_tree)
+// and the launch picks the instantiation whose BLAS stack (BSTACK = 32 or 64 entries) is deep enough; the TLAS stack
+// is RT_TLAS_STACK_SIZE entries (rt_types.h), checked per frame. Smaller arrays = a smaller local-memory frame per
+// thread (151 552 resident threads: every 4 bytes are 0.6 MB of L2 footprint).
 
 struct Ray {               // Ray.h:7-16
 	v3 origin, direction;
@@ -229,6 +233,45 @@ __device__ __forceinline__ bool blas_shadow(const float4 * __restrict__ records,
 	return false;
 }
 
+#ifdef RT_WIDE_SHADOW
+// Experiment (off by default): the any-hit query on the tree collapsed to four children per record (threaded_nodes.h:
+// build_wide_nodes) — half the dependent loads per ray. Same boolean as the binary walk for REGULAR rays (the slab
+// computation is monotone in the box, and a skipped node's box contains the tested ones below it); irregular rays
+// (a zero direction component: NaN arithmetic is not monotone) keep the binary walk.
+#define RT_WIDE_STACK 48
+__device__ __forceinline__ bool blas_shadow_wide(const float4 * __restrict__ records, const float4 * __restrict__ hot, v3 o, v3 inv_d, v3 d, float max_distance) {
+	int stack[RT_WIDE_STACK];
+	int size = 1;
+	stack[0] = 0;
+	while (size > 0) {
+		const float4 * r = records + 8 * size_t(stack[--size]);
+		const float4 lox = load_node(r), loy = load_node(r + 1), loz = load_node(r + 2), hix = load_node(r + 3), hiy = load_node(r + 4), hiz = load_node(r + 5);
+		const float4 links = load_node(r + 6), counts = load_node(r + 7);
+		const float lo_x[4] = { lox.x, lox.y, lox.z, lox.w }, lo_y[4] = { loy.x, loy.y, loy.z, loy.w }, lo_z[4] = { loz.x, loz.y, loz.z, loz.w };
+		const float hi_x[4] = { hix.x, hix.y, hix.z, hix.w }, hi_y[4] = { hiy.x, hiy.y, hiy.z, hiy.w }, hi_z[4] = { hiz.x, hiz.y, hiz.z, hiz.w };
+		const int link[4] = { __float_as_int(links.x), __float_as_int(links.y), __float_as_int(links.z), __float_as_int(links.w) };
+		const int count[4] = { __float_as_int(counts.x), __float_as_int(counts.y), __float_as_int(counts.z), __float_as_int(counts.w) };
+#pragma unroll
+		for (int k = 0; k < 4; k++) {
+			if (count[k] < 0) continue;
+			// AABB::intersect with the reference's operations (aabb_intersect, regular rays)
+			const float t0x = (lo_x[k] - o.x) * inv_d.x, t1x = (hi_x[k] - o.x) * inv_d.x;
+			const float t0y = (lo_y[k] - o.y) * inv_d.y, t1y = (hi_y[k] - o.y) * inv_d.y;
+			const float t0z = (lo_z[k] - o.z) * inv_d.z, t1z = (hi_z[k] - o.z) * inv_d.z;
+			const float t_near = fmaxf(fmaxf(RT_EPSILON,   fminf(t0x, t1x)), fmaxf(fminf(t0y, t1y), fminf(t0z, t1z)));
+			const float t_far  = fminf(fminf(max_distance, fmaxf(t0x, t1x)), fminf(fmaxf(t0y, t1y), fmaxf(t0z, t1z)));
+			if (!(t_near < t_far)) continue;
+			if (count[k] == 0) { stack[size++] = link[k]; continue; }
+			for (int i = link[k]; i < link[k] + count[k]; i++) {
+				float t, u, v;
+				if (triangle_test(hot + 3 * size_t(i), o, d, max_distance, t, u, v)) return true;
+			}
+		}
+	}
+	return false;
+}
+#endif
+
 #ifdef RT_OCTANT_THREADED
 // Experiment (off by default): closest hit on the copy of the tree threaded in this ray's visiting order
 // (threaded_nodes.h: build_threaded_nodes with an octant). The records come in the sequence the stack traversal pops
@@ -305,7 +348,7 @@ __device__ __forceinline__ float plane_t(const DevicePlane * __restrict__ plane,
 
 // Scene::trace_primitives, Scene.cpp:173-177: spheres, planes, then the TLAS, all against one
 // running closest distance.
-template<bool COUNT>
+template<bool COUNT, int BSTACK>
 __device__ __forceinline__ void trace_closest(const SceneParams & P, v3 o, v3 d, Candidate & best, Counters & cnt) {
 	best.t = CUDART_INF_F; best.u = 0.0f; best.v = 0.0f; best.instance = HIT_NONE; best.primitive = -1;
 
@@ -319,8 +362,8 @@ __device__ __forceinline__ void trace_closest(const SceneParams & P, v3 o, v3 d,
 	}
 
 	// TopLevelBVH::trace, TopLevelBVH.cpp:53-87
-	int tlas_stack[RT_STACK_SIZE];
-	int blas_stack[RT_STACK_SIZE];
+	int tlas_stack[RT_TLAS_STACK_SIZE];
+	int blas_stack[BSTACK];
 
 	const v3 inv_d = V(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
 	const bool exact = !ray_is_regular(o, inv_d);
@@ -364,7 +407,7 @@ __device__ __forceinline__ void trace_closest(const SceneParams & P, v3 o, v3 d,
 }
 
 // Scene::intersect_primitives, Scene.cpp:179-190
-template<bool COUNT>
+template<bool COUNT, int BSTACK>
 __device__ __forceinline__ bool trace_any(const SceneParams & P, v3 o, v3 d, float max_distance, Counters & cnt) {
 	for (int i = 0; i < P.sphere_count; i++) if (sphere_intersect(P.spheres + i, o, d, max_distance)) return true;
 	for (int i = 0; i < P.plane_count; i++) {
@@ -373,8 +416,8 @@ __device__ __forceinline__ bool trace_any(const SceneParams & P, v3 o, v3 d, flo
 	}
 
 	// TopLevelBVH::intersect, TopLevelBVH.cpp:89-129
-	int tlas_stack[RT_STACK_SIZE];
-	int blas_stack[RT_STACK_SIZE];
+	int tlas_stack[RT_TLAS_STACK_SIZE];
+	int blas_stack[COUNT ? BSTACK : 1];   // the shipped any-hit walk is stackless (blas_shadow); only the counting build pushes
 
 	const v3 inv_d = V(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
 	const bool exact = !ray_is_regular(o, inv_d);
@@ -396,6 +439,16 @@ __device__ __forceinline__ bool trace_any(const SceneParams & P, v3 o, v3 d, flo
 				if (COUNT) cnt.instances++;
 				const float4 * hot = P.triangles_hot + 3 * size_t(inst.triangle_offset);
 				const v3 local_o = transform_position(inst.inverse, o), local_d = transform_direction(inst.inverse, d);
+#ifdef RT_WIDE_SHADOW
+				if (!COUNT) {
+					const v3 local_inv_d = V(1.0f / local_d.x, 1.0f / local_d.y, 1.0f / local_d.z);
+					const int wide_offset = __ldg(&P.instances[instance].reserved[1]);
+					if (wide_offset >= 0 && ray_is_regular(local_o, local_inv_d)) {
+						if (blas_shadow_wide(P.wide_nodes + 8 * size_t(wide_offset), hot, local_o, local_inv_d, local_d, max_distance)) return true;
+						continue;
+					}
+				}
+#endif
 				if (COUNT ? blas_intersect<COUNT>(P.nodes + 2 * size_t(inst.node_offset), hot, local_o, local_d, max_distance, blas_stack, cnt, traversal_order_mask(P, local_d))
 				          : blas_shadow(P.shadow_nodes + 2 * size_t(inst.shadow_node_offset), hot, local_o, local_d, max_distance)) return true;
 			}
@@ -410,4 +463,4 @@ __device__ __forceinline__ bool trace_any(const SceneParams & P, v3 o, v3 d, flo
 	return false;
 }
 
-} // namespace rt
+} // namespace RT_NAMESPACE

@@ -51,6 +51,7 @@ class Config(C.Structure):
         ("max_anisotropy", C.c_float), ("enable_fxaa", C.c_int32), ("device", C.c_int32),
         ("tile_stride", C.c_int32), ("tile_phase", C.c_int32), ("count_traversal", C.c_int32),
         ("traversal_naive", C.c_int32), ("texture_sample_mode", C.c_int32),
+        ("arithmetic", C.c_int32), ("deep_queue", C.c_int32),
     ]
 
 
@@ -60,6 +61,7 @@ class Stats(C.Structure):
         ("nodes_visited", C.c_uint64), ("triangles_tested", C.c_uint64), ("texels_fetched", C.c_uint64),
         ("hits_accepted", C.c_uint64), ("instances_entered", C.c_uint64),
         ("device_ms_render", C.c_float), ("device_ms_fxaa", C.c_float), ("device_ms_total", C.c_float), ("device_ms_tail", C.c_float),
+        ("queue_nodes", C.c_uint32), ("queue_bounce_items", C.c_uint32), ("queue_shadow_items", C.c_uint32), ("queue_fallbacks", C.c_uint32),
     ]
 
     def as_dict(self):
@@ -73,11 +75,19 @@ class Outputs(C.Structure):
     ]
 
 
+ARITHMETIC = {"exact": 0, "fast": 1}
+DEEP_QUEUE = {"off": 0, "glass": 1, "all": 2}
+DEFAULT_DEEP_QUEUE = "off"
+
+
 def make_config(width, height, bounces, mipmap_filter="aniso", max_anisotropy=8.0, enable_fxaa=True, device=0,
-                tile_stride=1, tile_phase=0, count_traversal=False, traversal="ordered", texture_mode="mipmap"):
+                tile_stride=1, tile_phase=0, count_traversal=False, traversal="ordered", texture_mode="mipmap",
+                arithmetic=None, deep_queue=None):
     f = FILTERS[mipmap_filter] if isinstance(mipmap_filter, str) else int(mipmap_filter)
+    arithmetic = arithmetic or os.environ.get("B200RT_ARITHMETIC", "exact")     # the environment overrides the defaults (tools/, variant timing)
+    deep_queue = deep_queue or os.environ.get("B200RT_DEEP_QUEUE", DEFAULT_DEEP_QUEUE)
     return Config(width, height, bounces, f, max_anisotropy, 1 if enable_fxaa else 0, device, tile_stride, tile_phase, 1 if count_traversal else 0,
-                  TRAVERSALS[traversal], TEXTURE_MODES[texture_mode])
+                  TRAVERSALS[traversal], TEXTURE_MODES[texture_mode], ARITHMETIC[arithmetic], DEEP_QUEUE[deep_queue])
 
 
 def _load(path):

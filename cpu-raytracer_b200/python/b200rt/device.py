@@ -19,10 +19,11 @@ class DeviceError(RuntimeError):
 
 class Renderer:
     def __init__(self, width, height, bounces, mipmap_filter="aniso", max_anisotropy=8.0, enable_fxaa=True, device=0,
-                 tile_stride=1, tile_phase=0, count_traversal=False, traversal="ordered", texture_mode="mipmap"):
+                 tile_stride=1, tile_phase=0, count_traversal=False, traversal="ordered", texture_mode="mipmap",
+                 arithmetic=None, deep_queue=None):
         self._lib = _ffi.device_lib()
         self.config = _ffi.make_config(width, height, bounces, mipmap_filter, max_anisotropy, enable_fxaa, device,
-                                       tile_stride, tile_phase, count_traversal, traversal, texture_mode)
+                                       tile_stride, tile_phase, count_traversal, traversal, texture_mode, arithmetic, deep_queue)
         self._h = C.c_void_p()
         if self._lib.b200rt_create(C.byref(self.config), C.byref(self._h)) != 0:
             raise DeviceError(self._lib.b200rt_last_error(None).decode())

@@ -293,6 +293,29 @@ def sibenik_standin(out=None, width=3840, height=2160, directory=None):
     return s.write(out or os.path.join(d, "sibenik_%dx%d.scene" % (width, height)))
 
 
+def dielectrics_hall(data, out=None, width=1920, height=1080, directory=None):
+    """Config 4 as SURVEY.md 8(d) states it: the Sponza hall (stand-in, seed 1234) with the reference's own
+    Magnifier.obj in front of the shipped camera (Lense: Kt 1, Ni 1.45, Ks 0.5 — at the origin, where SCENE_SPONZA puts
+    it, Scene.cpp:75-81), Diamond.obj (Kt (0.5, 0.1, 0.5), Ni 2.4) and the two glass spheres of Scene.cpp:8-19 (ior 1.33 /
+    1.68, transmittance 0.6) behind the lens, Concave.obj where SCENE_SPONZA has it, the shipped directional light and
+    the point light of config 2. 8 bounces, EWA, MAX_ANISOTROPY 8 are the renderer's settings. `data` holds the
+    reference's shipped meshes (oracle/_ref/Data)."""
+    d = _ensure(directory or cache_dir(), "sponza_standin_v1", 1234, 262267)
+    s = scenes.SceneWriter(width, height)
+    s.camera((19.729143, 18.946165, 0.0), (0.0, -0.707107, 0.0, 0.707107))   # Scene.cpp:127-128
+    s.ambient((0.2, 0.2, 0.2))
+    s.sky(os.path.join(d, "sky_256.float"))
+    s.sphere(2.0, (-7.0, 16.0, -4.5), diffuse=(0.2, 0.2, 0.0), reflection=(0.6, 0.6, 0.0), transmittance=(0.6, 0.6, 0.6), ior=1.33)
+    s.sphere(2.0, (-7.0, 16.0, +4.5), diffuse=(0.0, 0.2, 0.2), reflection=(0.0, 0.6, 0.6), transmittance=(0.6, 0.6, 0.6), ior=1.68)
+    s.mesh(os.path.join(d, "hall.obj"))
+    s.mesh(os.path.join(data, "Magnifier.obj"))
+    s.mesh(os.path.join(data, "Diamond.obj"), (-5.0, 20.0, 0.0), scenes.axis_angle((0, 0, 1), scenes.F(0.6)))
+    s.mesh(os.path.join(data, "Concave.obj"), (20.0, 0.0, 0.0), scenes.axis_angle((0, 1, 0), scenes.PI))
+    s.point_light((2000.0, 1800.0, 1600.0), (0.0, 60.0, 0.0))
+    s.directional_light((0.9, 0.9, 0.9), _normalize((0.1, -1.0, 0.1)))
+    return s.write(out or os.path.join(d, "dielectrics_hall_%dx%d.scene" % (width, height)))
+
+
 def _normalize(v):
     v = np.asarray(v, dtype=np.float64)
     return tuple(v / np.linalg.norm(v))

@@ -150,7 +150,19 @@ typedef struct {
 	int32_t traversal_naive;
 	/* TEXTURE_SAMPLE_MODE (Config.h:37-42, Texture.h:33-49): B200RT_TEXTURE_*; 0 = the shipped setting.                 */
 	int32_t texture_sample_mode;
+	/* B200RT_ARITHMETIC_*. EXACT (0, the default): every operation in the reference's association order, a multiply-add
+	 * fused exactly where the reference calls madd / msub (SIMD_Vector3.h:53-63, Matrix4.h:39-85) — primary-hit ids, hit
+	 * distances and the 8-bit image come out as the reference's bits. FAST: a second set of kernels compiled with
+	 * contraction and a cheaper box / triangle arithmetic, inside north_star's tolerance (>= 99.9 % ids, >= 50 dB) but
+	 * not bit-identical — the reference's own release build is of that kind (/fp:fast, Raytracer.vcxproj).            */
+	int32_t arithmetic;
+	/* Deep-pixel ray queue: 0 = every pixel's ray tree is walked depth-first by one thread;
+	 * 1 = pixels whose primary ray hits a transmissive material hand their rays (closest-hit and shadow rays alike) to
+	 * device-side queues that all persistent warps pop; 2 = every pixel whose primary hit spawns rays does.
+	 * Same image bit for bit in every setting: the node values are combined in the reference's order.               */
+	int32_t deep_queue;
 } b200rt_config;
+enum { B200RT_ARITHMETIC_EXACT = 0, B200RT_ARITHMETIC_FAST = 1 };
 enum { B200RT_TEXTURE_MIPMAP = 0,   /* TEXTURE_SAMPLE_MODE_MIPMAP: mipmap_filter on mip-mapped textures, bilinear on the others */
        B200RT_TEXTURE_BILINEAR = 1, /* TEXTURE_SAMPLE_MODE_BILINEAR: Texture::sample_bilinear on level 0, Texture.cpp:156-186   */
        B200RT_TEXTURE_NEAREST = 2 };/* TEXTURE_SAMPLE_MODE_NEAREST: Texture::sample_nearest, Texture.cpp:149-154              */
@@ -171,6 +183,9 @@ typedef struct {
 	float    device_ms_total;      /* uploads + kernels + downloads on the context's stream
 	                                * (= device_ms_render from b200rt_wait_frame)                         */
 	float    device_ms_tail;       /* part of device_ms_render during which some warps had already run out of work */
+	/* deep-pixel queue (config.deep_queue != 0): node records, bounce-ray and shadow-ray items of the frame, and how
+	 * many of them found their pool exhausted and were walked depth-first instead (correct either way)            */
+	uint32_t queue_nodes, queue_bounce_items, queue_shadow_items, queue_fallbacks;
 } b200rt_stats;
 
 /* Host buffers to fill; any pointer may be NULL to skip that output.                      */
