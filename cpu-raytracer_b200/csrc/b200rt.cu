@@ -46,6 +46,7 @@ struct b200rt_ctx {
 	std::vector<int> records_per_copy;    // per BLAS: records in one threaded copy (RT_OCTANT_THREADED)
 	std::vector<int> wide_node_offset;    // per BLAS: first record of its four-wide copy, -1 if it has none (RT_WIDE_SHADOW)
 	DeviceBuffer wide_nodes;
+	DeviceBuffer hot_fast, texels_half;   // FAST unit: precomputed triangle transforms, RGBA16F texel pool
 	int sky_size = 0;
 	bool have_static = false;
 	std::vector<b200rt_blas> blas;
@@ -210,7 +211,7 @@ extern "C" void b200rt_destroy(b200rt_ctx * ctx) {
 	if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
 	for (DeviceBuffer * b : { &ctx->nodes, &ctx->shadow_nodes, &ctx->hot, &ctx->cold, &ctx->materials, &ctx->textures, &ctx->texels, &ctx->sky, &ctx->gamma,
 	                          &ctx->frame_block[0], &ctx->frame_block[1], &ctx->frame_buffer, &ctx->presented, &ctx->colour_float, &ctx->ids, &ctx->hits, &ctx->counters, &ctx->l2_scratch, &ctx->tile_cost, &ctx->tile_order,
-	                          &ctx->q_nodes, &ctx->q_bounce, &ctx->q_shadow, &ctx->q_bounce_ready, &ctx->q_shadow_ready, &ctx->wide_nodes }) b->release();
+	                          &ctx->q_nodes, &ctx->q_bounce, &ctx->q_shadow, &ctx->q_bounce_ready, &ctx->q_shadow_ready, &ctx->wide_nodes, &ctx->hot_fast, &ctx->texels_half }) b->release();
 	for (auto & slot : ctx->slots) {
 		slot.frame_buffer.release(); slot.presented.release();
 		if (slot.pinned_counters) cudaFreeHost(slot.pinned_counters);
@@ -324,6 +325,27 @@ extern "C" int b200rt_upload_static(b200rt_ctx * ctx, const b200rt_static_scene 
 		if (upload(ctx, ctx->hot, packed.data(), packed.size() * sizeof(float))) return -1;
 	}
 	if (upload(ctx, ctx->cold, s->triangles_cold, size_t(s->triangle_count) * sizeof(b200rt_triangle_cold))) return -1;
+	if (ctx->kernels->fast_features & 2) {
+		// Woop / Baldwin-Weber: rows of [e1 e2 n]^-1 (n = e1 x e2) with the offset -row . p0, so that the transformed
+		// ray's third coordinate gives t and the first two give u, v. Computed in double, stored as float: {w row}{u row}{v row}.
+		std::vector<float> packed(size_t(s->triangle_count) * 12, 0.0f);
+		for (int i = 0; i < s->triangle_count; i++) {
+			const b200rt_triangle_hot & t = s->triangles_hot[i];
+			const double p0[3] = { t.position_0[0], t.position_0[1], t.position_0[2] }, e1[3] = { t.position_edge_1[0], t.position_edge_1[1], t.position_edge_1[2] }, e2[3] = { t.position_edge_2[0], t.position_edge_2[1], t.position_edge_2[2] };
+			auto cross = [](const double a[3], const double b[3], double r[3]) { r[0] = a[1] * b[2] - a[2] * b[1]; r[1] = a[2] * b[0] - a[0] * b[2]; r[2] = a[0] * b[1] - a[1] * b[0]; };
+			double n[3], ru[3], rv[3];
+			cross(e1, e2, n); cross(e2, n, ru); cross(n, e1, rv);
+			const double det = n[0] * n[0] + n[1] * n[1] + n[2] * n[2];   // (e1 x e2) . n
+			const double * rows[3] = { n, ru, rv };
+			for (int r = 0; r < 3; r++) {
+				double row[3], offset = 0.0;
+				for (int c = 0; c < 3; c++) { row[c] = det > 0.0 ? rows[r][c] / det : 0.0; offset -= row[c] * p0[c]; }
+				float * out = &packed[size_t(i) * 12 + 4 * r];
+				out[0] = float(row[0]); out[1] = float(row[1]); out[2] = float(row[2]); out[3] = float(offset);
+			}
+		}
+		if (upload(ctx, ctx->hot_fast, packed.data(), packed.size() * sizeof(float))) return -1;
+	}
 
 	{ // Material -> three float4
 		std::vector<DeviceMaterial> packed(s->material_count);
@@ -391,6 +413,11 @@ extern "C" int b200rt_upload_static(b200rt_ctx * ctx, const b200rt_static_scene 
 			if (e != cudaSuccess) { ctx->error = std::string("texture ingest: ") + cudaGetErrorString(e); return -1; }
 		}
 		if (upload_rgb(ctx->sky, s->sky, size_t(s->sky_size) * s->sky_size + 1)) return -1; // + the pad texel (Sky.cpp:45)
+	}
+	if (ctx->kernels->fast_features & 4) {
+		CHECK_CUDA(ctx, ctx->texels_half.ensure(std::max<size_t>(size_t(s->texel_count), 1) * sizeof(uint2)));
+		CHECK_CUDA(ctx, ctx->kernels->texel_halves(static_cast<const float4 *>(ctx->texels.ptr), static_cast<uint2 *>(ctx->texels_half.ptr), s->texel_count, ctx->stream));
+		CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 	}
 	ctx->sky_size = s->sky_size;
 	ctx->blas_stack_entries = blas_depth + 1;
@@ -514,6 +541,8 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 	P.shadow_nodes = static_cast<const float4 *>(ctx->shadow_nodes.ptr);
 	P.wide_nodes = static_cast<const float4 *>(ctx->wide_nodes.ptr);
 	P.triangles_hot = static_cast<const float4 *>(ctx->hot.ptr);
+	P.triangles_test = (ctx->kernels->fast_features & 2) ? static_cast<const float4 *>(ctx->hot_fast.ptr) : P.triangles_hot;
+	P.texels_half = static_cast<const uint2 *>(ctx->texels_half.ptr);
 	P.triangles_cold = static_cast<const float4 *>(ctx->cold.ptr);
 	P.materials = static_cast<const DeviceMaterial *>(ctx->materials.ptr);
 	P.textures = static_cast<const DeviceTexture *>(ctx->textures.ptr);

@@ -6,7 +6,8 @@
 namespace rt {
 
 struct KernelTable {
-	const char * name;   // "exact" | "fast"
+	const char * name;   // "rt_exact" | "rt_fast"
+	int fast_features;   // RT_FAST_FEATURES of the unit: 2 = it tests precomputed triangle transforms (SceneParams::triangles_test), 4 = it reads SceneParams::texels_half
 	// constant tables of the unit (Texture::ewa_weight_table, Texture.h:20-21,53-62)
 	cudaError_t (*init)(const float ewa_weight_table[128]);
 	// resident blocks per SM of the render kernel the launch below would pick for these parameters
@@ -19,6 +20,7 @@ struct KernelTable {
 	cudaError_t (*fxaa)(const unsigned * frame_buffer, unsigned char * rgb8, const float * gamma_table, int width, int height, int enable_fxaa, int row_begin, int row_end, cudaStream_t stream);
 	cudaError_t (*texture_level0)(const unsigned char * rgb8, const float * gamma_lut, float4 * out, long long texel_count, cudaStream_t stream);
 	cudaError_t (*texture_mip)(const float4 * previous, float4 * out, int width, int height, int previous_width, cudaStream_t stream);
+	cudaError_t (*texel_halves)(const float4 * texels, uint2 * out, long long texel_count, cudaStream_t stream);
 };
 
 const KernelTable & kernels_exact();   // -fmad=false: the reference's association order, bit for bit

@@ -268,6 +268,22 @@ texture_level0_kernel(const unsigned char * __restrict__ rgb8, const float * __r
 		out[i] = make_float4(lut[rgb8[3 * i]], lut[rgb8[3 * i + 1]], lut[rgb8[3 * i + 2]], 0.0f);
 }
 
+// FAST arithmetic, RT_FAST_TEXEL: the float4 pool re-stored as four halves per texel (round to nearest even)
+__global__ void __launch_bounds__(256)
+texel_halves_kernel(const float4 * __restrict__ texels, uint2 * __restrict__ out, long long texel_count) {
+	for (long long i = blockIdx.x * 256ll + threadIdx.x; i < texel_count; i += gridDim.x * 256ll) {
+		const float4 t = texels[i];
+#ifdef RT_EMULATE
+		const unsigned r = emu_float_to_half(t.x), g = emu_float_to_half(t.y), b = emu_float_to_half(t.z);
+#elif defined(RT_FAST_TEXEL)
+		const unsigned r = __half_as_ushort(__float2half_rn(t.x)), g = __half_as_ushort(__float2half_rn(t.y)), b = __half_as_ushort(__float2half_rn(t.z));
+#else
+		const unsigned r = 0, g = 0, b = 0; (void) t;
+#endif
+		out[i] = make_uint2(r | (g << 16), b);
+	}
+}
+
 __global__ void __launch_bounds__(256)
 texture_mip_kernel(const float4 * __restrict__ previous, float4 * __restrict__ out, int width, int height, int previous_width) {
 	const int i = blockIdx.x * 32 + (threadIdx.x & 31), j = blockIdx.y * 8 + (threadIdx.x >> 5);

@@ -68,9 +68,15 @@ static cudaError_t tu_texture_mip(const float4 * previous, float4 * out, int wid
 	return cudaGetLastError();
 }
 
+static cudaError_t tu_texel_halves(const float4 * texels, uint2 * out, long long texel_count, cudaStream_t stream) {
+	const unsigned blocks = unsigned(texel_count + 255 < 256ll * 148 * 8 ? (texel_count + 255) / 256 : 148 * 8);
+	RT_LAUNCH(texel_halves_kernel, blocks ? blocks : 1u, 256, stream, false, texels, out, texel_count);
+	return cudaGetLastError();
+}
+
 #define RT_STRINGIFY2(x) #x
 #define RT_STRINGIFY(x) RT_STRINGIFY2(x)
-static const rt::KernelTable table = { RT_STRINGIFY(RT_NAMESPACE), tu_init, tu_render_occupancy, tu_render, tu_primary_hits, tu_schedule, tu_fxaa, tu_texture_level0, tu_texture_mip };
+static const rt::KernelTable table = { RT_STRINGIFY(RT_NAMESPACE), RT_FEATURE_BITS, tu_init, tu_render_occupancy, tu_render, tu_primary_hits, tu_schedule, tu_fxaa, tu_texture_level0, tu_texture_mip, tu_texel_halves };
 
 } // namespace RT_NAMESPACE
 

@@ -17,6 +17,29 @@
 #ifndef RT_NAMESPACE
 #define RT_NAMESPACE rt_exact
 #endif
+// What the FAST unit changes besides contraction (-fmad=true), one bit each so that every candidate can be built and
+// timed alone (Makefile: fast_* variants; DESIGN.md has the table): 1 = slab test as one multiply-add per plane,
+// 2 = precomputed-transform triangle test + approximate reciprocal, 4 = RGBA16F texels.
+#ifdef RT_FAST
+#ifndef RT_FAST_FEATURES
+#define RT_FAST_FEATURES 7
+#endif
+#if RT_FAST_FEATURES & 1
+#define RT_FAST_SLAB
+#endif
+#if RT_FAST_FEATURES & 2
+#define RT_FAST_TRI
+#endif
+#if RT_FAST_FEATURES & 4
+#define RT_FAST_TEXEL
+#endif
+#define RT_FEATURE_BITS RT_FAST_FEATURES
+#else
+#define RT_FEATURE_BITS 0
+#endif
+#if defined(RT_FAST_TEXEL) && !defined(RT_EMULATE)
+#include <cuda_fp16.h>
+#endif
 
 namespace RT_NAMESPACE {
 using namespace rt;

@@ -60,6 +60,8 @@ struct SceneParams {
 	const float4 * __restrict__ shadow_nodes;   // the same trees threaded for the any-hit traversal (threaded_nodes.h: build_threaded_nodes)
 	const float4 * __restrict__ wide_nodes;     // -DRT_WIDE_SHADOW: the same trees, four children per record (threaded_nodes.h: build_wide_nodes)
 	const float4 * __restrict__ triangles_hot;
+	const float4 * __restrict__ triangles_test; // what the traversal tests: triangles_hot, or the precomputed transforms of the FAST unit (RT_FAST_TRI)
+	const uint2  * __restrict__ texels_half;    // the texel pool as four halves per texel (FAST unit, RT_FAST_TEXEL)
 	const float4 * __restrict__ triangles_cold;
 	const DeviceMaterial * __restrict__ materials;
 	const DeviceTexture  * __restrict__ textures;

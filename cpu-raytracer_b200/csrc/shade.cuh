@@ -161,7 +161,26 @@ __device__ __forceinline__ void build_record(const SceneParams & P, const Ray & 
 // ---------------------------------------------------------------------------- textures ---
 __constant__ float c_ewa_weight_table[128]; // Texture::ewa_weight_table, Texture.h:20-21,53-62 (filled by the host)
 
-struct TexView { const float4 * texels; int width, height, mip_levels; const int * mip_offsets; };
+// A texel in HBM: float4 (linear RGB + pad; the reference keeps 3 floats, Texture.cpp:30-129), or — FAST arithmetic,
+// RT_FAST_TEXEL — four halves in 8 bytes (11 significant bits: the source images have 8).
+#ifdef RT_FAST_TEXEL
+typedef uint2 Texel;
+__device__ __forceinline__ float half_bits_to_float(unsigned h) {
+#ifdef RT_EMULATE
+	return emu_half_to_float((unsigned short)h);
+#else
+	return __half2float(__ushort_as_half((unsigned short)h));
+#endif
+}
+__device__ __forceinline__ v3 texel_rgb(const Texel * p) { const uint2 h = __ldg(p); return V(half_bits_to_float(h.x & 0xffffu), half_bits_to_float(h.x >> 16), half_bits_to_float(h.y & 0xffffu)); }
+__device__ __forceinline__ const Texel * texel_pool(const SceneParams & P) { return P.texels_half; }
+#else
+typedef float4 Texel;
+__device__ __forceinline__ v3 texel_rgb(const Texel * p) { return V(load_texel(p)); }
+__device__ __forceinline__ const Texel * texel_pool(const SceneParams & P) { return P.texels; }
+#endif
+
+struct TexView { const Texel * texels; int width, height, mip_levels; const int * mip_offsets; };
 
 // Texture::fetch_texel, Texture.cpp:131-147 (repeat wrap by positive modulo)
 template<bool COUNT>
@@ -171,7 +190,7 @@ __device__ __forceinline__ v3 fetch_texel(const TexView & tex, int x, int y, int
 	x = positive_mod(x, level_width);
 	y = positive_mod(y, level_height);
 	if (COUNT) cnt.texels++;
-	return V(load_texel(tex.texels + (__ldg(tex.mip_offsets + level) + x + y * level_width)));
+	return texel_rgb(tex.texels + (__ldg(tex.mip_offsets + level) + x + y * level_width));
 }
 
 // Texture::sample_bilinear, Texture.cpp:156-186
@@ -342,7 +361,7 @@ __device__ __forceinline__ v3 get_albedo(const SceneParams & P, float4 diffuse_t
 
 	const DeviceTexture * dt = P.textures + texture;
 	TexView tex;
-	tex.texels = P.texels + __ldg(&dt->texel_offset);
+	tex.texels = texel_pool(P) + __ldg(&dt->texel_offset);
 	tex.width = __ldg(&dt->width); tex.height = __ldg(&dt->height); tex.mip_levels = __ldg(&dt->mip_levels);
 	tex.mip_offsets = dt->mip_offsets;
 

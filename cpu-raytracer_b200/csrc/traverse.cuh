@@ -53,6 +53,27 @@ struct Counters { unsigned nodes, triangles, texels, shadow, reflection, refract
 __device__ __forceinline__ bool ray_is_regular(v3 o, v3 inv_d) {
 	return isfinite(o.x) && isfinite(o.y) && isfinite(o.z) && isfinite(inv_d.x) && isfinite(inv_d.y) && isfinite(inv_d.z);
 }
+#ifdef RT_FAST_SLAB
+// FAST arithmetic (b200rt_config.arithmetic): one fused multiply-add per slab plane, t = plane * (1/d) - o * (1/d),
+// against the reference's subtract-then-multiply: 6 instructions instead of 12 in the hottest loop of the kernel.
+// `o` here is slab_origin() = -(o * inv_d); NaNs (0 * inf) fall out of fminf / fmaxf, i.e. that slab does not constrain.
+// 1/d is kept finite (a zero component gives +-1e30, not inf): inf * plane - inf * o would be NaN or the wrong
+// infinity exactly where the reference's (plane - o) * inf is right — a ray parallel to a slab and inside it.
+__device__ __forceinline__ v3 inv_direction(v3 d) {
+	return V(fminf(fmaxf(1.0f / d.x, -1e30f), 1e30f), fminf(fmaxf(1.0f / d.y, -1e30f), 1e30f), fminf(fmaxf(1.0f / d.z, -1e30f), 1e30f));
+}
+__device__ __forceinline__ v3 slab_origin(v3 o, v3 inv_d) { return V(0.0f - o.x * inv_d.x, 0.0f - o.y * inv_d.y, 0.0f - o.z * inv_d.z); }
+__device__ __forceinline__ bool aabb_intersect(float4 n0, float4 n1, v3 o, v3 inv_d, float max_distance, bool) {
+	const float t0x = __fmaf_rn(n0.x, inv_d.x, o.x), t1x = __fmaf_rn(n0.w, inv_d.x, o.x);
+	const float t0y = __fmaf_rn(n0.y, inv_d.y, o.y), t1y = __fmaf_rn(n1.x, inv_d.y, o.y);
+	const float t0z = __fmaf_rn(n0.z, inv_d.z, o.z), t1z = __fmaf_rn(n1.y, inv_d.z, o.z);
+	const float t_near = fmaxf(fmaxf(RT_EPSILON,   fminf(t0x, t1x)), fmaxf(fminf(t0y, t1y), fminf(t0z, t1z)));
+	const float t_far  = fminf(fminf(max_distance, fmaxf(t0x, t1x)), fminf(fmaxf(t0y, t1y), fmaxf(t0z, t1z)));
+	return t_near < t_far;
+}
+#else
+__device__ __forceinline__ v3 inv_direction(v3 d) { return V(1.0f / d.x, 1.0f / d.y, 1.0f / d.z); }
+__device__ __forceinline__ v3 slab_origin(v3 o, v3) { return o; }
 __device__ __forceinline__ bool aabb_intersect(float4 n0, float4 n1, v3 o, v3 inv_d, float max_distance, bool exact) {
 	float t0x = (n0.x - o.x) * inv_d.x, t1x = (n0.w - o.x) * inv_d.x;
 	float t0y = (n0.y - o.y) * inv_d.y, t1y = (n1.x - o.y) * inv_d.y;
@@ -71,6 +92,7 @@ __device__ __forceinline__ bool aabb_intersect(float4 n0, float4 n1, v3 o, v3 in
 	float t_far  = sse_min(sse_min(max_distance, tmaxx), sse_min(tmaxy, tmaxz));
 	return t_near < t_far;
 }
+#endif
 
 // BVHNode::should_visit_left_first, BVHNode.h:30-40 (axis in the top two bits of count)
 __device__ __forceinline__ bool visit_left_first(int count, v3 d) {
@@ -94,6 +116,32 @@ __device__ __forceinline__ int left_first_bit(int count, unsigned order_mask) {
 
 // Moller-Trumbore with the reference's operation order; all comparisons strict
 // (BottomLevelBVH.cpp:214-252 / :311-346).
+#ifdef RT_FAST_TRI
+// FAST arithmetic: the triangle as a precomputed world-to-barycentric transform (Woop / Baldwin-Weber; b200rt.cu builds
+// it at upload, same 48 bytes as TriangleHot): rows of [e1 e2 n]^-1 with the offset -row . p0 in .w. The ray's
+// transformed z gives t, then u and v are one multiply-add each — about 25 operations and one MUFU.RCP against
+// Moller-Trumbore's 31 and an IEEE division, and the test that fails most often (t) comes first.
+__device__ __forceinline__ float fast_rcp(float x) {
+#ifdef RT_EMULATE
+	return 1.0f / x;
+#else
+	float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r;
+#endif
+}
+__device__ __forceinline__ bool triangle_test(const float4 * __restrict__ tri, v3 o, v3 d, float max_t, float & t_out, float & u_out, float & v_out) {
+	const float4 rw = load_node(tri), ru = load_node(tri + 1), rv = load_node(tri + 2);
+	const float dz = __fmaf_rn(rw.x, d.x, __fmaf_rn(rw.y, d.y, rw.z * d.z));
+	const float oz = __fmaf_rn(rw.x, o.x, __fmaf_rn(rw.y, o.y, __fmaf_rn(rw.z, o.z, rw.w)));
+	const float t = (0.0f - oz) * fast_rcp(dz);
+	if (!(t > RT_EPSILON && t < max_t)) return false;
+	const float u = __fmaf_rn(t, __fmaf_rn(ru.x, d.x, __fmaf_rn(ru.y, d.y, ru.z * d.z)), __fmaf_rn(ru.x, o.x, __fmaf_rn(ru.y, o.y, __fmaf_rn(ru.z, o.z, ru.w))));
+	if (!(u > 0.0f && u < 1.0f)) return false;
+	const float v = __fmaf_rn(t, __fmaf_rn(rv.x, d.x, __fmaf_rn(rv.y, d.y, rv.z * d.z)), __fmaf_rn(rv.x, o.x, __fmaf_rn(rv.y, o.y, __fmaf_rn(rv.z, o.z, rv.w))));
+	if (!(v > 0.0f && (u + v) < 1.0f)) return false;
+	t_out = t; u_out = u; v_out = v;
+	return true;
+}
+#else
 __device__ __forceinline__ bool triangle_test(const float4 * __restrict__ tri, v3 o, v3 d, float max_t, float & t_out, float & u_out, float & v_out) {
 	const float4 a0 = load_node(tri), a1 = load_node(tri + 1), a2 = load_node(tri + 2);
 	const v3 p0 = V(a0.x, a0.y, a0.z), edge_1 = V(a0.w, a1.x, a1.y), edge_2 = V(a1.z, a1.w, a2.x);
@@ -115,6 +163,7 @@ __device__ __forceinline__ bool triangle_test(const float4 * __restrict__ tri, v
 	t_out = t; u_out = u; v_out = v;
 	return true;
 }
+#endif
 
 __device__ __forceinline__ DeviceInstance load_instance_inverse(const DeviceInstance * __restrict__ inst) {
 	const float4 * p = reinterpret_cast<const float4 *>(inst);
@@ -128,8 +177,9 @@ __device__ __forceinline__ DeviceInstance load_instance_inverse(const DeviceInst
 // BottomLevelBVH::trace, BottomLevelBVH.cpp:355-396 (object-space ray, shared t)
 template<bool COUNT>
 __device__ __forceinline__ void blas_trace(const float4 * __restrict__ nodes, const float4 * __restrict__ hot, v3 o, v3 d, int instance, Candidate & best, int * stack, Counters & cnt, unsigned order_mask) {
-	const v3 inv_d = V(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+	const v3 inv_d = inv_direction(d);
 	const bool exact = !ray_is_regular(o, inv_d);
+	const v3 so = slab_origin(o, inv_d);
 
 	int stack_size = 1;
 	stack[0] = 0;
@@ -139,7 +189,7 @@ __device__ __forceinline__ void blas_trace(const float4 * __restrict__ nodes, co
 		const float4 n0 = load_node(nodes + 2 * index), n1 = load_node(nodes + 2 * index + 1);
 		if (COUNT) cnt.nodes++;
 
-		if (!aabb_intersect(n0, n1, o, inv_d, best.t, exact)) continue;
+		if (!aabb_intersect(n0, n1, so, inv_d, best.t, exact)) continue;
 
 		const int left_or_first = __float_as_int(n1.z), count = __float_as_int(n1.w);
 		if ((count & 0x3FFFFFFF) > 0) {
@@ -174,8 +224,9 @@ __device__ __forceinline__ void blas_trace(const float4 * __restrict__ nodes, co
 // stays the reference algorithm's work.
 template<bool COUNT>
 __device__ __forceinline__ bool blas_intersect(const float4 * __restrict__ nodes, const float4 * __restrict__ hot, v3 o, v3 d, float max_distance, int * stack, Counters & cnt, unsigned order_mask) {
-	const v3 inv_d = V(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+	const v3 inv_d = inv_direction(d);
 	const bool exact = !ray_is_regular(o, inv_d);
+	const v3 so = slab_origin(o, inv_d);
 
 	int stack_size = 1;
 	stack[0] = 0;
@@ -185,7 +236,7 @@ __device__ __forceinline__ bool blas_intersect(const float4 * __restrict__ nodes
 		const float4 n0 = load_node(nodes + 2 * index), n1 = load_node(nodes + 2 * index + 1);
 		if (COUNT) cnt.nodes++;
 
-		if (!aabb_intersect(n0, n1, o, inv_d, max_distance, exact)) continue;
+		if (!aabb_intersect(n0, n1, so, inv_d, max_distance, exact)) continue;
 
 		const int left_or_first = __float_as_int(n1.z), count = __float_as_int(n1.w);
 		if ((count & 0x3FFFFFFF) > 0) {
@@ -208,15 +259,16 @@ __device__ __forceinline__ bool blas_intersect(const float4 * __restrict__ nodes
 // the order they are visited (right child first), so a hit inner node continues with the next
 // record and everything else follows the record's skip link — no stack, no push, no pop.
 __device__ __forceinline__ bool blas_shadow(const float4 * __restrict__ records, const float4 * __restrict__ hot, v3 o, v3 d, float max_distance) {
-	const v3 inv_d = V(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+	const v3 inv_d = inv_direction(d);
 	const bool exact = !ray_is_regular(o, inv_d);
+	const v3 so = slab_origin(o, inv_d);
 
 	int index = 0;
 	while (index >= 0) {
 		const float4 n0 = load_node(records + 2 * index), n1 = load_node(records + 2 * index + 1);
 		int next = __float_as_int(n1.z);                       // skip link
 		if (next >= 0) prefetch_record(records + 2 * next);
-		if (aabb_intersect(n0, n1, o, inv_d, max_distance, exact)) {
+		if (aabb_intersect(n0, n1, so, inv_d, max_distance, exact)) {
 			const int leaf = __float_as_int(n1.w);
 			if (leaf != 0) {
 				const int first = leaf >> 6, count = leaf & 63;
@@ -277,8 +329,9 @@ __device__ __forceinline__ bool blas_shadow_wide(const float4 * __restrict__ rec
 // (threaded_nodes.h: build_threaded_nodes with an octant). The records come in the sequence the stack traversal pops
 // the nodes in, each tested against the running best.t: same tests, same order, no stack.
 __device__ __forceinline__ void blas_trace_threaded(const float4 * __restrict__ records, const float4 * __restrict__ hot, v3 o, v3 d, int instance, Candidate & best) {
-	const v3 inv_d = V(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+	const v3 inv_d = inv_direction(d);
 	const bool exact = !ray_is_regular(o, inv_d);
+	const v3 so = slab_origin(o, inv_d);
 
 	int index = 0;
 	while (index >= 0) {
@@ -286,7 +339,7 @@ __device__ __forceinline__ void blas_trace_threaded(const float4 * __restrict__ 
 		int next = __float_as_int(n1.z);                       // skip link
 		if (next >= 0) prefetch_record(records + 2 * next);
 		const int leaf = __float_as_int(n1.w);                 // bit 31: continuation of a long leaf, no box test
-		if (leaf < 0 || aabb_intersect(n0, n1, o, inv_d, best.t, exact)) {
+		if (leaf < 0 || aabb_intersect(n0, n1, so, inv_d, best.t, exact)) {
 			if (leaf != 0) {
 				const int first = (leaf & 0x7FFFFFFF) >> 6, count = leaf & 63;
 				for (int i = first; i < first + count; i++) {
@@ -365,8 +418,9 @@ __device__ __forceinline__ void trace_closest(const SceneParams & P, v3 o, v3 d,
 	int tlas_stack[RT_TLAS_STACK_SIZE];
 	int blas_stack[BSTACK];
 
-	const v3 inv_d = V(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+	const v3 inv_d = inv_direction(d);
 	const bool exact = !ray_is_regular(o, inv_d);
+	const v3 so = slab_origin(o, inv_d);
 	int stack_size = 1;
 	tlas_stack[0] = 0;
 
@@ -375,7 +429,7 @@ __device__ __forceinline__ void trace_closest(const SceneParams & P, v3 o, v3 d,
 		const float4 n0 = __ldg(P.tlas_nodes + 2 * index), n1 = __ldg(P.tlas_nodes + 2 * index + 1);
 		if (COUNT) cnt.nodes++;
 
-		if (!aabb_intersect(n0, n1, o, inv_d, best.t, exact)) continue;
+		if (!aabb_intersect(n0, n1, so, inv_d, best.t, exact)) continue;
 
 		const int left_or_first = __float_as_int(n1.z), count = __float_as_int(n1.w);
 		if ((count & 0x3FFFFFFF) > 0) {
@@ -390,10 +444,10 @@ __device__ __forceinline__ void trace_closest(const SceneParams & P, v3 o, v3 d,
 					const int octant = P.traversal_naive ? 7 : (local_d.x > 0.0f ? 1 : 0) | (local_d.y > 0.0f ? 2 : 0) | (local_d.z > 0.0f ? 4 : 0);
 					const int records_per_copy = __ldg(&P.instances[instance].reserved[0]);
 					blas_trace_threaded(P.shadow_nodes + 2 * (size_t(inst.shadow_node_offset) + size_t(1 + octant) * size_t(records_per_copy)),
-					                    P.triangles_hot + 3 * size_t(inst.triangle_offset), transform_position(inst.inverse, o), local_d, instance, best);
+					                    P.triangles_test + 3 * size_t(inst.triangle_offset), transform_position(inst.inverse, o), local_d, instance, best);
 				} else
 #endif
-				blas_trace<COUNT>(P.nodes + 2 * size_t(inst.node_offset), P.triangles_hot + 3 * size_t(inst.triangle_offset),
+				blas_trace<COUNT>(P.nodes + 2 * size_t(inst.node_offset), P.triangles_test + 3 * size_t(inst.triangle_offset),
 				                  transform_position(inst.inverse, o), local_d, instance, best, blas_stack, cnt, traversal_order_mask(P, local_d));
 			}
 		} else if (P.traversal_naive || visit_left_first(count, d)) {
@@ -419,8 +473,9 @@ __device__ __forceinline__ bool trace_any(const SceneParams & P, v3 o, v3 d, flo
 	int tlas_stack[RT_TLAS_STACK_SIZE];
 	int blas_stack[COUNT ? BSTACK : 1];   // the shipped any-hit walk is stackless (blas_shadow); only the counting build pushes
 
-	const v3 inv_d = V(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+	const v3 inv_d = inv_direction(d);
 	const bool exact = !ray_is_regular(o, inv_d);
+	const v3 so = slab_origin(o, inv_d);
 	int stack_size = 1;
 	tlas_stack[0] = 0;
 
@@ -429,7 +484,7 @@ __device__ __forceinline__ bool trace_any(const SceneParams & P, v3 o, v3 d, flo
 		const float4 n0 = __ldg(P.tlas_nodes + 2 * index), n1 = __ldg(P.tlas_nodes + 2 * index + 1);
 		if (COUNT) cnt.nodes++;
 
-		if (!aabb_intersect(n0, n1, o, inv_d, max_distance, exact)) continue;
+		if (!aabb_intersect(n0, n1, so, inv_d, max_distance, exact)) continue;
 
 		const int left_or_first = __float_as_int(n1.z), count = __float_as_int(n1.w);
 		if ((count & 0x3FFFFFFF) > 0) {
@@ -437,11 +492,11 @@ __device__ __forceinline__ bool trace_any(const SceneParams & P, v3 o, v3 d, flo
 				const int instance = __ldg(P.tlas_indices + i);
 				const DeviceInstance inst = load_instance_inverse(P.instances + instance);
 				if (COUNT) cnt.instances++;
-				const float4 * hot = P.triangles_hot + 3 * size_t(inst.triangle_offset);
+				const float4 * hot = P.triangles_test + 3 * size_t(inst.triangle_offset);
 				const v3 local_o = transform_position(inst.inverse, o), local_d = transform_direction(inst.inverse, d);
 #ifdef RT_WIDE_SHADOW
 				if (!COUNT) {
-					const v3 local_inv_d = V(1.0f / local_d.x, 1.0f / local_d.y, 1.0f / local_d.z);
+					const v3 local_inv_d = inv_direction(local_d);
 					const int wide_offset = __ldg(&P.instances[instance].reserved[1]);
 					if (wide_offset >= 0 && ray_is_regular(local_o, local_inv_d)) {
 						if (blas_shadow_wide(P.wide_nodes + 8 * size_t(wide_offset), hot, local_o, local_inv_d, local_d, max_distance)) return true;

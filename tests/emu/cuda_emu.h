@@ -36,6 +36,8 @@
 struct __attribute__((aligned(16))) float4 { float x, y, z, w; };
 struct __attribute__((aligned(16))) int4 { int x, y, z, w; };
 struct uint3 { unsigned x, y, z; };
+struct uint2 { unsigned x, y; };
+static inline uint2 make_uint2(unsigned x, unsigned y) { uint2 r; r.x = x; r.y = y; return r; }
 struct dim3 { unsigned x, y, z; dim3(unsigned x_ = 1, unsigned y_ = 1, unsigned z_ = 1) : x(x_), y(y_), z(z_) {} };
 static inline float4 make_float4(float x, float y, float z, float w) { float4 r; r.x = x; r.y = y; r.z = z; r.w = w; return r; }
 
@@ -124,6 +126,10 @@ static inline unsigned emu_lane() { return (threadIdx.x + threadIdx.y * blockDim
 template<typename T> static inline T __shfl_sync(unsigned mask, T v, int lane) { unsigned bits; static_assert(sizeof(T) == 4, "32-bit shuffles only"); memcpy(&bits, &v, 4); bits = emu::warp_exchange(mask, bits, lane & 31); memcpy(&v, &bits, 4); return v; }
 template<typename T> static inline T __shfl_xor_sync(unsigned mask, T v, int lane_mask) { return __shfl_sync(mask, v, int(emu_lane()) ^ lane_mask); }
 template<typename T> static inline T __shfl_up_sync(unsigned mask, T v, unsigned delta) { const int lane = int(emu_lane()); return __shfl_sync(mask, v, lane >= int(delta) ? lane - int(delta) : lane); }
+
+#include <immintrin.h>
+static inline float emu_half_to_float(unsigned short h) { return _cvtsh_ss(h); }
+static inline unsigned emu_float_to_half(float f) { return _cvtss_sh(f, 0); }   // round to nearest even
 
 // atomics: one OS thread runs all fibres, so plain operations are atomic; the yield lets another fibre run between
 // this thread's memory operations, as another SM would on the device

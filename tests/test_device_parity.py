@@ -102,7 +102,7 @@ def test_tile_partition_reassembles_the_frame(golden):
             r.upload_static(golden.pack)
             part = r.render(golden.pack, want_presented=False)["frame_buffer"]
             r.close()
-            assert (merged[part != 0] == 0).all() or True
+            assert (merged[part != 0] == 0).all(), f"stride {n}: phase {phase} wrote pixels another phase had written"
             merged |= part
         assert np.array_equal(merged, full), f"stride {n}"
 
@@ -118,7 +118,6 @@ def test_page_locked_outputs_equal_pageable(golden):
     r.render(golden.pack, out=pinned)
     assert np.array_equal(pinned["frame_buffer"], pageable["frame_buffer"])
     assert np.array_equal(pinned["presented"], pageable["presented"])
-    assert np.array_equal(pinned["frame_buffer"], golden.ref_frame_buffer) or True
     del pinned
     r.close()
 
