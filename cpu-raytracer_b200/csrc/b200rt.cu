@@ -581,7 +581,8 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 // A pool that runs out costs nothing but speed: the producer walks that subtree depth-first (FrameCounters::q_fallbacks).
 static int ensure_queue(b200rt_ctx * ctx, SceneParams & P) {
 	const size_t pixels = size_t(std::max(ctx->tile_count_mine, 1)) * 1024;
-	const size_t nodes = std::min<size_t>(4 * pixels, (size_t(1) << 26) - 1), bounce = 4 * pixels, shadow = 8 * pixels;
+	size_t nodes = std::min<size_t>(4 * pixels, (size_t(1) << 26) - 1), bounce = 4 * pixels, shadow = 8 * pixels;
+	if (const char * text = getenv("B200RT_QUEUE_CAPACITY")) nodes = bounce = shadow = size_t(std::max(atoi(text), 32));   // tests: small pools force the fall-back paths
 	if (!ctx->q_nodes.ptr) {
 		CHECK_CUDA(ctx, ctx->q_nodes.ensure(nodes * 6 * sizeof(float4)));
 		CHECK_CUDA(ctx, ctx->q_bounce.ensure(bounce * 5 * sizeof(float4)));

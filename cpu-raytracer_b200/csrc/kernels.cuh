@@ -96,10 +96,17 @@ render_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, float *
 	flush_ray_counters(counters, cnt, primary, COUNT);
 }
 
-// The same frame with the deep-pixel queue (render.cuh): a warp takes, in this order of preference, 32 bounce items,
-// 32 shadow items, a tile unit, whatever items are left — and leaves when the frame's count of outstanding work
-// (units not finished + items not finished) is zero. Items first: the rays of the deep pixels are the frame's
+// The same frame with the deep-pixel queue (render.cuh). A warp takes, in this order of preference, 32 bounce items,
+// 32 shadow items, a tile unit, whatever items are left. Items first: the rays of the deep pixels are the frame's
 // critical path, and popping them as soon as a full warp's worth exists keeps the queues (and their L2 footprint) short.
+//
+// A warp that finds nothing LEAVES — after looking three more times, 2 / 4 / 8 us apart — instead of waiting for the
+// frame to end: whoever publishes an item looks at the queues again right afterwards, so every item is taken by
+// somebody still running, and the number of warps at work follows the supply of items by itself. (The first version
+// kept all 4 736 resident warps polling the cursors until the frame's count of outstanding work was zero: the polls
+// saturated the one L2 slice that holds them and the frame took 150 ms instead of 1 — profiles/r02_variants_call1.jsonl.)
+// The count of outstanding work (tile units + items not finished) is still kept: a warp that sees it at zero knows
+// that nothing can appear any more and leaves at once.
 template<int MAXB, int BSTACK>
 __global__ void __launch_bounds__(RT_BLOCK_THREADS, RT_MIN_BLOCKS)
 render_queue_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, float * __restrict__ colour_float, FrameCounters * counters) {
@@ -110,7 +117,8 @@ render_queue_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, f
 
 	Counters cnt = { 0, 0, 0, 0, 0, 0, 0, 0 };
 	unsigned primary = 0;
-	bool was_idle = false;
+	int idle_looks = 0;
+	bool units_left = total_units > 0;   // this warp's view; once false it stays false (the cursor only grows)
 
 	if (threadIdx.x == 0) atomicMax(&counters->first_start_ns, ~global_timer_ns());
 
@@ -118,10 +126,9 @@ render_queue_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, f
 		// ---- lane 0 chooses the warp's next piece of work ------------------------------------------------
 		int kind = WORK_NONE; unsigned first = 0, n = 0;
 		if (lane == 0) {
-			for (int attempt = 0; attempt < 8 && kind == WORK_NONE; attempt++) {
+			for (int attempt = 0; attempt < 4 && kind == WORK_NONE; attempt++) {
 				const unsigned hb = peek(&counters->q_bounce_head), rb = min(peek(&counters->q_bounce_reserved), P.q_bounce_capacity), ab = rb > hb ? rb - hb : 0u;
 				const unsigned hs = peek(&counters->q_shadow_head), rs = min(peek(&counters->q_shadow_reserved), P.q_shadow_capacity), as = rs > hs ? rs - hs : 0u;
-				const bool units_left = peek(&counters->next_unit) < total_units;
 				if (ab >= 32u || (ab > 0u && !units_left && as < 32u)) {
 					n = min(ab, 32u);
 					if (atomicCAS(&counters->q_bounce_head, hb, hb + n) == hb) { kind = WORK_BOUNCE; first = hb; }
@@ -130,17 +137,17 @@ render_queue_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, f
 					if (atomicCAS(&counters->q_shadow_head, hs, hs + n) == hs) { kind = WORK_SHADOW; first = hs; }
 				} else if (units_left) {
 					first = atomicAdd(&counters->next_unit, 1u);
-					if (first < total_units) kind = WORK_UNIT;
+					if (first < total_units) kind = WORK_UNIT; else units_left = false;
 				} else break;
 			}
-			if (kind == WORK_NONE && peek(&counters->q_outstanding) > 0) kind = WORK_WAIT;   // nothing to take, or every race lost: look again
+			if (kind == WORK_NONE && idle_looks < 3 && peek(&counters->q_outstanding) > 0) kind = WORK_WAIT;
 		}
 		kind = __shfl_sync(0xffffffffu, kind, 0); first = __shfl_sync(0xffffffffu, first, 0); n = __shfl_sync(0xffffffffu, n, 0);
 		if (kind == WORK_NONE) break;
 		if (kind == WORK_WAIT) {
-			if (lane == 0 && !was_idle) atomicMax(&counters->first_idle_ns, ~global_timer_ns());
-			was_idle = true;
-			__nanosleep(200);
+			if (lane == 0 && idle_looks == 0) atomicMax(&counters->first_idle_ns, ~global_timer_ns());
+			__nanosleep(2000u << idle_looks);
+			idle_looks++;
 			continue;
 		}
 
@@ -183,7 +190,7 @@ render_queue_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, f
 
 	if (lane == 0) {
 		const unsigned long long now = global_timer_ns();
-		if (!was_idle) atomicMax(&counters->first_idle_ns, ~now);
+		if (idle_looks == 0) atomicMax(&counters->first_idle_ns, ~now);
 		atomicMax(&counters->last_done_ns, now);
 	}
 	flush_ray_counters(counters, cnt, primary, false);
@@ -303,10 +310,11 @@ texture_mip_kernel(const float4 * __restrict__ previous, float4 * __restrict__ o
 #define FXAA_TILE_W 64
 #define FXAA_TILE_H 4
 
-__device__ __forceinline__ v3 fxaa_screen(const unsigned * __restrict__ fb, const float * gamma, int W, int H, float fx, float fy) {
-	// GL_REPEAT. The taps reach a few pixels beyond the frame at most: the integer division of positive_mod
+// texture2D(screen, uv): texel (floor(u * W) mod W, floor(v * H) mod H) (OpenGL 4.2 spec 3.9.11: NEAREST, GL_REPEAT)
+__device__ __forceinline__ v3 fxaa_screen(const unsigned * __restrict__ fb, const float * gamma, int W, int H, float u, float v) {
+	// The taps reach a few pixels beyond the frame at most: the integer division of positive_mod
 	// (~20 instructions, 18 of them per pixel) is only paid by the pixels that do wrap
-	int x = int(floorf(fx)), y = int(floorf(fy));
+	int x = int(floorf(u * float(W))), y = int(floorf(v * float(H)));
 	if (x < 0 || x >= W) x = positive_mod(x, W);
 	if (y < 0 || y >= H) y = positive_mod(y, H);
 	const unsigned c = __ldg(fb + size_t(x) + size_t(W) * y);
@@ -332,19 +340,20 @@ fxaa_kernel(const unsigned * __restrict__ fb, unsigned char * __restrict__ rgb8,
 	const int py = row_begin + blockIdx.y * FXAA_TILE_H + threadIdx.y; // rows [row_begin, row_end): the whole frame, or this GPU's band
 
 	if (px < W && py < row_end) {
-		const float cx = float(px) + 0.5f, cy = float(py) + 0.5f;
+		// The shader's own coordinates: in_uv = ((px + .5) / W, (py + .5) / H) (vertex.glsl:7-11), inv_screen_size = (1 / W, 1 / H)
+		// (Window.cpp:57); taps are formed in uv space like the GLSL's and only fxaa_screen() goes back to texels.
+		const float inv_x = 1.0f / float(W), inv_y = 1.0f / float(H);
+		const float in_u = (float(px) + 0.5f) / float(W), in_v = (float(py) + 0.5f) / float(H);
 		v3 out;
 		if (!enable_fxaa) {
-			out = fxaa_screen(fb, gamma, W, H, cx, cy);
+			out = fxaa_screen(fb, gamma, W, H, in_u, in_v);
 		} else {
-			// vec2(+-inv.x, +-inv_screen_size) takes .x for both components (fragment_fxaa.glsl:25-28):
-			// +-1 px in x, +-H/W px in y
-			const float diag_y = float(H) / float(W);
-			const float luma_tl = fxaa_luma(fxaa_screen(fb, gamma, W, H, cx - 1.0f, cy - diag_y));
-			const float luma_tr = fxaa_luma(fxaa_screen(fb, gamma, W, H, cx + 1.0f, cy - diag_y));
-			const float luma_bl = fxaa_luma(fxaa_screen(fb, gamma, W, H, cx - 1.0f, cy + diag_y));
-			const float luma_br = fxaa_luma(fxaa_screen(fb, gamma, W, H, cx + 1.0f, cy + diag_y));
-			const float luma_m  = fxaa_luma(fxaa_screen(fb, gamma, W, H, cx, cy));
+			// vec2(+-inv.x, +-inv_screen_size) takes .x for both components (fragment_fxaa.glsl:25-28)
+			const float luma_tl = fxaa_luma(fxaa_screen(fb, gamma, W, H, in_u - inv_x, in_v - inv_x));
+			const float luma_tr = fxaa_luma(fxaa_screen(fb, gamma, W, H, in_u + inv_x, in_v - inv_x));
+			const float luma_bl = fxaa_luma(fxaa_screen(fb, gamma, W, H, in_u - inv_x, in_v + inv_x));
+			const float luma_br = fxaa_luma(fxaa_screen(fb, gamma, W, H, in_u + inv_x, in_v + inv_x));
+			const float luma_m  = fxaa_luma(fxaa_screen(fb, gamma, W, H, in_u, in_v));
 
 			const float luma_min = fminf(fminf(fminf(luma_tl, luma_tr), fminf(luma_bl, luma_br)), luma_m);
 			const float luma_max = fmaxf(fmaxf(fmaxf(luma_tl, luma_tr), fmaxf(luma_bl, luma_br)), luma_m);
@@ -355,14 +364,14 @@ fxaa_kernel(const unsigned * __restrict__ fb, unsigned char * __restrict__ rgb8,
 			const float reduce = fmaxf(1.0f / 128.0f, (luma_tl + luma_tr + luma_bl + luma_br) * 0.25f * (1.0f / 8.0f));
 			const float adjust = 1.0f / (fminf(fabsf(dir_x), fabsf(dir_y)) + reduce);
 
-			dir_x = fminf(fmaxf(dir_x * adjust, -8.0f), 8.0f); // in pixels: * inv_screen_size * screen_size
-			dir_y = fminf(fmaxf(dir_y * adjust, -8.0f), 8.0f);
+			dir_x = fminf(fmaxf(dir_x * adjust, -8.0f), 8.0f) * inv_x; // :46
+			dir_y = fminf(fmaxf(dir_y * adjust, -8.0f), 8.0f) * inv_y;
 
 			const float k1 = 1.0f / 3.0f - 0.5f, k2 = 2.0f / 3.0f - 0.5f;
-			const v3 a0 = fxaa_screen(fb, gamma, W, H, cx + dir_x * k1, cy + dir_y * k1);
-			const v3 a1 = fxaa_screen(fb, gamma, W, H, cx + dir_x * k2, cy + dir_y * k2);
-			const v3 b0 = fxaa_screen(fb, gamma, W, H, cx + dir_x * -0.5f, cy + dir_y * -0.5f);
-			const v3 b1 = fxaa_screen(fb, gamma, W, H, cx + dir_x * 0.5f,  cy + dir_y * 0.5f);
+			const v3 a0 = fxaa_screen(fb, gamma, W, H, in_u + dir_x * k1, in_v + dir_y * k1);
+			const v3 a1 = fxaa_screen(fb, gamma, W, H, in_u + dir_x * k2, in_v + dir_y * k2);
+			const v3 b0 = fxaa_screen(fb, gamma, W, H, in_u + dir_x * -0.5f, in_v + dir_y * -0.5f);
+			const v3 b1 = fxaa_screen(fb, gamma, W, H, in_u + dir_x * 0.5f,  in_v + dir_y * 0.5f);
 
 			const v3 result_a = (a0 + a1) * 0.5f;
 			const v3 result_b = (b0 + b1) * 0.5f;

@@ -450,10 +450,7 @@ __device__ __forceinline__ void warp_add(int * counter, int n) {
 __device__ __forceinline__ unsigned peek(const unsigned * p) { return *reinterpret_cast<const volatile unsigned *>(p); }   // a fresh value, not this SM's L1 copy
 __device__ __forceinline__ int      peek(const int * p)      { return *reinterpret_cast<const volatile int *>(p); }
 
-__device__ __forceinline__ void publish(unsigned * ready, unsigned slot, unsigned serial) {
-	__threadfence();
-	__stcg(ready + slot, serial);
-}
+__device__ __forceinline__ void publish(unsigned * ready, unsigned slot, unsigned serial) { __stcg(ready + slot, serial); }   // behind a __threadfence() that follows the payload
 __device__ __forceinline__ void write_bounce_item(const SceneParams & P, unsigned slot, const Ray & r, int parent, int which, int bounces_left) {
 	float4 * item = P.q_bounce + 5 * size_t(slot);
 	__stcg(item,     make_float4(r.origin.x, r.origin.y, r.origin.z, r.direction.x));
@@ -461,7 +458,6 @@ __device__ __forceinline__ void write_bounce_item(const SceneParams & P, unsigne
 	__stcg(item + 2, make_float4(r.dO_dx.z, r.dO_dy.x, r.dO_dy.y, r.dO_dy.z));
 	__stcg(item + 3, make_float4(r.dD_dx.x, r.dD_dx.y, r.dD_dx.z, r.dD_dy.x));
 	__stcg(item + 4, make_float4(r.dD_dy.y, r.dD_dy.z, as_f(parent), as_f(which | (bounces_left << 1))));
-	publish(P.q_bounce_ready, slot, P.frame_serial);
 }
 __device__ __forceinline__ void read_bounce_item(const SceneParams & P, unsigned slot, Ray & r, int & parent, int & which, int & bounces_left) {
 	const float4 * item = P.q_bounce + 5 * size_t(slot);
@@ -473,13 +469,11 @@ __device__ __forceinline__ void read_bounce_item(const SceneParams & P, unsigned
 }
 __device__ __forceinline__ void write_null_bounce_item(const SceneParams & P, unsigned slot) {
 	__stcg(P.q_bounce + 5 * size_t(slot) + 4, make_float4(0.0f, 0.0f, as_f(QUEUE_NULL_ITEM), 0.0f));
-	publish(P.q_bounce_ready, slot, P.frame_serial);
 }
 __device__ __forceinline__ void write_shadow_item(const SceneParams & P, unsigned slot, v3 origin, v3 direction, float max_distance, int word) {
 	float4 * item = P.q_shadow + 2 * size_t(slot);
 	__stcg(item,     make_float4(origin.x, origin.y, origin.z, max_distance));
 	__stcg(item + 1, make_float4(direction.x, direction.y, direction.z, as_f(word)));
-	publish(P.q_shadow_ready, slot, P.frame_serial);
 }
 
 // One call of bounce() as a work item. WARP-COLLECTIVE: all 32 lanes call it; `active` lanes carry a ray.
@@ -557,6 +551,9 @@ __device__ __forceinline__ void process_bounce(const SceneParams & P, const Pixe
 	if (node_slot >= P.q_node_capacity) { // no record to be had: walk the subtree here; the item slots reserved above are published empty
 		for (int k = 0; k < n_children; k++) if (bounce_slot + k < P.q_bounce_capacity) write_null_bounce_item(P, bounce_slot + k);
 		for (int i = 0; i < n_shadow; i++)   if (shadow_slot + i < P.q_shadow_capacity) write_shadow_item(P, shadow_slot + i, hit.point, hit.normal, 0.0f, QUEUE_NULL_ITEM);
+		__threadfence();
+		for (int k = 0; k < n_children; k++) if (bounce_slot + k < P.q_bounce_capacity) publish(P.q_bounce_ready, bounce_slot + k, P.frame_serial);
+		for (int i = 0; i < n_shadow; i++)   if (shadow_slot + i < P.q_shadow_capacity) publish(P.q_shadow_ready, shadow_slot + i, P.frame_serial);
 		float distance;
 		const v3 value = shade_subtree_call<MAXB, BSTACK>(P, ray, bounces_left, cnt, distance, &best);
 		deliver(P, out, parent, which, value, distance);
@@ -571,38 +568,42 @@ __device__ __forceinline__ void process_bounce(const SceneParams & P, const Pixe
 	__stcg(rec + 1, make_float4(hit.point.x, hit.point.y, hit.point.z, best.t));
 	__stcg(rec + 2, make_float4(hit.normal.x, hit.normal.y, hit.normal.z, F_r));
 	__stcg(rec + 3, make_float4(material_diffuse.x, material_diffuse.y, material_diffuse.z, as_f(0)));
-	// (every item is published behind a __threadfence(): the record is in L2 before an item that names it can be seen)
-
-	unsigned slot = bounce_slot;
-	for (int k = 0; k < 2; k++) { // children (Raytracer.cpp:249-271, :316-342); a child without a slot is walked here
-		const bool present = k == 0 ? (flags & FRAME_HAS_REFLECTION) != 0 : ((flags & FRAME_HAS_REFRACTION) && !(flags & FRAME_TIR));
-		if (!present) continue;
+	// Payloads first — the record above, every item that has a slot — then ONE __threadfence(), then the items' ready
+	// words: record and items are in L2 before any consumer can see an item that names the record. Whatever found no
+	// slot is walked right here afterwards (its report may complete the record: the record is visible by then).
+	const bool has_child[2] = { (flags & FRAME_HAS_REFLECTION) != 0, (flags & FRAME_HAS_REFRACTION) && !(flags & FRAME_TIR) };
+	unsigned child_slot[2] = { bounce_slot, bounce_slot + (has_child[0] ? 1u : 0u) };
+	for (int k = 0; k < 2; k++) { // children (Raytracer.cpp:249-271, :316-342)
+		if (!has_child[k]) continue;
 		if (k == 0) cnt.reflection++; else cnt.refraction++;
-		const Ray & child = k == 0 ? reflected : refracted;
-		if (slot < P.q_bounce_capacity) {
-			write_bounce_item(P, slot, child, node, k, bounces_left - 1);
-		} else {
-			__threadfence();
-			float distance;
-			const v3 value = shade_subtree_call<MAXB, BSTACK>(P, child, bounces_left - 1, cnt, distance, nullptr);
-			deliver(P, out, node, k, value, distance);
-			atomicAdd(&counters->q_fallbacks, 1u);
-			atomicSub(&counters->q_outstanding, 1);
-		}
-		slot++;
+		if (child_slot[k] < P.q_bounce_capacity) write_bounce_item(P, child_slot[k], k == 0 ? reflected : refracted, node, k, bounces_left - 1);
 	}
 	for (int i = 0; i < n_shadow; i++) { // shadow rays (:155-198)
+		cnt.shadow++;
+		if (shadow_slot + i >= P.q_shadow_capacity) continue;
 		LightSample s;
 		light_sample(P, i, hit.point, s);
-		cnt.shadow++;
-		if (shadow_slot + i < P.q_shadow_capacity) {
-			write_shadow_item(P, shadow_slot + i, hit.point, s.to_light, s.distance, (node << 5) | i);
-		} else {
-			__threadfence();
-			deliver_shadow(P, out, node, i, trace_any<false, BSTACK>(P, hit.point, s.to_light, s.distance, cnt));
-			atomicAdd(&counters->q_fallbacks, 1u);
-			atomicSub(&counters->q_outstanding, 1);
-		}
+		write_shadow_item(P, shadow_slot + i, hit.point, s.to_light, s.distance, (node << 5) | i);
+	}
+	__threadfence();
+	for (int k = 0; k < 2; k++) if (has_child[k] && child_slot[k] < P.q_bounce_capacity) publish(P.q_bounce_ready, child_slot[k], P.frame_serial);
+	for (int i = 0; i < n_shadow; i++) if (shadow_slot + i < P.q_shadow_capacity) publish(P.q_shadow_ready, shadow_slot + i, P.frame_serial);
+
+	for (int k = 0; k < 2; k++) { // a pool was exhausted: no slot, no item
+		if (!has_child[k] || child_slot[k] < P.q_bounce_capacity) continue;
+		float distance;
+		const v3 value = shade_subtree_call<MAXB, BSTACK>(P, k == 0 ? reflected : refracted, bounces_left - 1, cnt, distance, nullptr);
+		deliver(P, out, node, k, value, distance);
+		atomicAdd(&counters->q_fallbacks, 1u);
+		atomicSub(&counters->q_outstanding, 1);
+	}
+	for (int i = 0; i < n_shadow; i++) {
+		if (shadow_slot + i < P.q_shadow_capacity) continue;
+		LightSample s;
+		light_sample(P, i, hit.point, s);
+		deliver_shadow(P, out, node, i, trace_any<false, BSTACK>(P, hit.point, s.to_light, s.distance, cnt));
+		atomicAdd(&counters->q_fallbacks, 1u);
+		atomicSub(&counters->q_outstanding, 1);
 	}
 }
 

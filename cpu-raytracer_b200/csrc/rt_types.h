@@ -111,13 +111,12 @@ struct FrameCounters {   // accumulated with one atomicAdd per warp
 	unsigned int pad;
 	unsigned long long first_idle_ns, last_done_ns; // globaltimer when the first (stored as ~t) / the last warp ran out of work: the tail of the launch
 	unsigned long long first_start_ns, pad2[3];     // globaltimer when the first block started (stored as ~t)
-	// deep-pixel queue, on a 128-byte line of its own: pool cursors, and the frame's outstanding work
-	// (tile units not finished + items not finished; the queue kernel's warps leave when it is zero)
-	unsigned int q_node_reserved, q_bounce_reserved, q_shadow_reserved, q_fallbacks;
-	unsigned int q_bounce_head, q_shadow_head;
-	int q_outstanding;
-	unsigned int q_pad[25];
+	// deep-pixel queue (render.cuh). Producers' cursors, consumers' heads and the count of outstanding work (tile units
+	// + items not finished) each on a 128-byte line of their own: they are hit by different warps at the same time
+	unsigned int q_node_reserved, q_bounce_reserved, q_shadow_reserved, q_fallbacks, q_pad0[28];
+	unsigned int q_bounce_head, q_shadow_head, q_pad1[30];
+	int q_outstanding; unsigned int q_pad2[31];
 };
-static_assert(sizeof(FrameCounters) == 256, "two 128-byte lines");
+static_assert(sizeof(FrameCounters) == 512, "four 128-byte lines");
 
 } // namespace rt

@@ -1012,9 +1012,11 @@ int oracle_render(const b200rt_static_scene * scene, const b200rt_frame * frame,
  * "parity unpinned" for this pass only: no reference execution of the shader is possible. */
 typedef struct { const uint32_t * fb; int w, h; const float * gamma; } screen_t;
 
-static inline v3 get_screen(const screen_t * s, float px, float py) { /* texel containing pixel-space point (px, py) */
-	int x = positive_mod((int)floorf(px), s->w);
-	int y = positive_mod((int)floorf(py), s->h);
+/* texture2D(screen, uv) on the NEAREST / GL_REPEAT sampler of Window.cpp:48-50: the texel is
+ * (floor(u * W) mod W, floor(v * H) mod H) (OpenGL 4.2 spec 3.9.11: unnormalised coordinate, floor, wrap). */
+static inline v3 get_screen(const screen_t * s, float u, float v) {
+	int x = positive_mod((int)floorf(u * (float)s->w), s->w);
+	int y = positive_mod((int)floorf(v * (float)s->h), s->h);
 	uint32_t c = s->fb[(size_t)x + (size_t)s->w * y];
 	return V(s->gamma[(c >> 16) & 255], s->gamma[(c >> 8) & 255], s->gamma[c & 255]);
 }
@@ -1034,22 +1036,25 @@ void oracle_present(const uint32_t * frame_buffer, int width, int height, int en
 	oracle_gamma_table(gamma);
 	screen_t s = { frame_buffer, width, height, gamma };
 
-	/* vec2(+-inv.x, +-inv_screen_size) takes .x for BOTH components (fragment_fxaa.glsl:25-28):
-	 * the diagonal taps are (+-1/W, +-1/W) in uv, i.e. +-1 px in x and +-H/W px in y. */
-	const float diag_y = (float)height / (float)width;
+	/* The shader's own coordinates: in_uv = ((px + .5) / W, (py + .5) / H) (vertex.glsl:7-11, interpolated to the pixel
+	 * centre), inv_screen_size = (1 / W, 1 / H) (Window.cpp:57). Every tap is formed in uv space, as the GLSL forms it, and
+	 * only get_screen() goes back to texels: a tap within rounding distance of a texel border picks the texel the shader's
+	 * arithmetic picks (round 1 stepped in pixel space: 60 of 2 073 600 pixels came out differently at 1080p). */
+	const float inv_x = 1.0f / (float)width, inv_y = 1.0f / (float)height;
 
 	for (int py = 0; py < height; py++) {
 		for (int px = 0; px < width; px++) {
-			const float cx = (float)px + 0.5f, cy = (float)py + 0.5f;
+			const float in_u = ((float)px + 0.5f) / (float)width, in_v = ((float)py + 0.5f) / (float)height;
 			v3 out;
 			if (!enable_fxaa) { /* fragment_identity.glsl */
-				out = get_screen(&s, cx, cy);
+				out = get_screen(&s, in_u, in_v);
 			} else {
-				float luma_tl = luma_of(get_screen(&s, cx - 1.0f, cy - diag_y));
-				float luma_tr = luma_of(get_screen(&s, cx + 1.0f, cy - diag_y));
-				float luma_bl = luma_of(get_screen(&s, cx - 1.0f, cy + diag_y));
-				float luma_br = luma_of(get_screen(&s, cx + 1.0f, cy + diag_y));
-				float luma_m  = luma_of(get_screen(&s, cx, cy));
+				/* vec2(+-inv.x, +-inv_screen_size) takes .x for BOTH components (fragment_fxaa.glsl:25-28) */
+				float luma_tl = luma_of(get_screen(&s, in_u - inv_x, in_v - inv_x));
+				float luma_tr = luma_of(get_screen(&s, in_u + inv_x, in_v - inv_x));
+				float luma_bl = luma_of(get_screen(&s, in_u - inv_x, in_v + inv_x));
+				float luma_br = luma_of(get_screen(&s, in_u + inv_x, in_v + inv_x));
+				float luma_m  = luma_of(get_screen(&s, in_u, in_v));
 
 				float luma_min = fminf(fminf(fminf(luma_tl, luma_tr), fminf(luma_bl, luma_br)), luma_m);
 				float luma_max = fmaxf(fmaxf(fmaxf(luma_tl, luma_tr), fmaxf(luma_bl, luma_br)), luma_m);
@@ -1060,15 +1065,15 @@ void oracle_present(const uint32_t * frame_buffer, int width, int height, int en
 				float reduce = fmaxf(1.0f / 128.0f, (luma_tl + luma_tr + luma_bl + luma_br) * 0.25f * (1.0f / 8.0f));
 				float adjust = 1.0f / (fminf(fabsf(dir_x), fabsf(dir_y)) + reduce);
 
-				/* clamp(dir * adjust, -8, 8) * inv_screen_size, then * screen size again = pixels */
-				dir_x = fminf(fmaxf(dir_x * adjust, -8.0f), 8.0f);
-				dir_y = fminf(fmaxf(dir_y * adjust, -8.0f), 8.0f);
+				/* clamp(dir * adjust, -8, 8) * inv_screen_size (:46) */
+				dir_x = fminf(fmaxf(dir_x * adjust, -8.0f), 8.0f) * inv_x;
+				dir_y = fminf(fmaxf(dir_y * adjust, -8.0f), 8.0f) * inv_y;
 
 				const float k1 = 1.0f / 3.0f - 0.5f, k2 = 2.0f / 3.0f - 0.5f;
-				v3 a0 = get_screen(&s, cx + dir_x * k1, cy + dir_y * k1);
-				v3 a1 = get_screen(&s, cx + dir_x * k2, cy + dir_y * k2);
-				v3 b0 = get_screen(&s, cx + dir_x * -0.5f, cy + dir_y * -0.5f);
-				v3 b1 = get_screen(&s, cx + dir_x * 0.5f,  cy + dir_y * 0.5f);
+				v3 a0 = get_screen(&s, in_u + dir_x * k1, in_v + dir_y * k1);
+				v3 a1 = get_screen(&s, in_u + dir_x * k2, in_v + dir_y * k2);
+				v3 b0 = get_screen(&s, in_u + dir_x * -0.5f, in_v + dir_y * -0.5f);
+				v3 b1 = get_screen(&s, in_u + dir_x * 0.5f,  in_v + dir_y * 0.5f);
 
 				v3 result_a = scale(add(a0, a1), 0.5f);
 				v3 result_b = scale(add(b0, b1), 0.5f);
