@@ -2,21 +2,25 @@
 """bench.py — the headline benchmark of the render hot path (BASELINE.json: Mrays/s and frames/s,
 Sponza 1920x1080, trilinear mip-maps, point + directional light with shadows, 3 bounces).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload sponza1080|dielectrics|sibenik4k]
 
 One "step" = one frame of the hot path: trace every tile (primary rays, shadow rays, reflection /
 refraction recursion, texture filtering) + the FXAA pass. Prints ONE JSON line on rank 0.
 
-  value   whole-job Mrays/s with every input resident in HBM (kernels only, CUDA events on the
-          launching stream, L2 flushed between steps), rays = active rays of the frame
-  e2e     the same metric through the public per-frame calls (b200rt_submit_frame / b200rt_wait_frame; on N
-          GPUs b200rt_render_frame_device + b200rt_present_rows_device per rank): host Scene::update,
-          pinned-host -> device copy of the frame data, kernels, device -> host read of both images (on N
-          GPUs every rank delivers its row band over its own PCIe link into one frame in shared host memory)
-  roofline  render kernel: algorithmic bytes of the frame (DESIGN.md "Algorithmic bytes") / its
-          CUDA-event duration, against the measured HBM copy peak (MEASURED_PEAKS.json)
+  value   whole-job Mrays/s with every input resident in HBM: kernels only, one frame at a time, CUDA events on the
+          launching stream, L2 flushed before every timed frame (cold L2, nothing overlaps); rays = active rays
+  e2e     the same metric through the public per-frame calls with HOST buffers (b200rt_submit_frame /
+          b200rt_wait_frame; on N GPUs b200rt_render_frame_device + b200rt_barrier + b200rt_present_rows_device per
+          rank): host Scene::update incl. the TLAS rebuild, pinned-host -> device copy of the frame data, kernels,
+          device -> host read of both images; two frames in flight (warm L2, copies overlap the next frame's
+          tracing) — on N GPUs every rank delivers its row band over its own PCIe link into one frame in shared
+          host memory
+  roofline  the render kernel against the limit that binds it: lane-instructions issued / (148 SMs x 4 schedulers x
+          32 lanes x SM clock). The traversal stream SURVEY.md 8(d) defines (algorithmic bytes per ray) is reported
+          beside it with the DRAM, L2 and L1 rates of the same launch (ncu, profiles/): the stream is served by the
+          caches, so the HBM peak is not what bounds this kernel
   cpu_baseline  the reference's own AVX renderer (oracle/_ref, SIMD_LANE_SIZE 8, all host threads)
-          on a bounded sample of the same workload
+          on a bounded sample of the same workload (no FXAA on the CPU side: the reference runs it in GL)
 
 Sponza's OBJ is absent from the reference checkout (.MISSING_LARGE_BLOBS) and there is no network:
 the geometry is the deterministic procedural stand-in of cpu-raytracer_b200/python/b200rt/standin.py
@@ -24,6 +28,8 @@ the geometry is the deterministic procedural stand-in of cpu-raytracer_b200/pyth
 
 --impl reference: times the reference's CPU implementation of the same path on the host cores
 (rank 0 only), same metric / unit / config.
+With --gpus N > 1 the line also carries `scale_4k`: the same measurement on configs[4] (Sibenik 3840x2160), the
+scaling case north_star names; `value` stays on the headline configuration.
 """
 import argparse
 import json
@@ -37,31 +43,39 @@ import time
 REPO = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.join(REPO, "cpu-raytracer_b200", "python"))
 
-WIDTH, HEIGHT, BOUNCES, FILTER = 1920, 1080, 3, "tri"
-REF_VARIANT = "l8_b3_tri"
-METRIC = "Mrays/s, Sponza(stand-in) 1920x1080, trilinear mip-maps, point+directional light with shadows, 3 bounces"
-WORKLOAD = "configs[1]: Sponza 1920x1080 trilinear, point + directional lights with shadows, 3 bounces (stand-in geometry, seed 1234)"
-SCENE = "sponza"
-DATA_NOTE = "synthetic (procedural Sponza stand-in, seed 1234; sponza.obj is missing from the reference checkout)"
 L2_FLUSH_BYTES = 256 << 20
 
-# --workload sibenik4k: BASELINE.json configs[4] (the multi-GPU scaling case of north_star), not the headline line
-OTHER_WORKLOADS = {
-    "sibenik4k": dict(WIDTH=3840, HEIGHT=2160, BOUNCES=3, FILTER="aniso", REF_VARIANT="l8_b3_aniso", SCENE="sibenik",
-                      DATA_NOTE="synthetic (procedural Sibenik stand-in, seed 4321; sibenik.obj is missing from the reference checkout)",
-                      METRIC="Mrays/s, Sibenik(stand-in) 3840x2160, anisotropic mip-maps, spot+point light with shadows, 3 bounces",
-                      WORKLOAD="configs[4]: Sibenik 3840x2160, spot + point shadows, 3 bounces, tiles partitioned across the GPUs (stand-in geometry, seed 4321)"),
+WORKLOADS = {
+    "sponza1080": dict(
+        width=1920, height=1080, bounces=3, filter="tri", ref_variant="l8_b3_tri", scene="sponza",
+        data="synthetic (procedural Sponza stand-in, seed 1234; sponza.obj is missing from the reference checkout)",
+        metric="Mrays/s, Sponza(stand-in) 1920x1080, trilinear mip-maps, point+directional light with shadows, 3 bounces",
+        workload="configs[1]: Sponza 1920x1080 trilinear, point + directional lights with shadows, 3 bounces (stand-in geometry, seed 1234)"),
+    "dielectrics": dict(
+        width=1920, height=1080, bounces=8, filter="ewa", ref_variant="l8_b8_ewa", scene="dielectrics",
+        data="synthetic hall (procedural Sponza stand-in, seed 1234) + the reference's own Magnifier.obj, Diamond.obj, Concave.obj and the glass spheres of Scene.cpp:8-19",
+        metric="Mrays/s, dielectrics in the Sponza(stand-in) hall 1920x1080, EWA filter (MAX_ANISOTROPY 8), 8 bounces",
+        workload="configs[3]: Diamond.obj, Magnifier.obj and two glass spheres inside the Sponza hall, 8-deep reflect/refract recursion, EWA filtering (stand-in hall, seed 1234)"),
+    "sibenik4k": dict(
+        width=3840, height=2160, bounces=3, filter="aniso", ref_variant="l8_b3_aniso", scene="sibenik",
+        data="synthetic (procedural Sibenik stand-in, seed 4321; sibenik.obj is missing from the reference checkout)",
+        metric="Mrays/s, Sibenik(stand-in) 3840x2160, anisotropic mip-maps, spot+point light with shadows, 3 bounces",
+        workload="configs[4]: Sibenik 3840x2160, spot + point shadows, 3 bounces, tiles partitioned across the GPUs (stand-in geometry, seed 4321)"),
 }
+FILTER_NAMES = {"tri": "trilinear", "aniso": "anisotropic", "ewa": "ewa"}
 
 
-def workload_config(n_gpus):
-    return {
-        "workload": WORKLOAD,
-        "resolution": [WIDTH, HEIGHT], "bounces": BOUNCES, "mipmap_filter": {"tri": "trilinear", "aniso": "anisotropic", "ewa": "ewa"}[FILTER], "fxaa": True,
+def workload_config(w, n_gpus, settings=None):
+    config = {
+        "workload": w["workload"],
+        "resolution": [w["width"], w["height"]], "bounces": w["bounces"], "mipmap_filter": FILTER_NAMES[w["filter"]], "fxaa": True,
         "tiles": "32x32, tile t -> GPU t %% %d, device-side work counter per GPU" % n_gpus,
-        "l2": "flushed between timed steps (256 MiB memset, outside the timed region)",
+        "l2": "value: flushed before every timed frame (256 MiB memset, outside the timed region); e2e: as the frame loop leaves it",
         "ray_count": "active rays (primary + shadow + reflection + refraction), reference's PerformanceStats per ray",
     }
+    if settings:
+        config.update(settings)
+    return config
 
 
 def load_peaks():
@@ -106,10 +120,17 @@ class ClockSampler:
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm)}
 
 
-def build_scene():
+def build_scene(w=None):
+    """(scene file, HostScene after one Scene::update) of a workload (default: the headline one)."""
     from b200rt import standin
     from b200rt.host import HostScene
-    scene_file = (standin.sponza_standin if SCENE == "sponza" else standin.sibenik_standin)(width=WIDTH, height=HEIGHT)
+    w = w or WORKLOADS["sponza1080"]
+    if w["scene"] == "sponza":
+        scene_file = standin.sponza_standin(width=w["width"], height=w["height"])
+    elif w["scene"] == "sibenik":
+        scene_file = standin.sibenik_standin(width=w["width"], height=w["height"])
+    else:
+        scene_file = standin.dielectrics_hall(os.path.join(REPO, "oracle", "_ref", "Data"), width=w["width"], height=w["height"])
     scene = HostScene(scene_file)
     scene.update(0.0, 0)
     return scene_file, scene
@@ -121,86 +142,89 @@ def algorithmic_bytes(stats, pixels):
             + 64 * stats["instances_entered"] + 12 * stats["texels_fetched"] + 4 * pixels)
 
 
+def total_rays(stats):
+    return stats["primary_rays"] + stats["shadow_rays"] + stats["reflection_rays"] + stats["refraction_rays"]
+
+
 # ------------------------------------------------------------------------- reference / CPU arm ---
-def reference_frames(scene_file, frames, threads=None):
-    """Runs the reference's AVX renderer (oracle/_ref) for `frames` frames; returns ms per frame list or None."""
-    binary = os.path.join(REPO, "oracle", "_ref", "bin", "ref_" + REF_VARIANT)
+def reference_frames(w, scene_file, frames, threads=None):
+    """Runs the reference's AVX renderer (oracle/_ref) for `frames` frames; returns its JSON record or None."""
+    binary = os.path.join(REPO, "oracle", "_ref", "bin", "ref_" + w["ref_variant"])
     if not os.path.exists(binary):
         return None
     env = dict(os.environ)
     if threads:
         env["REF_THREADS"] = str(threads)
-    out = subprocess.run([binary, scene_file, "--frames", str(frames), "--width", str(WIDTH), "--height", str(HEIGHT)],
+    out = subprocess.run([binary, scene_file, "--frames", str(frames), "--width", str(w["width"]), "--height", str(w["height"])],
                          capture_output=True, text=True, env=env, check=True).stdout
-    info = json.loads([l for l in out.splitlines() if l.startswith("{")][-1])
-    return info
+    return json.loads([l for l in out.splitlines() if l.startswith("{")][-1])
 
 
-def cpu_baseline(scene_file, pack, rays, frames):
+def cpu_baseline(w, scene_file, pack, rays, frames):
     """The reference's CPU path on this box's host cores, bounded sample (`frames` full frames after 1 warm-up)."""
     cores = os.cpu_count() or 1
+    note = "ray tracing only: the reference runs its FXAA pass in GL (unavailable on this box), so no CPU figure includes it"
     info = None
     try:
-        info = reference_frames(scene_file, frames + 1)
+        info = reference_frames(w, scene_file, frames + 1)
     except (subprocess.CalledProcessError, OSError, ValueError, IndexError):
         info = None
     if info is not None:
         ms = statistics.median(info["ms_total"][1:])
         return {"value": rays / ms / 1e3, "unit": "Mrays/s", "cores": info["threads"], "kind": "reference",
-                "sample": "%d full 1920x1080 frames of the same scene after 1 warm-up, median; reference AVX path (SIMD_LANE_SIZE 8) built by oracle/ref_recipe, %d threads" % (frames, info["threads"]),
-                "ms_per_frame": ms, "frames_per_s": 1e3 / ms,
-                "rays_reference_convention": sum(info["rays"].values())}
+                "sample": "%d full %dx%d frames of the same scene after 1 warm-up, median; reference AVX path (SIMD_LANE_SIZE 8) built by oracle/ref_recipe, %d threads"
+                          % (frames, w["width"], w["height"], info["threads"]),
+                "ms_per_frame": ms, "frames_per_s": 1e3 / ms, "rays_reference_convention": sum(info["rays"].values()), "note": note}
     # the reference binary did not travel: time the C port instead (only place bench.py may run oracle/)
     sys.path.insert(0, os.path.join(REPO, "oracle"))
     import oracle_ffi
     times = []
     for _ in range(max(2, frames // 2)):
         t = time.perf_counter()
-        oracle_ffi.render(pack, BOUNCES, FILTER, want_ids=False, threads=cores)
+        oracle_ffi.render(pack, w["bounces"], w["filter"], want_ids=False, threads=cores)
         times.append((time.perf_counter() - t) * 1e3)
     ms = statistics.median(times[1:]) if len(times) > 1 else times[0]
     return {"value": rays / ms / 1e3, "unit": "Mrays/s", "cores": cores, "kind": "port",
-            "sample": "%d full frames, C oracle port (scalar per ray), %d threads" % (len(times), cores), "ms_per_frame": ms, "frames_per_s": 1e3 / ms}
+            "sample": "%d full frames, C oracle port (scalar per ray), %d threads" % (len(times), cores), "ms_per_frame": ms, "frames_per_s": 1e3 / ms, "note": note}
 
 
-def run_reference_arm(args):
+def run_reference_arm(args, w):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    scene_file, scene = build_scene()
+    scene_file, scene = build_scene(w)
     pack = scene.pack()
     # active rays of the frame, from the C oracle's counters (deterministic, = the GPU path's counters)
     sys.path.insert(0, os.path.join(REPO, "oracle"))
     import oracle_ffi
-    stats = oracle_ffi.render(pack, BOUNCES, FILTER, want_ids=False)["stats"]
-    rays = stats["primary_rays"] + stats["shadow_rays"] + stats["reflection_rays"] + stats["refraction_rays"]
+    rays = total_rays(oracle_ffi.render(pack, w["bounces"], w["filter"], want_ids=False)["stats"])
 
     frames = args.warmup + args.steps
     info = None
     try:
-        info = reference_frames(scene_file, frames)
+        info = reference_frames(w, scene_file, frames)
     except (subprocess.CalledProcessError, OSError, ValueError, IndexError):
         info = None
     if info is not None:
         ms = info["ms_total"][args.warmup:]
         kind, cores = "reference", info["threads"]
-        sample = "each step = one full 1920x1080 frame, reference AVX path (SIMD_LANE_SIZE 8), %d threads" % cores
+        sample = "each step = one full %dx%d frame, reference AVX path (SIMD_LANE_SIZE 8), %d threads; ray tracing only (its FXAA pass runs in GL)" % (w["width"], w["height"], cores)
     else:
         cores = os.cpu_count() or 1
         ms = []
         for i in range(frames):
             t = time.perf_counter()
-            oracle_ffi.render(pack, BOUNCES, FILTER, want_ids=False, threads=cores)
+            oracle_ffi.render(pack, w["bounces"], w["filter"], want_ids=False, threads=cores)
             if i >= args.warmup:
                 ms.append((time.perf_counter() - t) * 1e3)
         kind = "port"
-        sample = "each step = one full 1920x1080 frame, C oracle port, %d threads" % cores
+        sample = "each step = one full %dx%d frame, C oracle port, %d threads" % (w["width"], w["height"], cores)
     total_ms = sum(ms)
     value = rays * len(ms) / total_ms / 1e3
     line = {
-        "impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": len(ms), "warmup": args.warmup,
+        "impl": "reference", "metric": w["metric"], "value": value, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": len(ms), "warmup": args.warmup,
         "ms_per_step": total_ms / len(ms), "frames_per_s": 1e3 * len(ms) / total_ms, "higher_is_better": True, "scaling": "strong",
-        "vs_baseline": None, "dtype": "f32", "data": DATA_NOTE, "config": workload_config(args.gpus),
+        "vs_baseline": None, "dtype": "f32", "data": w["data"], "config": workload_config(w, args.gpus),
         "rays_per_frame": rays,
         "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -211,7 +235,58 @@ def run_reference_arm(args):
 
 
 # ------------------------------------------------------------------------------------ GPU arm ---
-def run_gpu_arm(args):
+def ncu_figures(workload):
+    """What ncu measured for the render kernel of this workload (profiles/ncu_render_kernel.json: one entry per workload,
+    each naming the capture it comes from). Instruction and byte counts of a launch do not depend on the box."""
+    try:
+        with open(os.path.join(REPO, "profiles", "ncu_render_kernel.json")) as f:
+            data = json.load(f)
+    except (OSError, ValueError):
+        return {}
+    entry = data.get("workloads", {}).get(workload)
+    if entry is None and data.get("workload") == workload:
+        entry = data
+    return entry or {}
+
+
+def roofline_record(workload, kernel_ms, alg_bytes, rays, clocks, own_walk=None):
+    """The judged fraction is ISSUE: lane-instructions issued against what the SMs can issue (<= 1 by construction)."""
+    if not kernel_ms:
+        return None
+    ncu = ncu_figures(workload)
+    peak_hbm, peak_source = load_peaks()
+    seconds = kernel_ms * 1e-3
+    sm_hz = (clocks.get("sm_mhz") or 1965.0) * 1e6
+    issue_peak = 148 * 4 * 32 * sm_hz
+    thread_instructions = ncu.get("thread_instructions_per_launch")
+    record = {
+        "bound": "issue", "kernel": ncu.get("kernel", "render_kernel"), "kernel_ms": kernel_ms,
+        "achieved": None if not thread_instructions else thread_instructions / seconds / 1e12, "peak": issue_peak / 1e12, "unit": "T lane-instructions/s",
+        "frac": None if not thread_instructions else thread_instructions / seconds / issue_peak,
+        "peak_source": "148 SMs x 4 schedulers x 32 lanes x SM clock sampled during the timed region (%.0f MHz)" % (sm_hz / 1e6),
+        "thread_instructions_per_launch": thread_instructions, "threads_per_instruction": ncu.get("threads_per_instruction"), "issue_active_pct": ncu.get("issue_active_pct"),
+        "stalls_per_issue": ncu.get("stalls_per_issue"),
+        "traffic": ncu.get("dram_bytes_per_launch"),
+        # the byte streams of the same launch, all per second of the live-timed kernel
+        "algorithmic_bytes_per_launch": alg_bytes, "algorithmic_bytes_per_ray": alg_bytes / rays,
+        "algorithmic_gbs": alg_bytes / seconds / 1e9,
+        "dram_gbs": None if not ncu.get("dram_bytes_per_launch") else ncu["dram_bytes_per_launch"] / seconds / 1e9,
+        "l2_gbs": None if not ncu.get("l2_bytes_per_launch") else ncu["l2_bytes_per_launch"] / seconds / 1e9,
+        "l1_gbs": None if not ncu.get("l1_bytes_per_launch") else ncu["l1_bytes_per_launch"] / seconds / 1e9,
+        "hbm_peak_gbs": peak_hbm, "hbm_peak_source": peak_source,
+        "hbm_frac_of_algorithmic_stream": alg_bytes / seconds / 1e9 / peak_hbm,
+        "hbm_frac_of_dram_traffic": None if not ncu.get("dram_bytes_per_launch") else ncu["dram_bytes_per_launch"] / seconds / 1e9 / peak_hbm,
+        "l1_hit_pct": ncu.get("l1_hit_pct"), "l2_hit_pct": ncu.get("l2_hit_pct"),
+        "ncu_source": ncu.get("source"),
+        "shipped_walk": own_walk,
+        "note": "SURVEY 8(d)'s algorithmic stream (BVH nodes + triangles, ~2 KB per ray, counted on the reference's visiting order) is served by L1 and L2 (the working set fits the 126 MB L2): "
+                "against the HBM peak it reads hbm_frac_of_algorithmic_stream > 1, which means cache-resident, not beyond a roofline; the DRAM the launch really moves is `traffic` "
+                "(hbm_frac_of_dram_traffic). The limit that binds is instruction issue: `frac`.",
+    }
+    return record
+
+
+def run_gpu_arm(args, w):
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -226,44 +301,45 @@ def run_gpu_arm(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    if world > 1 and rank != 0:
-        dist.barrier()                                     # rank 0 generates the stand-in assets and the BVH caches first
-    scene_file, scene = build_scene()
-    if world > 1 and rank == 0:
-        dist.barrier()
-    pack = scene.pack()
-    pixels = WIDTH * HEIGHT
-
-    # one instrumented frame (outside every timed region): ray counts + traversal counters of the WHOLE frame
-    counting = Renderer(WIDTH, HEIGHT, BOUNCES, FILTER, device=local_rank, count_traversal=True)
-    counting.upload_static(pack)
-    full_stats = counting.render(pack, want_presented=False)["stats"]
-    counting.close()
-    rays = full_stats["primary_rays"] + full_stats["shadow_rays"] + full_stats["reflection_rays"] + full_stats["refraction_rays"]
-
-    renderer = Renderer(WIDTH, HEIGHT, BOUNCES, FILTER, device=local_rank, tile_stride=world, tile_phase=rank)
-    renderer.upload_static(pack)
-    stream = torch.cuda.current_stream()
+    clocks = ClockSampler(local_rank)
+    from b200rt import _ffi
+    settings = {"arithmetic": args.arithmetic, "deep_queue": args.deep_queue or os.environ.get("B200RT_DEEP_QUEUE", _ffi.DEFAULT_DEEP_QUEUE)}
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device="cuda")
-    clocks = ClockSampler(local_rank)
+    def prepare(wl):
+        """Scene (rank 0 generates the stand-in assets and BVH caches first), pack, the instrumented frame's counters."""
+        if world > 1 and rank != 0:
+            dist.barrier()
+        scene_file, scene = build_scene(wl)
+        if world > 1 and rank == 0:
+            dist.barrier()
+        pack = scene.pack()
+        counting = Renderer(wl["width"], wl["height"], wl["bounces"], wl["filter"], device=local_rank, count_traversal=1)
+        counting.upload_static(pack)
+        full_stats = counting.render(pack, want_presented=False)["stats"]
+        counting.close()
+        return scene_file, scene, pack, full_stats
 
-    if world == 1:
+    def measure_one_gpu(wl, scene, pack, steps, warmup):
+        width, height = wl["width"], wl["height"]
+        pixels = width * height
+        renderer = Renderer(width, height, wl["bounces"], wl["filter"], device=local_rank, arithmetic=args.arithmetic, deep_queue=args.deep_queue)
+        renderer.upload_static(pack)
         # ---- resident: kernels only, CUDA events on the launching stream (inside the library) ----------
         first = renderer.render(pack)                      # uploads the frame once; also the e2e warm-up
-        for _ in range(args.warmup):
+        for _ in range(max(warmup, 3)):
+            renderer.render(pack)                          # the tile order settles on the measured costs
             renderer.time_resident(1, L2_FLUSH_BYTES)
         barrier()
         with clocks:
-            ms_render, ms_fxaa = renderer.time_resident(args.steps, L2_FLUSH_BYTES)
+            ms_render, ms_fxaa = renderer.time_resident(steps, L2_FLUSH_BYTES)
         barrier()
-        ms_step = ms_render + ms_fxaa
-        warm_render, warm_fxaa = renderer.time_resident(args.steps, 0)
+        tail_ms = renderer.render(pack)["stats"]["device_ms_tail"]
+        warm_render, warm_fxaa = renderer.time_resident(steps, 0)
 
         # ---- e2e: the frame loop a user writes — Scene::update on the host, then the frame through the public
         # per-frame call with HOST buffers in and out. Pipelined form (b200rt_submit_frame / b200rt_wait_frame):
@@ -272,105 +348,140 @@ def run_gpu_arm(args):
         # both of its images; the clock runs from the first submit to the arrival of the last image. --------
         outs = [renderer.alloc_outputs(), renderer.alloc_outputs()]   # page-locked host images, two frames in flight
 
-        def frame_loop(n):
+        def frame_loop(n, move=None):
             for i in range(n):
+                if move is not None:
+                    move(i)
                 scene.update(0.0, 0)                       # host per-frame prep incl. TLAS rebuild (Scene.cpp:139-171)
                 renderer.submit(pack.with_frame(scene.frame_view()), outs[i & 1])
                 if i >= 1:
                     renderer.wait()                        # frame i-1 has arrived in outs[(i-1) & 1]
             renderer.wait()
 
-        frame_loop(args.warmup)
+        frame_loop(max(warmup, 3))
         barrier()
         t0 = time.perf_counter()
-        frame_loop(args.steps)
+        frame_loop(steps)
         barrier()
-        e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+        e2e_ms = (time.perf_counter() - t0) * 1e3 / steps
 
         # the same loop, one frame at a time (b200rt_render_frame: nothing overlaps), for reference
         t0 = time.perf_counter()
-        for _ in range(args.steps):
+        for _ in range(steps):
             scene.update(0.0, 0)
             renderer.render(pack.with_frame(scene.frame_view()), out=outs[0])
         barrier()
-        e2e_sync_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+        e2e_sync_ms = (time.perf_counter() - t0) * 1e3 / steps
         if not (np.array_equal(outs[0]["frame_buffer"], first["frame_buffer"]) and np.array_equal(outs[1]["presented"], first["presented"])):
             raise SystemExit("pipelined frames differ from the synchronous frame")
-        h2d = pack.frame_bytes()
-        d2h = pixels * 4 + pixels * 3
-        launches = 4 * args.steps      # per frame: reset_counters_kernel, render_kernel, fxaa_kernel, tile_schedule_kernel
-        kernel_ms = ms_render
-        e2e_api = "Scene::update + b200rt_submit_frame/b200rt_wait_frame (two frames in flight)"
-        band_d2h_ms = None
-    else:
-        # ---- N GPUs: each rank traces its interleaved tiles, one collective moves the frame to rank 0,
-        # rank 0 runs FXAA. Timed on the device with events on the stream everything is issued on. ------
-        stream = torch.cuda.Stream()                       # ONE stream for kernels, barriers / collectives and copies of this rank
-        torch.cuda.set_stream(stream)
-        renderer.set_stream(stream.cuda_stream)
-        fb = torch.zeros(HEIGHT, WIDTH, dtype=torch.int32, device="cuda")
-        presented = torch.empty(HEIGHT, WIDTH, 3, dtype=torch.uint8, device="cuda")
-        host_fb = torch.empty(HEIGHT, WIDTH, dtype=torch.int32).pin_memory()
-        host_rgb = torch.empty(HEIGHT, WIDTH, 3, dtype=torch.uint8).pin_memory()
 
-        from b200rt.multigpu import HALO, BandFrames, FrameGather, PrivateHostImage, SharedHostImage, band_partition, shared_memory_free_bytes
-        gather = FrameGather()
-        bands = None
-        partition = band_partition(HEIGHT, world, width=WIDTH)
+        # a moving camera: every frame differs from the one the tile order was measured on (the timed frames above are
+        # identical, so the schedule always had a perfect cost history). A slow pan + dolly along the hall, e2e loop.
+        moving = None
+        if wl["scene"] != "sibenik":
+            import math
+            base = pack.a["f_camera"][:3].astype(float)
+
+            def move(i):
+                angle = -0.5 * math.pi + 0.004 * i
+                scene.set_camera(position=(base[0] - 0.05 * i, base[1], base[2] + 0.02 * i), rotation=(0.0, math.sin(angle / 2), 0.0, math.cos(angle / 2)))
+            frame_loop(3, move)
+            barrier()
+            t0 = time.perf_counter()
+            frame_loop(steps, lambda i: move(i + 3))
+            barrier()
+            moving = {"ms_per_step": (time.perf_counter() - t0) * 1e3 / steps, "frames": steps,
+                      "what": "e2e frame loop with the camera panning and dollying every frame (tile order from the PREVIOUS, different frame)"}
+            scene.set_camera(position=tuple(base), rotation=(0.0, -0.707107, 0.0, 0.707107))
+            scene.update(0.0, 0)
+        renderer.close()
+        return {"ms_render": ms_render, "ms_fxaa": ms_fxaa, "ms_step": ms_render + ms_fxaa, "warm": (warm_render, warm_fxaa), "tail_ms": tail_ms,
+                "e2e_ms": e2e_ms, "e2e_sync_ms": e2e_sync_ms, "h2d": pack.frame_bytes(), "d2h": pixels * 7, "launches": 3 * steps, "moving_camera": moving,
+                "e2e_api": "Scene::update + b200rt_submit_frame/b200rt_wait_frame (two frames in flight)"}
+
+    def measure_n_gpus(wl, scene, pack, steps, warmup):
+        """N GPUs: each rank traces its interleaved tiles, the render kernel stores every pixel into the image of the rank
+        that owns the pixel's band (peer memory of the C ABI), a device barrier, every rank filters its band. All of it on
+        the renderer's own stream; timed with CUDA events on that stream, max over ranks."""
+        from b200rt.multigpu import HALO, FrameGather, PeerImages, PrivateHostImage, SharedHostImage, band_partition, band_rows_needed, shared_memory_free_bytes
+        width, height = wl["width"], wl["height"]
+        pixels = width * height
+        renderer = Renderer(width, height, wl["bounces"], wl["filter"], device=local_rank, tile_stride=world, tile_phase=rank, arithmetic=args.arithmetic, deep_queue=args.deep_queue)
+        renderer.upload_static(pack)
+        stream = torch.cuda.ExternalStream(renderer.stream)   # the context's own stream, seen from torch (events, the flush)
+        flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device="cuda")
+
+        def exchange(mine):
+            everyone = [None] * world
+            dist.all_gather_object(everyone, mine)             # set-up plumbing only: 64-byte handles, once
+            return everyone
+
+        partition = band_partition(height, world, width=width)
+        peers = None
         if os.environ.get("B200RT_GATHER", "bands") == "bands" and partition is not None:
             try:
-                # two sets alternate, so no rank has to be told that the previous frame has been consumed:
-                # frame n+2 is written into the images of frame n only after every rank has passed the
-                # barriers of frame n+1, which it reaches after its own FXAA of frame n (stream order)
-                frames = [BandFrames(HEIGHT, WIDTH, world, rank) for _ in range(2)]
-                shown = [BandFrames(HEIGHT, WIDTH, world, rank, dtype=torch.uint8, channels=3) for _ in range(2)]   # rank 0's copy is the presented image
-                bands = partition
-            except Exception as e:                         # no symmetric memory on this box: NCCL reduction instead
+                # two sets of images alternate, so no rank has to be told that the previous frame has been consumed:
+                # frame n+2 is written into the images of frame n only after every rank has passed the barriers of
+                # frame n+1, which it reaches after its own FXAA of frame n (stream order)
+                peers = PeerImages(renderer, world, rank, exchange, [pixels * 4, pixels * 4, pixels * 3, pixels * 3])
+            except Exception as e:                         # no peer access on this box: NCCL reduction instead
                 if rank == 0:
                     print("peer memory unavailable (%s): gathering with an NCCL reduce" % (str(e).splitlines() or ["?"])[0], file=sys.stderr)
-        if bands is not None:
-            band_rows, ranges = bands
+        ok_flag = torch.tensor([1 if peers is not None else 0], device="cuda")
+        dist.all_reduce(ok_flag, op=dist.ReduceOp.MIN)
+        if not ok_flag.item() and peers is not None:
+            peers.close(); peers = None
+        gather = FrameGather()
+        fb = torch.zeros(height, width, dtype=torch.int32, device="cuda")
+        presented = torch.empty(height, width, 3, dtype=torch.uint8, device="cuda")
+        if peers is not None:
+            band_rows, ranges = partition
             y0, y1 = ranges[rank]
+            frames = [peers.tensor(k, (height, width), 4) for k in range(2)]
+            shown = [peers.tensor(2 + k, (height, width, 3), 1) for k in range(2)]
+        else:
+            torch.cuda.set_stream(stream)
 
         phase_events = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
         phase_ms = [0.0, 0.0, 0.0]
+        kernel_ms = [0.0]
         frame_number = [0]
 
         def step(phases=False):
             """One frame, everything resident: trace this rank's tiles, exchange, FXAA; the presented image ends on rank 0."""
-            if bands is not None:
+            if peers is not None:
                 b = frame_number[0] & 1
                 frame_number[0] += 1
-                renderer.set_band_targets(frames[b].ptrs, band_rows, HALO)
+                renderer.set_band_targets(peers.ptrs[b], band_rows, HALO)
                 if phases: phase_events[0].record(stream)
-                renderer.render_device(pack, frames[b].ptrs[rank], wait=False)   # every pixel is stored into the image of its band's owner over NVLink
+                renderer.render_device(pack, peers.ptrs[b][rank], wait=False)   # every pixel is stored into the image of its band's owner over NVLink
                 if phases: phase_events[1].record(stream)
-                frames[b].barrier()                        # all pixels of the frame have landed
+                peers.barrier()                            # all pixels of the frame have landed
                 if phases: phase_events[2].record(stream)
-                renderer.present_rows_device(frames[b].ptrs[rank], shown[b].ptrs[0], y0, y1, wait=False)   # this rank's band, filtered into rank 0's presented image
-                shown[b].barrier()                         # rank 0 holds the whole presented image
+                renderer.present_rows_device(peers.ptrs[b][rank], peers.ptrs[2 + b][0], y0, y1, wait=False)   # this rank's band, filtered into rank 0's presented image
+                peers.barrier()                            # rank 0 holds the whole presented image
                 if phases: phase_events[3].record(stream)
             else:
-                fb.zero_()                                 # every rank: only its own tiles may be non-zero going into the SUM
-                renderer.render_device(pack, fb.data_ptr(), wait=False)
-                gather(fb)                                 # tiles are disjoint and the rest is zero: SUM == gather (b200rt/multigpu.py)
-                if rank == 0:
-                    renderer.present_device(fb.data_ptr(), presented.data_ptr(), wait=False)
+                with torch.cuda.stream(stream):
+                    fb.zero_()                             # every rank: only its own tiles may be non-zero going into the SUM
+                    renderer.render_device(pack, fb.data_ptr(), wait=False)
+                    gather(fb)                             # tiles are disjoint and the rest is zero: SUM == gather (b200rt/multigpu.py)
+                    if rank == 0:
+                        renderer.present_device(fb.data_ptr(), presented.data_ptr(), wait=False)
 
         # the exchanged frame must be the single-GPU frame, bit for bit (checked once, untimed): every rank
         # checks the band (+ halo) it received, rank 0 the presented image
         step()
         torch.cuda.synchronize()
-        whole = Renderer(WIDTH, HEIGHT, BOUNCES, FILTER, device=local_rank)
+        whole = Renderer(width, height, wl["bounces"], wl["filter"], device=local_rank, arithmetic=args.arithmetic)
         whole.upload_static(pack)
         expect = whole.render(pack)
         whole.close()
-        if bands is not None:
-            from b200rt.multigpu import band_rows_needed
-            held = band_rows_needed(HEIGHT, y0, y1)
-            ok = np.array_equal(frames[0].local.cpu().numpy().view(np.uint32)[held], expect["frame_buffer"][held])
+        if peers is not None:
+            held = band_rows_needed(height, y0, y1)
+            ok = np.array_equal(frames[0].cpu().numpy().view(np.uint32)[held], expect["frame_buffer"][held])
             if rank == 0:
-                ok = ok and np.array_equal(shown[0].local.cpu().numpy(), expect["presented"])
+                ok = ok and np.array_equal(shown[0].cpu().numpy(), expect["presented"])
         else:
             ok = rank != 0 or (np.array_equal(fb.cpu().numpy().view(np.uint32), expect["frame_buffer"]) and np.array_equal(presented.cpu().numpy(), expect["presented"]))
         if not ok:
@@ -379,44 +490,46 @@ def run_gpu_arm(args):
         dist.all_reduce(verdict, op=dist.ReduceOp.MIN)
         gather_verified = bool(verdict.item())
 
-        for _ in range(args.warmup):
+        for _ in range(max(warmup, 3)):
             step()
         barrier()
         with clocks:
             start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             total = 0.0
-            for _ in range(args.steps):
-                flush.fill_(1)                              # evict L2, outside the timed region
+            for _ in range(steps):
+                with torch.cuda.stream(stream):
+                    flush.fill_(1)                          # evict L2, outside the timed region
                 barrier()
-                if bands is not None:
+                if peers is not None:
                     # the ranks' streams line up on a device-side barrier (untimed): the clock of every rank starts at the same
                     # moment, with the step already queued behind it, instead of whenever its host got out of the host barrier
-                    frames[frame_number[0] & 1].barrier()
+                    peers.barrier()
                 start.record(stream)
-                step(phases=bands is not None)
+                step(phases=peers is not None)
                 end.record(stream)
                 torch.cuda.synchronize()
                 total += start.elapsed_time(end)
-                if bands is not None:
+                kernel_ms[0] += renderer.last_frame_stats()["device_ms_render"] / steps   # the render kernel's own %globaltimer span
+                if peers is not None:
                     for k in range(3):
-                        phase_ms[k] += phase_events[k].elapsed_time(phase_events[k + 1]) / args.steps
+                        phase_ms[k] += phase_events[k].elapsed_time(phase_events[k + 1]) / steps
         barrier()
-        t = torch.tensor([total / args.steps], device="cuda")
+        t = torch.tensor([total / steps, kernel_ms[0]], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_step = float(t.item())
-        ms_render, ms_fxaa, warm_render, warm_fxaa = ms_step, 0.0, None, None
-        kernel_ms = None
+        ms_step, slowest_kernel_ms = float(t[0].item()), float(t[1].item())
 
         # ---- end to end: the frame loop with host buffers, pipelined like the single-GPU loop. Every rank
         # filters its band and sends it (both images) to the host over its OWN PCIe link, into one frame in
         # shared page-locked memory; frame n leaves on a second stream while frame n+1 is traced. ----------
-        if bands is not None:
-            tag = "b200rt_%s_" % os.environ.get("MASTER_PORT", "0")
+        band_d2h_ms = None
+        if peers is not None:
+            tag = "b200rt_%s_%s_" % (os.environ.get("MASTER_PORT", "0"), wl["scene"])
             # one frame for the whole job in POSIX shared memory — if /dev/shm has room for two of them (a container's
             # default is 64 MiB); else every rank keeps the band it delivered in page-locked memory of its own
             room = torch.tensor([shared_memory_free_bytes()], dtype=torch.int64, device="cuda")
             dist.all_reduce(room, op=dist.ReduceOp.MIN)
             one_frame = int(room.item()) > 2 * pixels * 7 + (64 << 20) and os.environ.get("B200RT_SHARED_FRAME", "1") != "0"
+
             def shared(name, shape, dtype, rows=None):
                 if not one_frame:
                     return PrivateHostImage(shape, dtype)
@@ -438,13 +551,13 @@ def run_gpu_arm(args):
                 dist.barrier()
                 image.register()
                 return image
-            host_fb = [shared("fb%d" % b, (HEIGHT, WIDTH), np.int32, (y0, y1)) for b in range(2)]
-            host_rgb = [shared("rgb%d" % b, (HEIGHT, WIDTH, 3), np.uint8, (y0, y1)) for b in range(2)]
+            host_fb = [shared("fb%d" % b, (height, width), np.int32, (y0, y1)) for b in range(2)]
+            host_rgb = [shared("rgb%d" % b, (height, width, 3), np.uint8, (y0, y1)) for b in range(2)]
             arrived = shared("arrived", (2, world), np.int64)      # arrived[b][r] = number of the last frame whose band rank r has delivered into images b
             arrived.array[:] = 0
             dist.barrier()
             page_locked = all(h.registered and h.tensor.is_pinned() for h in host_fb + host_rgb + [arrived])
-            presented_local = [torch.empty(HEIGHT, WIDTH, 3, dtype=torch.uint8, device="cuda") for _ in range(2)]
+            presented_local = [torch.empty(height, width, 3, dtype=torch.uint8, device="cuda") for _ in range(2)]
             sequence = [torch.zeros(1, dtype=torch.int64, device="cuda") for _ in range(2)]
             copy_stream = torch.cuda.Stream()
             fxaa_done = [torch.cuda.Event(), torch.cuda.Event()]
@@ -457,16 +570,16 @@ def run_gpu_arm(args):
                     b = i & 1
                     scene.update(0.0, 0)
                     frame_pack = pack.with_frame(scene.frame_view())
-                    renderer.set_band_targets(frames[b].ptrs, band_rows, HALO)
-                    renderer.render_device(frame_pack, frames[b].ptrs[rank], wait=False)
+                    renderer.set_band_targets(peers.ptrs[b], band_rows, HALO)
+                    renderer.render_device(frame_pack, peers.ptrs[b][rank], wait=False)
                     if i > first:
                         stream.wait_event(copied[b ^ 1])     # my band of frame i-1 has left images b^1: beyond this barrier the others may trace frame i+1 into them
-                    frames[b].barrier()
-                    renderer.present_rows_device(frames[b].ptrs[rank], presented_local[b].data_ptr(), y0, y1, wait=False)
+                    peers.barrier()
+                    renderer.present_rows_device(peers.ptrs[b][rank], presented_local[b].data_ptr(), y0, y1, wait=False)
                     fxaa_done[b].record(stream)
                     copy_stream.wait_event(fxaa_done[b])
                     with torch.cuda.stream(copy_stream):
-                        host_fb[b].tensor[y0:y1].copy_(frames[b].local[y0:y1], non_blocking=True)
+                        host_fb[b].tensor[y0:y1].copy_(frames[b][y0:y1], non_blocking=True)
                         host_rgb[b].tensor[y0:y1].copy_(presented_local[b][y0:y1], non_blocking=True)
                         sequence[b].fill_(i + 1)
                         arrived.tensor[b, rank:rank + 1].copy_(sequence[b], non_blocking=True)
@@ -484,15 +597,15 @@ def run_gpu_arm(args):
                 delivered[0] = first + n
                 torch.cuda.synchronize()
 
-            e2e_loop(max(2, args.warmup))
+            e2e_loop(max(2, warmup))
             barrier()
             t0 = time.perf_counter()
-            e2e_loop(args.steps)
+            e2e_loop(steps)
             barrier()
-            elapsed = (time.perf_counter() - t0) * 1e3 / args.steps
+            elapsed = (time.perf_counter() - t0) * 1e3 / steps
             ok = True       # both host frames of the pipeline must be the single-GPU frame: every rank checks the band it delivered, rank 0 the whole frame
             for b in range(2):
-                rows = slice(0, HEIGHT) if (rank == 0 and one_frame) else slice(y0, y1)
+                rows = slice(0, height) if (rank == 0 and one_frame) else slice(y0, y1)
                 ok = ok and np.array_equal(host_fb[b].array.view(np.uint32)[rows], expect["frame_buffer"][rows]) and np.array_equal(host_rgb[b].array[rows], expect["presented"][rows])
             verdict = torch.tensor([1 if ok else 0], device="cuda")
             dist.all_reduce(verdict, op=dist.ReduceOp.MIN)
@@ -503,7 +616,7 @@ def run_gpu_arm(args):
             with torch.cuda.stream(copy_stream):
                 copy_events[0].record(copy_stream)
                 for _ in range(10):
-                    host_fb[0].tensor[y0:y1].copy_(frames[0].local[y0:y1], non_blocking=True)
+                    host_fb[0].tensor[y0:y1].copy_(frames[0][y0:y1], non_blocking=True)
                     host_rgb[0].tensor[y0:y1].copy_(presented_local[0][y0:y1], non_blocking=True)
                 copy_events[1].record(copy_stream)
             torch.cuda.synchronize()
@@ -513,84 +626,98 @@ def run_gpu_arm(args):
             barrier()
             for h in host_fb + host_rgb + [arrived]:
                 h.close()
-            e2e_api = ("Scene::update + b200rt_render_frame_device per rank (pixels stored into the band owners' images over NVLink) + b200rt_present_rows_device per rank + "
-                       "D2H of every rank's band over its own PCIe link into %s %s host memory; frame n+1 traced while frame n leaves"
+            e2e_api = ("Scene::update + b200rt_render_frame_device per rank (pixels stored into the band owners' images over NVLink: b200rt_peer_alloc / b200rt_peer_open) + b200rt_barrier + "
+                       "b200rt_present_rows_device per rank + D2H of every rank's band over its own PCIe link into %s %s host memory; frame n+1 traced while frame n leaves"
                        % ("one frame in shared" if one_frame else "its own (no shared frame: /dev/shm too small, or B200RT_SHARED_FRAME=0)", "page-locked" if page_locked else "PAGEABLE (cudaHostRegister failed)"))
         else:
+            host_fb = torch.empty(height, width, dtype=torch.int32).pin_memory()
+            host_rgb = torch.empty(height, width, 3, dtype=torch.uint8).pin_memory()
+
             def step_e2e():
                 scene.update(0.0, 0)
-                fb.zero_()
-                renderer.render_device(pack.with_frame(scene.frame_view()), fb.data_ptr(), wait=False)
-                gather(fb)
-                if rank == 0:
-                    renderer.present_device(fb.data_ptr(), presented.data_ptr(), wait=False)
-                    host_fb.copy_(fb, non_blocking=True)
-                    host_rgb.copy_(presented, non_blocking=True)
-                    torch.cuda.synchronize()
+                with torch.cuda.stream(stream):
+                    fb.zero_()
+                    renderer.render_device(pack.with_frame(scene.frame_view()), fb.data_ptr(), wait=False)
+                    gather(fb)
+                    if rank == 0:
+                        renderer.present_device(fb.data_ptr(), presented.data_ptr(), wait=False)
+                        host_fb.copy_(fb, non_blocking=True)
+                        host_rgb.copy_(presented, non_blocking=True)
+                        torch.cuda.synchronize()
             barrier()
             t0 = time.perf_counter()
-            for _ in range(args.steps):
+            for _ in range(steps):
                 step_e2e()
             barrier()
-            elapsed = (time.perf_counter() - t0) * 1e3 / args.steps
+            elapsed = (time.perf_counter() - t0) * 1e3 / steps
             e2e_api = "Scene::update + b200rt_render_frame_device per rank + NCCL reduce + b200rt_present_device + D2H on rank 0"
         t = torch.tensor([elapsed], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item())
-        h2d = pack.frame_bytes() * world                  # every rank uploads the frame block
-        d2h = pixels * 4 + pixels * 3 + (8 * world if bands is not None else 0)   # whole job: the bands add up to both images (+ the arrival stamps)
-        launches = 4 * args.steps                          # per rank and frame: reset_counters, render, tile_schedule, fxaa (the NCCL path runs fxaa on rank 0 only)
-        e2e_sync_ms = None
-        if bands is None:
-            band_d2h_ms = None
+        if peers is not None:
+            barrier()
+            peers.close()
+        renderer.close()
+        return {"ms_render": slowest_kernel_ms, "ms_fxaa": None, "ms_step": ms_step, "warm": None, "tail_ms": None,
+                "e2e_ms": e2e_ms, "e2e_sync_ms": None, "h2d": pack.frame_bytes() * world,      # every rank uploads the frame block
+                "d2h": pixels * 7 + (8 * world if peers is not None else 0),                   # whole job: the bands add up to both images (+ the arrival stamps)
+                "launches": (5 if peers is not None else 3) * steps,                           # per rank and frame: render, barrier, fxaa, barrier, tile_schedule (the NCCL path: render, tile_schedule, fxaa on rank 0)
+                "moving_camera": None, "e2e_api": e2e_api, "band_d2h_ms": band_d2h_ms, "gather_verified": gather_verified,
+                "phases": None if peers is None else {"upload_and_render": phase_ms[0], "barrier_all_pixels_landed": phase_ms[1], "fxaa_band_into_rank0_and_barrier": phase_ms[2]},
+                "gather": ("%d bands of %d rows (+%d halo): render kernel stores each pixel into its band owner's image over NVLink peer memory (cudaIpc through the C ABI), device barrier (b200rt_barrier), every rank filters its band"
+                           % (world, partition[0], HALO)) if peers is not None else "NCCL reduce(SUM) of disjoint tiles"}
 
-    if rank == 0:
-        peak, peak_source = load_peaks()
-        alg_bytes = algorithmic_bytes(full_stats, pixels)
-        roofline = None
-        if kernel_ms:
-            achieved = alg_bytes / (kernel_ms * 1e-3) / 1e9
-            ncu = {}
-            try:
-                with open(os.path.join(REPO, "profiles", "ncu_render_kernel.json")) as f:
-                    ncu = json.load(f)
-            except (OSError, ValueError):
-                pass
-            if ncu.get("workload", "sponza1080") != args.workload:
-                ncu = {}   # the capture describes another frame: no traffic / instruction figures for this one
-            sm_hz = (clocks.summary()["sm_mhz"] or 1965.0) * 1e6
-            issue = None
-            if ncu.get("thread_instructions_per_launch"):
-                # second yardstick: lane-instructions the launch executes vs what 148 SMs x 4 schedulers x 32 lanes can issue
-                issue_peak = 148 * 4 * 32 * sm_hz
-                issue = {"thread_instructions_per_launch": ncu["thread_instructions_per_launch"], "achieved_per_s": ncu["thread_instructions_per_launch"] / (kernel_ms * 1e-3),
-                         "peak_per_s": issue_peak, "frac": ncu["thread_instructions_per_launch"] / (kernel_ms * 1e-3) / issue_peak,
-                         "threads_per_instruction": ncu.get("threads_per_instruction"), "issue_active_pct": ncu.get("issue_active_pct")}
-            roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": ncu.get("dram_bytes_per_launch"),
-                        "kernel": "render_kernel<false>", "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": alg_bytes,
-                        "algorithmic_bytes_per_ray": alg_bytes / rays, "peak_source": peak_source, "traffic_source": ncu.get("source"),
-                        "issue_roofline": issue,
-                        "note": "the algorithmic stream (BVH nodes + triangles, 2 KB per ray) is served by L1/L2 (working set 39 MB < 126 MB L2): DRAM traffic per launch is `traffic`, ~1 % of the algorithmic bytes, so frac > 1 against the HBM peak means 'cache-resident', not 'beyond the roofline'; the binding limit is instruction issue (issue_roofline)"}
-        baseline = cpu_baseline(scene_file, pack, rays, frames=6) if world == 1 else None
+    def record(wl, name, scene_file, scene, pack, full_stats, m, with_cpu):
+        pixels = wl["width"] * wl["height"]
+        rays = total_rays(full_stats)
+        clk = clocks.summary()
+        own_walk = None
+        if with_cpu:      # the shipped kernel's own traversal work, next to the reference-order counts the roofline uses
+            counting = Renderer(wl["width"], wl["height"], wl["bounces"], wl["filter"], device=local_rank, count_traversal=2)
+            counting.upload_static(pack)
+            s = counting.render(pack, want_presented=False)["stats"]
+            counting.close()
+            own_walk = {"nodes_visited": s["nodes_visited"], "triangles_tested": s["triangles_tested"],
+                        "reference_order": {"nodes_visited": full_stats["nodes_visited"], "triangles_tested": full_stats["triangles_tested"]},
+                        "what": "shadow rays on the threaded copy, right child first (the walk that is timed) vs the reference's front-to-back order (the walk the algorithmic bytes are counted on); closest-hit rays are the same in both"}
+        roofline = roofline_record(name, m["ms_render"], algorithmic_bytes(full_stats, pixels), rays, clk, own_walk)
+        if roofline is not None and world > 1:
+            roofline["kernel_ms_source"] = "the slowest rank's render kernel, timed by the kernel itself (%globaltimer, first block started .. last warp done); instruction and byte counts are the whole frame's (single-GPU capture), so achieved figures are per-job"
         line = {
-            "metric": METRIC, "value": rays / ms_step / 1e3, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_step, "frames_per_s": 1e3 / ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "f32", "data": DATA_NOTE,
-            "config": workload_config(world),
+            "metric": wl["metric"], "value": rays / m["ms_step"] / 1e3, "unit": "Mrays/s", "n_gpus": world,
+            "ms_per_step": m["ms_step"], "frames_per_s": 1e3 / m["ms_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": wl["data"], "config": workload_config(wl, world, settings),
+            "value_conditions": "resident inputs, one frame at a time, L2 flushed before every frame, CUDA events on the launching stream" + (", clocks of all ranks started behind a device barrier, max over ranks" if world > 1 else ""),
             "rays_per_frame": rays, "rays": {k: full_stats[k] for k in ("primary_rays", "shadow_rays", "reflection_rays", "refraction_rays")},
-            "ms_render_kernel": ms_render, "ms_fxaa_kernel": ms_fxaa,
-            "warm_l2": None if warm_render is None else {"ms_render_kernel": warm_render, "ms_fxaa_kernel": warm_fxaa, "value": rays / (warm_render + warm_fxaa) / 1e3},
-            "e2e": {"value": rays / e2e_ms / 1e3, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "frames_per_s": 1e3 / e2e_ms,
-                    "api": e2e_api, "unpipelined_ms_per_step": e2e_sync_ms, "band_d2h_ms_alone": band_d2h_ms},
-            "gpu_launches": launches,
-            "gather_verified": gather_verified if world > 1 else None,
-            "rank0_phases_ms": None if world == 1 or bands is None else {"upload_and_render": phase_ms[0], "barrier_all_pixels_landed": phase_ms[1], "fxaa_band_into_rank0_and_barrier": phase_ms[2]},
-            "gather": None if world == 1 else ("%d bands of %d rows (+%d halo): render kernel stores each pixel into its band owner's image over NVLink peer memory, device barrier, every rank filters its band"
-                                              % (world, bands[0], HALO) if bands is not None else "NCCL reduce(SUM) of disjoint tiles"),
-            "clocks": clocks.summary(),
-            "roofline": roofline,
-            "cpu_baseline": baseline,
+            "ms_render_kernel": m["ms_render"], "ms_fxaa_kernel": m["ms_fxaa"], "ms_render_tail": m["tail_ms"],
+            "warm_l2": None if m["warm"] is None else {"ms_render_kernel": m["warm"][0], "ms_fxaa_kernel": m["warm"][1], "value": rays / (m["warm"][0] + m["warm"][1]) / 1e3},
+            "e2e": {"value": rays / m["e2e_ms"] / 1e3, "unit": "Mrays/s", "h2d_bytes_per_step": m["h2d"], "d2h_bytes_per_step": m["d2h"], "ms_per_step": m["e2e_ms"], "frames_per_s": 1e3 / m["e2e_ms"],
+                    "api": m["e2e_api"], "conditions": "host buffers in and out, two frames in flight (frame n's copies overlap frame n+1's tracing), L2 as the loop leaves it, wall clock / frames",
+                    "unpipelined_ms_per_step": m["e2e_sync_ms"], "band_d2h_ms_alone": m.get("band_d2h_ms"), "moving_camera": m["moving_camera"]},
+            "gpu_launches": m["launches"],
+            "gather_verified": m.get("gather_verified"), "rank0_phases_ms": m.get("phases"), "gather": m.get("gather"),
+            "clocks": clk, "roofline": roofline,
+            "cpu_baseline": cpu_baseline(wl, scene_file, pack, rays, frames=6 if wl["bounces"] <= 3 else 3) if with_cpu else None,
         }
+        return line
+
+    name = args.workload
+    scene_file, scene, pack, full_stats = prepare(w)
+    m = (measure_one_gpu if world == 1 else measure_n_gpus)(w, scene, pack, args.steps, args.warmup)
+    line = None
+    if rank == 0:
+        line = record(w, name, scene_file, scene, pack, full_stats, m, with_cpu=world == 1)
+        line["steps"], line["warmup"] = args.steps, args.warmup
+    if world > 1 and name != "sibenik4k" and not args.no_scale_4k:
+        # north_star: "near-linear scaling to 8 GPUs at 4K" — the same measurement on configs[4], so that the driver's
+        # 1 -> 8 runs see it too; `value` above stays the headline configuration's
+        w4 = WORKLOADS["sibenik4k"]
+        scene_file4, scene4, pack4, full_stats4 = prepare(w4)
+        m4 = measure_n_gpus(w4, scene4, pack4, max(5, args.steps // 2), args.warmup)
+        if rank == 0:
+            sub = record(w4, "sibenik4k", scene_file4, scene4, pack4, full_stats4, m4, with_cpu=False)
+            line["scale_4k"] = {k: sub[k] for k in ("metric", "value", "unit", "ms_per_step", "frames_per_s", "rays_per_frame", "ms_render_kernel", "e2e", "gather_verified", "rank0_phases_ms", "roofline", "config")}
+    if rank == 0:
         print(json.dumps(line), file=RESULT, flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -616,15 +743,17 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="sponza1080", choices=["sponza1080"] + sorted(OTHER_WORKLOADS))
+    ap.add_argument("--workload", default="sponza1080", choices=sorted(WORKLOADS))
+    ap.add_argument("--arithmetic", default="exact", choices=["exact", "fast"], help="b200rt_config.arithmetic; the headline is EXACT (bit-identical to the reference)")
+    ap.add_argument("--deep-queue", dest="deep_queue", default=None, choices=["off", "glass", "all"], help="b200rt_config.deep_queue (default: the library's shipped setting)")
+    ap.add_argument("--no-scale-4k", dest="no_scale_4k", action="store_true", help="N > 1: skip the configs[4] sub-record")
     args = ap.parse_args()
-    if args.workload != "sponza1080":
-        globals().update(OTHER_WORKLOADS[args.workload])
     if args.warmup < 3:
         args.warmup = 3
+    w = WORKLOADS[args.workload]
     if args.impl == "reference":
-        return run_reference_arm(args)
-    return run_gpu_arm(args)
+        return run_reference_arm(args, w)
+    return run_gpu_arm(args, w)
 
 
 if __name__ == "__main__":

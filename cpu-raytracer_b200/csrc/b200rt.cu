@@ -68,7 +68,7 @@ struct b200rt_ctx {
 	unsigned frame_number = 0;
 	// deep-pixel queue (render.cuh): pools, allocated on first use
 	DeviceBuffer q_nodes, q_bounce, q_shadow, q_bounce_ready, q_shadow_ready;
-	int queue_inline_below = 0;
+	int queue_inline_below = 0, queue_defer_shadows = 1;
 	int blas_stack_entries = 1;
 	DeviceBuffer tile_cost, tile_order; // schedule of the render kernel (kernels.cuh: tile_schedule_kernel)
 	int tile_count_mine = 0;
@@ -87,6 +87,9 @@ struct b200rt_ctx {
 	unsigned submitted = 0, waited = 0;
 
 	uint64_t band_targets[B200RT_MAX_BANDS] = {};   // b200rt_set_band_targets
+	unsigned * barrier_blocks[B200RT_MAX_BANDS] = {}; // b200rt_barrier_setup
+	int barrier_count = 0, barrier_rank = 0;
+	unsigned barrier_epoch = 0;
 	int band_count = 0, band_rows = 0, band_halo = 0;
 
 	SceneParams params;      // last frame's parameters (for b200rt_time_resident)
@@ -149,7 +152,8 @@ extern "C" int b200rt_create(const b200rt_config * config, b200rt_ctx ** out) {
 #else
 	ctx->kernels = &kernels_exact();
 #endif
-	if (const char * text = getenv("B200RT_QUEUE_INLINE_BELOW")) ctx->queue_inline_below = atoi(text);   // tuning knob (tools/): see SceneParams::queue_inline_below
+	if (const char * text = getenv("B200RT_QUEUE_INLINE_BELOW")) ctx->queue_inline_below = atoi(text);   // tuning knobs (tools/): see SceneParams
+	if (const char * text = getenv("B200RT_QUEUE_DEFER_SHADOWS")) ctx->queue_defer_shadows = atoi(text) != 0;
 
 	auto bail = [&](const char * what, cudaError_t err) { g_create_error = std::string(what) + ": " + cudaGetErrorString(err); b200rt_destroy(ctx); return -1; };
 
@@ -563,7 +567,7 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 	}
 	const b200rt_config & c = ctx->config;
 	P.width = c.width; P.height = c.height; P.bounces = c.bounces; P.mipmap_filter = c.mipmap_filter; P.max_anisotropy = c.max_anisotropy;
-	P.traversal_naive = c.traversal_naive; P.texture_sample_mode = c.texture_sample_mode;
+	P.traversal_naive = c.traversal_naive; P.texture_sample_mode = c.texture_sample_mode; P.count_shipped_walk = c.count_traversal == 2;
 	P.tiles_x = (c.width + 31) / 32; P.tiles_y = (c.height + 31) / 32; // Window.cpp:11-12
 	P.tile_stride = c.tile_stride; P.tile_phase = c.tile_phase;
 	const int tiles = P.tiles_x * P.tiles_y;
@@ -581,7 +585,7 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 // A pool that runs out costs nothing but speed: the producer walks that subtree depth-first (FrameCounters::q_fallbacks).
 static int ensure_queue(b200rt_ctx * ctx, SceneParams & P) {
 	const size_t pixels = size_t(std::max(ctx->tile_count_mine, 1)) * 1024;
-	size_t nodes = std::min<size_t>(4 * pixels, (size_t(1) << 26) - 1), bounce = 4 * pixels, shadow = 8 * pixels;
+	size_t nodes = std::min<size_t>(4 * pixels, (size_t(1) << 26) - 1), bounce = 8 * pixels, shadow = 8 * pixels;
 	if (const char * text = getenv("B200RT_QUEUE_CAPACITY")) nodes = bounce = shadow = size_t(std::max(atoi(text), 32));   // tests: small pools force the fall-back paths
 	if (!ctx->q_nodes.ptr) {
 		CHECK_CUDA(ctx, ctx->q_nodes.ensure(nodes * 6 * sizeof(float4)));
@@ -609,7 +613,7 @@ static int launch_render(b200rt_ctx * ctx, unsigned * frame_buffer, float * colo
 	if (!banded) P.band_count = 0;
 	P.blas_stack_entries = ctx->blas_stack_entries;
 	P.queue_mode = (count || P.light_count > 24 || P.bounces == 0) ? 0 : ctx->config.deep_queue;   // RT_QUEUE_MAX_LIGHTS: a node record keeps one bit per light
-	P.queue_inline_below = ctx->queue_inline_below;
+	P.queue_inline_below = ctx->queue_inline_below; P.queue_defer_shadows = ctx->queue_defer_shadows;
 	if (P.queue_mode != 0) {
 		if (ensure_queue(ctx, P)) return -1;
 		if (++ctx->launch_serial == 0) ctx->launch_serial = 1;
@@ -743,6 +747,20 @@ extern "C" int b200rt_render_frame_device(b200rt_ctx * ctx, const b200rt_frame *
 	return 0;
 }
 
+extern "C" int b200rt_last_frame_stats(b200rt_ctx * ctx, b200rt_stats * stats) {
+	if (!ctx) return -1;
+	if (!stats) return fail(ctx, "null stats");
+	if (!ctx->have_frame || ctx->frame_number == 0) return fail(ctx, "no frame has been rendered yet");
+	CHECK_CUDA(ctx, cudaSetDevice(ctx->config.device));
+	CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	CHECK_CUDA(ctx, cudaMemcpy(ctx->pinned_counters, counter_block(ctx, ctx->frame_number - 1), sizeof(FrameCounters), cudaMemcpyDeviceToHost));
+	const FrameCounters & c = *ctx->pinned_counters;
+	counters_to_stats(c, stats);
+	if (c.first_start_ns != 0 && c.last_done_ns > ~c.first_start_ns) stats->device_ms_render = float(double(c.last_done_ns - ~c.first_start_ns) * 1e-6);
+	stats->device_ms_total = stats->device_ms_render;
+	return 0;
+}
+
 extern "C" int b200rt_present_device(b200rt_ctx * ctx, uint64_t frame_buffer_dev, uint64_t presented_dev, float * device_ms) {
 	if (!ctx) return -1;
 	if (!frame_buffer_dev || !presented_dev) return fail(ctx, "null device pointer");
@@ -782,6 +800,71 @@ extern "C" int b200rt_set_band_targets(b200rt_ctx * ctx, const uint64_t * target
 	for (int b = 0; b < band_count; b++) if (!targets[b]) return fail(ctx, "null band target");
 	for (int b = 0; b < B200RT_MAX_BANDS; b++) ctx->band_targets[b] = b < band_count ? targets[b] : 0;
 	ctx->band_count = band_count; ctx->band_rows = band_rows; ctx->band_halo = halo_rows;
+	return 0;
+}
+
+// ------------------------------------------------------ peer memory + device barrier ---
+extern "C" int b200rt_peer_alloc(b200rt_ctx * ctx, uint64_t bytes, uint64_t * device_ptr, b200rt_peer_handle * handle) {
+	if (!ctx) return -1;
+	if (!device_ptr || !handle || bytes == 0) return fail(ctx, "bad argument");
+	static_assert(sizeof(cudaIpcMemHandle_t) == sizeof(b200rt_peer_handle), "b200rt_peer_handle is a cudaIpcMemHandle_t");
+	CHECK_CUDA(ctx, cudaSetDevice(ctx->config.device));
+	void * p = nullptr;
+	CHECK_CUDA(ctx, cudaMalloc(&p, size_t(bytes)));
+	cudaError_t e = cudaMemset(p, 0, size_t(bytes));
+	cudaIpcMemHandle_t h;
+	if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, p);
+	if (e != cudaSuccess) { cudaFree(p); ctx->error = std::string("peer allocation: ") + cudaGetErrorString(e); return -1; }
+	memcpy(handle->bytes, &h, sizeof(h));
+	*device_ptr = uint64_t(reinterpret_cast<uintptr_t>(p));
+	return 0;
+}
+extern "C" int b200rt_peer_free(b200rt_ctx * ctx, uint64_t device_ptr) {
+	if (!ctx) return -1;
+	CHECK_CUDA(ctx, cudaSetDevice(ctx->config.device));
+	CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	CHECK_CUDA(ctx, cudaFree(reinterpret_cast<void *>(uintptr_t(device_ptr))));
+	return 0;
+}
+extern "C" int b200rt_peer_open(b200rt_ctx * ctx, const b200rt_peer_handle * handle, uint64_t * device_ptr) {
+	if (!ctx) return -1;
+	if (!handle || !device_ptr) return fail(ctx, "bad argument");
+	CHECK_CUDA(ctx, cudaSetDevice(ctx->config.device));
+	cudaIpcMemHandle_t h;
+	memcpy(&h, handle->bytes, sizeof(h));
+	void * p = nullptr;
+	CHECK_CUDA(ctx, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+	*device_ptr = uint64_t(reinterpret_cast<uintptr_t>(p));
+	return 0;
+}
+extern "C" int b200rt_peer_close(b200rt_ctx * ctx, uint64_t device_ptr) {
+	if (!ctx) return -1;
+	CHECK_CUDA(ctx, cudaSetDevice(ctx->config.device));
+	CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	CHECK_CUDA(ctx, cudaIpcCloseMemHandle(reinterpret_cast<void *>(uintptr_t(device_ptr))));
+	return 0;
+}
+extern "C" int b200rt_peer_read(b200rt_ctx * ctx, uint64_t device_ptr, void * host, uint64_t bytes) {
+	if (!ctx) return -1;
+	if (!device_ptr || !host) return fail(ctx, "null pointer");
+	CHECK_CUDA(ctx, cudaSetDevice(ctx->config.device));
+	CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	CHECK_CUDA(ctx, cudaMemcpy(host, reinterpret_cast<const void *>(uintptr_t(device_ptr)), size_t(bytes), cudaMemcpyDeviceToHost));
+	return 0;
+}
+extern "C" int b200rt_barrier_setup(b200rt_ctx * ctx, const uint64_t * flag_blocks, int32_t count, int32_t rank) {
+	if (!ctx) return -1;
+	if (!flag_blocks || count < 1 || count > B200RT_MAX_BANDS || rank < 0 || rank >= count) return fail(ctx, "barrier needs 1..8 flag blocks and a rank among them");
+	for (int q = 0; q < count; q++) if (!flag_blocks[q]) return fail(ctx, "null flag block");
+	for (int q = 0; q < B200RT_MAX_BANDS; q++) ctx->barrier_blocks[q] = q < count ? reinterpret_cast<unsigned *>(uintptr_t(flag_blocks[q])) : nullptr;
+	ctx->barrier_count = count; ctx->barrier_rank = rank; ctx->barrier_epoch = 0;
+	return 0;
+}
+extern "C" int b200rt_barrier(b200rt_ctx * ctx) {
+	if (!ctx) return -1;
+	if (ctx->barrier_count == 0) return fail(ctx, "b200rt_barrier_setup has not been called");
+	CHECK_CUDA(ctx, cudaSetDevice(ctx->config.device));
+	CHECK_CUDA(ctx, ctx->kernels->barrier(ctx->barrier_blocks, ctx->barrier_count, ctx->barrier_rank, ++ctx->barrier_epoch, ctx->stream));
 	return 0;
 }
 

@@ -21,6 +21,7 @@ struct KernelTable {
 	cudaError_t (*texture_level0)(const unsigned char * rgb8, const float * gamma_lut, float4 * out, long long texel_count, cudaStream_t stream);
 	cudaError_t (*texture_mip)(const float4 * previous, float4 * out, int width, int height, int previous_width, cudaStream_t stream);
 	cudaError_t (*texel_halves)(const float4 * texels, uint2 * out, long long texel_count, cudaStream_t stream);
+	cudaError_t (*barrier)(unsigned * const * flag_blocks, int count, int rank, unsigned epoch, cudaStream_t stream);
 };
 
 const KernelTable & kernels_exact();   // -fmad=false: the reference's association order, bit for bit

@@ -96,96 +96,142 @@ render_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, float *
 	flush_ray_counters(counters, cnt, primary, COUNT);
 }
 
-// The same frame with the deep-pixel queue (render.cuh). A warp takes, in this order of preference, 32 bounce items,
-// 32 shadow items, a tile unit, whatever items are left. Items first: the rays of the deep pixels are the frame's
-// critical path, and popping them as soon as a full warp's worth exists keeps the queues (and their L2 footprint) short.
+// Warp-collective counter update: one atomicAdd per warp.
+__device__ __forceinline__ void warp_add(int * counter, int n) {
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+	if ((threadIdx.x & 31) == 0 && n != 0) atomicAdd(counter, n);
+}
+
+// The same frame with the deep-pixel queue (render.cuh). Every ray — a pixel's primary ray or an item popped from the
+// bounce queue — is the same depth-first walk (shade_subtree_body<QUEUE>), whose top node may be exported to the
+// queues; shadow items are any-hit queries. A warp works on ONE kind at a time, in this order of preference: bounce
+// items (the deep pixels' rays are the frame's critical path), shadow items, tile units.
 //
-// A warp that finds nothing LEAVES — after looking three more times, 2 / 4 / 8 us apart — instead of waiting for the
-// frame to end: whoever publishes an item looks at the queues again right afterwards, so every item is taken by
-// somebody still running, and the number of warps at work follows the supply of items by itself. (The first version
-// kept all 4 736 resident warps polling the cursors until the frame's count of outstanding work was zero: the polls
-// saturated the one L2 slice that holds them and the frame took 150 ms instead of 1 — profiles/r02_variants_call1.jsonl.)
-// The count of outstanding work (tile units + items not finished) is still kept: a warp that sees it at zero knows
-// that nothing can appear any more and leaves at once.
+// Items are claimed by TICKET: one atomicAdd on the queue's head hands a warp the next n slots — it never fails and is
+// never retried. (The first version claimed with compare-and-swap on the head: with thousands of warps contending, one
+// wins per L2 round trip and the frame's million items went through at ~20 per microsecond — 150 ms instead of 1;
+// profiles/r02_variants_call1.jsonl, r02_variants_call2.jsonl.) A ticket may name a slot that is not published yet, or
+// never will be: a lane keeps its ticket across iterations until the slot's ready word shows this frame's serial
+// number, and meanwhile the warp takes whatever else there is; tickets die when the frame's count of outstanding work
+// (tile units + items not finished) reaches zero. Tickets are only drawn against items seen in the queue, so few are
+// ever early. A warp with no ticket that finds nothing looks three more times (2 / 4 / 8 us apart) and leaves: whoever
+// publishes an item looks at the queues again right afterwards, so nothing is orphaned, and no warp polls for long.
 template<int MAXB, int BSTACK>
 __global__ void __launch_bounds__(RT_BLOCK_THREADS, RT_MIN_BLOCKS)
 render_queue_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, float * __restrict__ colour_float, FrameCounters * counters) {
 	const int lane = threadIdx.x & 31;
+	const unsigned lanes_below = (1u << lane) - 1u;
 	const unsigned total_units = unsigned(P.tile_count_mine) * 32u;
 	const PixelOut out = { frame_buffer, colour_float };
 	enum { WORK_NONE = 0, WORK_UNIT = 1, WORK_BOUNCE = 2, WORK_SHADOW = 3, WORK_WAIT = 4 };
+	const unsigned NO_TICKET = 0xffffffffu;
 
 	Counters cnt = { 0, 0, 0, 0, 0, 0, 0, 0 };
 	unsigned primary = 0;
 	int idle_looks = 0;
 	bool units_left = total_units > 0;   // this warp's view; once false it stays false (the cursor only grows)
+	unsigned ticket = NO_TICKET;         // this lane's claimed slot that is not published yet
+	int ticket_kind = WORK_NONE;         // warp-uniform: which queue the warp's tickets belong to
 
 	if (threadIdx.x == 0) atomicMax(&counters->first_start_ns, ~global_timer_ns());
 
 	for (;;) {
 		// ---- lane 0 chooses the warp's next piece of work ------------------------------------------------
+		const unsigned holding = __ballot_sync(0xffffffffu, ticket != NO_TICKET);
 		int kind = WORK_NONE; unsigned first = 0, n = 0;
 		if (lane == 0) {
-			for (int attempt = 0; attempt < 4 && kind == WORK_NONE; attempt++) {
-				const unsigned hb = peek(&counters->q_bounce_head), rb = min(peek(&counters->q_bounce_reserved), P.q_bounce_capacity), ab = rb > hb ? rb - hb : 0u;
-				const unsigned hs = peek(&counters->q_shadow_head), rs = min(peek(&counters->q_shadow_reserved), P.q_shadow_capacity), as = rs > hs ? rs - hs : 0u;
-				if (ab >= 32u || (ab > 0u && !units_left && as < 32u)) {
-					n = min(ab, 32u);
-					if (atomicCAS(&counters->q_bounce_head, hb, hb + n) == hb) { kind = WORK_BOUNCE; first = hb; }
-				} else if (as >= 32u || (as > 0u && !units_left)) {
-					n = min(as, 32u);
-					if (atomicCAS(&counters->q_shadow_head, hs, hs + n) == hs) { kind = WORK_SHADOW; first = hs; }
-				} else if (units_left) {
-					first = atomicAdd(&counters->next_unit, 1u);
-					if (first < total_units) kind = WORK_UNIT; else units_left = false;
-				} else break;
+			const unsigned free_lanes = 32u - unsigned(__popc(holding));
+			const unsigned hb = peek(&counters->q_bounce_head), rb = min(peek(&counters->q_bounce_reserved), P.q_bounce_capacity), ab = rb > hb ? rb - hb : 0u;
+			const unsigned hs = peek(&counters->q_shadow_head), rs = min(peek(&counters->q_shadow_reserved), P.q_shadow_capacity), as = rs > hs ? rs - hs : 0u;
+			if (holding) kind = ticket_kind;
+			else if (ab >= 32u || (ab > 0u && !units_left && as < 32u)) kind = WORK_BOUNCE;
+			else if (as >= 32u || (as > 0u && !units_left)) kind = WORK_SHADOW;
+			if (kind == WORK_BOUNCE && ab > 0u && free_lanes > 0u) { n = min(ab, free_lanes); first = atomicAdd(&counters->q_bounce_head, n); }
+			if (kind == WORK_SHADOW && as > 0u && free_lanes > 0u) { n = min(as, free_lanes); first = atomicAdd(&counters->q_shadow_head, n); }
+			if (kind == WORK_NONE && units_left) {
+				first = atomicAdd(&counters->next_unit, 1u);
+				if (first < total_units) kind = WORK_UNIT; else units_left = false;
 			}
-			if (kind == WORK_NONE && idle_looks < 3 && peek(&counters->q_outstanding) > 0) kind = WORK_WAIT;
+			if (kind == WORK_NONE && (units_left || ab > 0u || as > 0u || (idle_looks < 3 && peek(&counters->q_outstanding) > 0))) kind = WORK_WAIT;
 		}
 		kind = __shfl_sync(0xffffffffu, kind, 0); first = __shfl_sync(0xffffffffu, first, 0); n = __shfl_sync(0xffffffffu, n, 0);
 		if (kind == WORK_NONE) break;
 		if (kind == WORK_WAIT) {
 			if (lane == 0 && idle_looks == 0) atomicMax(&counters->first_idle_ns, ~global_timer_ns());
-			__nanosleep(2000u << idle_looks);
+			__nanosleep(2000u << min(idle_looks, 2));
 			idle_looks++;
 			continue;
 		}
 
-		int settled = 0;   // items (or the tile unit) this lane finishes: comes off the frame's outstanding work
-		if (kind == WORK_UNIT) {
-			const long long unit_begin = clock64();
-			int local_tile, px, py;
-			const bool inside = unit_pixel(P, first, lane, local_tile, px, py);
-			Ray ray;
-			if (inside) { ray = primary_ray(P, px, py); primary++; }
-			process_bounce<MAXB, BSTACK>(P, out, counters, inside, ray, P.bounces, -(px + P.width * py + 1), 0, cnt);
-			__syncwarp();
-			if (lane == 0) { atomicAdd(P.tile_cost + local_tile, unsigned((clock64() - unit_begin) >> 6)); settled = 1; }   // the unit itself
-		} else if (kind == WORK_BOUNCE) {
-			bool active = unsigned(lane) < n;
-			Ray ray; int parent = 0, which = 0, bounces_left = 0;
-			if (active) {
-				const unsigned slot = first + unsigned(lane);
-				while (__ldcg(P.q_bounce_ready + slot) != P.frame_serial) __nanosleep(20);   // reserved before it was written: a moment
-				__threadfence();
-				read_bounce_item(P, slot, ray, parent, which, bounces_left);
-				if (parent == QUEUE_NULL_ITEM) active = false; else settled = 1;
+		// ---- items: new tickets go to the lanes that hold none; whose slot is published? --------------------
+		bool active = false;
+		if (kind == WORK_BOUNCE || kind == WORK_SHADOW) {
+			ticket_kind = kind;
+			const unsigned rank = unsigned(__popc(~holding & lanes_below));
+			if (ticket == NO_TICKET && rank < n) ticket = first + rank;
+			const unsigned capacity = kind == WORK_BOUNCE ? P.q_bounce_capacity : P.q_shadow_capacity;
+			const unsigned * ready = kind == WORK_BOUNCE ? P.q_bounce_ready : P.q_shadow_ready;
+			if (ticket != NO_TICKET && ticket >= capacity) ticket = NO_TICKET;   // beyond the pool: that item was never queued
+			if (ticket != NO_TICKET) {
+				for (int look = 0; look < 3 && !active; look++) active = __ldcg(ready + ticket) == P.frame_serial;   // reserved a moment before it is written
+				if (active) __threadfence();
 			}
-			process_bounce<MAXB, BSTACK>(P, out, counters, active, ray, bounces_left, parent, which, cnt);
-		} else { // WORK_SHADOW
-			if (unsigned(lane) < n) {
-				const unsigned slot = first + unsigned(lane);
-				while (__ldcg(P.q_shadow_ready + slot) != P.frame_serial) __nanosleep(20);
-				__threadfence();
-				const float4 a = __ldcg(P.q_shadow + 2 * size_t(slot)), b = __ldcg(P.q_shadow + 2 * size_t(slot) + 1);
+			if (__ballot_sync(0xffffffffu, active) == 0u) { // nothing published yet: the tickets wait, the warp does something else
+				kind = WORK_NONE;
+				if (lane == 0) {
+					if (peek(&counters->q_outstanding) <= 0) kind = WORK_BOUNCE;   // the frame is done: the tickets are void (handled below)
+					else if (units_left) {
+						first = atomicAdd(&counters->next_unit, 1u);
+						if (first < total_units) kind = WORK_UNIT; else units_left = false;
+					}
+				}
+				kind = __shfl_sync(0xffffffffu, kind, 0); first = __shfl_sync(0xffffffffu, first, 0);
+				if (kind == WORK_BOUNCE) { ticket = NO_TICKET; ticket_kind = WORK_NONE; continue; }
+				if (kind == WORK_NONE) { __nanosleep(500); continue; }
+			}
+		}
+		idle_looks = 0;
+
+		int settled = 0;   // items (or the tile unit) this lane finishes: comes off the frame's outstanding work
+		if (kind == WORK_SHADOW) {
+			if (active) {
+				const float4 a = __ldcg(P.q_shadow + 2 * size_t(ticket)), b = __ldcg(P.q_shadow + 2 * size_t(ticket) + 1);
+				ticket = NO_TICKET;
 				const int word = as_i(b.w);
 				if (word != QUEUE_NULL_ITEM) {
-					deliver_shadow(P, out, word >> 5, word & 31, trace_any<false, BSTACK>(P, V(a), V(b), a.w, cnt));
+					deliver_shadow(P, out, word >> 5, word & 31, trace_any_call<BSTACK>(P, V(a), V(b), a.w, cnt));
 					settled = 1;
 				}
 			}
+		} else { // a walk: a pixel's (WORK_UNIT) or a popped bounce item's
+			const long long unit_begin = clock64();
+			Ray ray; int bounces_left = 0, local_tile = 0;
+			QueueContext q = { counters, 0, 0 };
+			if (kind == WORK_UNIT) {
+				int px, py;
+				active = unit_pixel(P, first, lane, local_tile, px, py);
+				if (active) { ray = primary_ray(P, px, py); primary++; bounces_left = P.bounces; q.parent = -(px + P.width * py + 1); }
+			} else if (active) {
+				read_bounce_item(P, ticket, ray, q.parent, q.which, bounces_left);
+				ticket = NO_TICKET;
+				if (q.parent == QUEUE_NULL_ITEM) active = false; else settled = 1;
+			}
+			if (active) {
+				float distance;
+				bool exported = false;
+				const v3 colour = shade_subtree_body<false, MAXB, BSTACK, true>(P, ray, bounces_left, cnt, distance, &q, exported);
+				if (!exported) {
+					if (q.parent < 0) { const int p = -(q.parent + 1); write_pixel(P, out, p % P.width, p / P.width, colour); }
+					else deliver(P, out, q.parent, q.which, colour, distance);
+				}
+			}
+			if (kind == WORK_UNIT) {
+				__syncwarp();
+				if (lane == 0) { atomicAdd(P.tile_cost + local_tile, unsigned((clock64() - unit_begin) >> 6)); settled = 1; }   // the unit itself
+			}
 		}
-		warp_add(&counters->q_outstanding, -settled);   // what this warp queued was added before it became visible (process_bounce)
+		warp_add(&counters->q_outstanding, -settled);   // what a walk queued was added before it became visible (export_node)
 	}
 
 	if (lane == 0) {
@@ -258,6 +304,23 @@ primary_hits_kernel(const SceneParams P, int * __restrict__ ids, float * __restr
 			material = float(hit.material_id); u = hit.u; v = hit.v;
 		}
 		hits[4 * p] = best.t; hits[4 * p + 1] = material; hits[4 * p + 2] = u; hits[4 * p + 3] = v;
+	}
+}
+
+// ------------------------------------------------------------------------ device barrier ---
+// b200rt_barrier (include/b200rt.h): thread q tells rank q "rank `rank` has reached barrier `epoch`" with a store into
+// q's flag block (peer memory over NVLink) and waits until this rank's own block says the same of rank q. The fences
+// order the earlier stores of this GPU (the render kernel's pixels in the peers' images) before the flag, and the
+// peers' flags before whatever this stream runs next.
+struct BarrierPeers { unsigned * block[B200RT_MAX_BANDS]; };
+__global__ void __launch_bounds__(32)
+barrier_kernel(BarrierPeers peers, int count, int rank, unsigned epoch) {
+	const int q = threadIdx.x;
+	if (q < count) {
+		__threadfence_system();
+		*reinterpret_cast<volatile unsigned *>(peers.block[q] + rank) = epoch;
+		while (*reinterpret_cast<volatile unsigned *>(peers.block[rank] + q) < epoch) __nanosleep(100);
+		__threadfence_system();
 	}
 }
 

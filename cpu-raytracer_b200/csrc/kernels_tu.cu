@@ -74,9 +74,16 @@ static cudaError_t tu_texel_halves(const float4 * texels, uint2 * out, long long
 	return cudaGetLastError();
 }
 
+static cudaError_t tu_barrier(unsigned * const * flag_blocks, int count, int rank, unsigned epoch, cudaStream_t stream) {
+	BarrierPeers peers;
+	for (int q = 0; q < B200RT_MAX_BANDS; q++) peers.block[q] = q < count ? flag_blocks[q] : nullptr;
+	RT_LAUNCH(barrier_kernel, 1, 32, stream, false, peers, count, rank, epoch);
+	return cudaGetLastError();
+}
+
 #define RT_STRINGIFY2(x) #x
 #define RT_STRINGIFY(x) RT_STRINGIFY2(x)
-static const rt::KernelTable table = { RT_STRINGIFY(RT_NAMESPACE), RT_FEATURE_BITS, tu_init, tu_render_occupancy, tu_render, tu_primary_hits, tu_schedule, tu_fxaa, tu_texture_level0, tu_texture_mip, tu_texel_halves };
+static const rt::KernelTable table = { RT_STRINGIFY(RT_NAMESPACE), RT_FEATURE_BITS, tu_init, tu_render_occupancy, tu_render, tu_primary_hits, tu_schedule, tu_fxaa, tu_texture_level0, tu_texture_mip, tu_texel_halves, tu_barrier };
 
 } // namespace RT_NAMESPACE
 

@@ -1,10 +1,8 @@
-// render.cuh — Raytracer::bounce for one ray per thread, in two forms that produce the same bits:
-//   shade_subtree   the whole ray tree of one call of bounce() walked depth-first by ONE thread with an explicit
-//                   frame stack (what every pixel used in round 1);
-//   process_bounce  ONE call of bounce() as a work item: closest hit, hit record, albedo, then the node's children
-//                   (reflection / refraction rays) and its shadow rays go to device-side queues as items of their
-//                   own, and the node's value is assembled bottom-up when the last of them has reported (the
-//                   deep-pixel queue; kernels.cuh has the loop that feeds persistent warps from the queues).
+// render.cuh — Raytracer::bounce for one ray per thread: shade_subtree walks the whole ray tree of one call of bounce()
+// depth-first with an explicit frame stack. With the deep-pixel queue on, the TOP node of a walk may instead be
+// exported: its children (reflection / refraction rays) and its shadow rays go to device-side queues as items of
+// their own, each walked by whichever thread pops it, and the node's value is assembled bottom-up when the last of
+// them has reported (kernels.cuh has the loop that feeds persistent warps from the queues). Same bits either way.
 //
 // Reference: Raytracer::render_tile (Raytracer.cpp:3-85), Raytracer::bounce (:87-400), Window::plot (Window.h:56-65).
 #pragma once
@@ -186,6 +184,190 @@ __device__ __forceinline__ v3 refraction_blend(const SceneParams & P, int materi
 	return result + blend;                                               // :395
 }
 
+// ------------------------------------------------------------------------------ deep-pixel queue ---
+// North_star's "wavefront traversal with ray compaction", restricted to where it pays. A pixel whose primary ray hits
+// glass is not walked by one thread: the top node of a walk can be EXPORTED — it becomes a node record in HBM, its
+// reflection / refraction rays become items of the bounce queue and its shadow rays items of the shadow queue, which
+// all persistent warps pop (kernels.cuh): a warp holds rays of ONE kind at a time (the compaction), the shadow rays
+// leave the pixel's critical chain (which rays are spawned never depends on a shadow ray's answer), and the sibling
+// subtrees of a fan-out run side by side on whatever warps are free. Every popped ray is again a walk whose top node
+// may be exported, so a deep tree unfolds level by level. A node's value is assembled when the last of its shadow
+// rays and children has reported (a countdown in the record), by the reporting thread, with the reference's sums in
+// the reference's order: the same bits as the recursive form.
+//
+//   node record  6 x float4   {parent, flags | which << 8, pending, material id} {point, distance} {normal, F_r}
+//                             {albedo (or the finished direct lighting: NODE_LIT), occluded-light bits}
+//                             {reflection child's colour, -} {refraction child's colour, its distance}
+//   bounce item  5 x float4   the Ray (18 floats), parent node, which | bounces_left << 1     (parent = QUEUE_NULL_ITEM: skip)
+//   shadow item  2 x float4   {origin, max distance} {direction, node << 5 | light}           (word = QUEUE_NULL_ITEM: skip)
+// An item is visible to consumers once its word in the queue's `ready` array holds the frame's serial number (written
+// after a __threadfence()). Records and items are bump-allocated per frame; when a pool is exhausted the node is not
+// exported and its subtree is walked by the thread that holds it: always correct, never blocked. Records and items
+// are read and written with .cg accesses (L2 only): another SM's L1 may hold a stale copy of the line.
+#define RT_QUEUE_MAX_LIGHTS 24
+#define QUEUE_NULL_ITEM int(0x80000000u)
+enum { NODE_LIT = 64 };   // with the FRAME_* bits in a record's flags: the albedo slot already holds the direct lighting
+
+__device__ __forceinline__ float as_f(int v) { return __int_as_float(v); }
+__device__ __forceinline__ int   as_i(float v) { return __float_as_int(v); }
+__device__ __forceinline__ unsigned peek(const unsigned * p) { return *reinterpret_cast<const volatile unsigned *>(p); }   // a fresh value, not this SM's L1 copy
+__device__ __forceinline__ int      peek(const int * p)      { return *reinterpret_cast<const volatile int *>(p); }
+
+// Value of a node whose shadow rays and children have all reported (the record is complete and no longer written).
+__device__ __forceinline__ v3 node_value(const SceneParams & P, const float4 * rec, float & distance_out, int & parent, int & which) {
+	const float4 r0 = __ldcg(rec), r1 = __ldcg(rec + 1), r2 = __ldcg(rec + 2), r3 = __ldcg(rec + 3);
+	parent = as_i(r0.x);
+	const int flags = as_i(r0.y) & 0xff; which = (as_i(r0.y) >> 8) & 1;
+	const int material_id = as_i(r0.w);
+	const v3 point = V(r1), normal = V(r2), material_diffuse = V(r3);
+	const unsigned occluded = unsigned(as_i(r3.w));
+	distance_out = r1.w;
+
+	v3 result = V(0.0f, 0.0f, 0.0f);
+	if (flags & NODE_LIT) {
+		result = material_diffuse;
+	} else if (dot(material_diffuse, material_diffuse) > 0.0f) {
+		v3 diffuse = V(P.ambient[0], P.ambient[1], P.ambient[2]);
+		const v3 to_camera = normalize(V(P.cam_position[0], P.cam_position[1], P.cam_position[2]) - point);
+		for (int i = 0; i < P.light_count; i++) {
+			if ((occluded >> i) & 1u) continue;
+			LightSample s;
+			light_sample(P, i, point, s);
+			diffuse = light_add(diffuse, s, normal, to_camera);
+		}
+		result = lit_result(diffuse, material_diffuse);
+	}
+	v3 colour_reflection = V(0.0f, 0.0f, 0.0f);
+	if (flags & FRAME_HAS_REFLECTION) {
+		const float4 m1 = __ldg(reinterpret_cast<const float4 *>(P.materials + material_id) + 1);
+		colour_reflection = V(m1) * V(__ldcg(rec + 4));
+		result = result + colour_reflection;
+		if (!(flags & FRAME_HAS_REFRACTION)) return result;
+		if (flags & FRAME_TIR) return result + colour_reflection;
+	} else if (!(flags & FRAME_HAS_REFRACTION) || (flags & FRAME_TIR)) {
+		return result;
+	}
+	const float4 r5 = __ldcg(rec + 5);
+	return refraction_blend(P, material_id, flags, r2.w, result, colour_reflection, V(r5), r5.w);
+}
+
+// A walk's colour (and hit distance) goes to its parent: the pixel, or a node record — and whoever brings a record's
+// countdown to zero computes the node's value and carries it one level up.
+__device__ __noinline__ void deliver(const SceneParams & P, const PixelOut & out, int parent, int which, v3 value, float distance) {
+	for (;;) {
+		if (parent < 0) { // the root's parent is the pixel
+			const int p = -(parent + 1);
+			write_pixel(P, out, p % P.width, p / P.width, value);
+			return;
+		}
+		float4 * rec = P.q_nodes + 6 * size_t(parent);
+		__stcg(rec + 4 + which, make_float4(value.x, value.y, value.z, distance));
+		__threadfence();
+		if (atomicSub(reinterpret_cast<int *>(rec) + 2, 1) != 1) return;
+		__threadfence();
+		value = node_value(P, rec, distance, parent, which);
+	}
+}
+__device__ __forceinline__ void deliver_shadow(const SceneParams & P, const PixelOut & out, int node, int light, bool occluded) {
+	float4 * rec = P.q_nodes + 6 * size_t(node);
+	if (occluded) atomicOr(reinterpret_cast<unsigned *>(rec) + 15, 1u << light);
+	__threadfence();
+	if (atomicSub(reinterpret_cast<int *>(rec) + 2, 1) != 1) return;
+	__threadfence();
+	float distance; int parent, which;
+	const v3 value = node_value(P, rec, distance, parent, which);
+	deliver(P, out, parent, which, value, distance);
+}
+
+__device__ __forceinline__ void write_bounce_item(const SceneParams & P, unsigned slot, const Ray & r, int parent, int which, int bounces_left) {
+	float4 * item = P.q_bounce + 5 * size_t(slot);
+	__stcg(item,     make_float4(r.origin.x, r.origin.y, r.origin.z, r.direction.x));
+	__stcg(item + 1, make_float4(r.direction.y, r.direction.z, r.dO_dx.x, r.dO_dx.y));
+	__stcg(item + 2, make_float4(r.dO_dx.z, r.dO_dy.x, r.dO_dy.y, r.dO_dy.z));
+	__stcg(item + 3, make_float4(r.dD_dx.x, r.dD_dx.y, r.dD_dx.z, r.dD_dy.x));
+	__stcg(item + 4, make_float4(r.dD_dy.y, r.dD_dy.z, as_f(parent), as_f(which | (bounces_left << 1))));
+}
+__device__ __forceinline__ void read_bounce_item(const SceneParams & P, unsigned slot, Ray & r, int & parent, int & which, int & bounces_left) {
+	const float4 * item = P.q_bounce + 5 * size_t(slot);
+	const float4 a = __ldcg(item), b = __ldcg(item + 1), c = __ldcg(item + 2), d = __ldcg(item + 3), e = __ldcg(item + 4);
+	r.origin = V(a.x, a.y, a.z); r.direction = V(a.w, b.x, b.y);
+	r.dO_dx = V(b.z, b.w, c.x); r.dO_dy = V(c.y, c.z, c.w);
+	r.dD_dx = V(d.x, d.y, d.z); r.dD_dy = V(d.w, e.x, e.y);
+	parent = as_i(e.z); which = as_i(e.w) & 1; bounces_left = as_i(e.w) >> 1;
+}
+
+// What a walk needs to export its top node.
+struct QueueContext { FrameCounters * counters; int parent, which; };
+
+// Slots for the lanes that happen to stand here together (one atomicAdd for the group): `per_lane` slots each.
+// The group is whoever is converged at this point — any grouping is correct, a larger one is cheaper.
+__device__ __forceinline__ unsigned group_reserve(unsigned * counter, unsigned per_lane) {
+#ifdef RT_EMULATE
+	return atomicAdd(counter, per_lane);
+#else
+	const unsigned mask = __activemask();
+	const int lane = threadIdx.x & 31, leader = __ffs(mask) - 1;
+	unsigned base = 0;
+	if (lane == leader) base = atomicAdd(counter, per_lane * unsigned(__popc(mask)));
+	base = __shfl_sync(mask, base, leader);
+	return base + per_lane * unsigned(__popc(mask & ((1u << lane) - 1u)));
+#endif
+}
+
+// Exports the top node of a walk: record, children and (deferred) shadow rays. Returns false when a pool is exhausted
+// (nothing has been published then, and the caller goes on walking). result: the node's finished direct lighting when
+// its shadow rays were traced in line (n_shadow == 0 and lit), else the albedo.
+__device__ __forceinline__ bool export_node(const SceneParams & P, const QueueContext & q, const HitRecord & hit, float distance, int flags, float F_r, v3 albedo_or_result, bool result_is_final,
+                                            const Ray & reflected, const Ray & refracted, int bounces_left, int n_shadow, Counters & cnt) {
+	const bool has_child[2] = { (flags & FRAME_HAS_REFLECTION) != 0, (flags & FRAME_HAS_REFRACTION) && !(flags & FRAME_TIR) };
+	const int n_children = (has_child[0] ? 1 : 0) + (has_child[1] ? 1 : 0);
+	// every exporting lane takes one record, two bounce slots and light_count shadow slots: fixed sizes keep the
+	// reservation one atomicAdd per group; a slot that stays unused is published as a null item
+	const unsigned node_slot = group_reserve(&q.counters->q_node_reserved, 1u);
+	if (node_slot >= P.q_node_capacity) { atomicAdd(&q.counters->q_fallbacks, 1u); return false; }
+	const unsigned bounce_slot = group_reserve(&q.counters->q_bounce_reserved, 2u);
+	const unsigned shadow_slot = n_shadow > 0 ? group_reserve(&q.counters->q_shadow_reserved, unsigned(P.light_count)) : 0u;
+	const bool fits = bounce_slot + 2u <= P.q_bounce_capacity && (n_shadow == 0 || shadow_slot + unsigned(P.light_count) <= P.q_shadow_capacity);
+	if (!fits) { // slots inside the pool must still be published (somebody may have claimed them): as null items
+		for (unsigned k = 0; k < 2u; k++) if (bounce_slot + k < P.q_bounce_capacity) __stcg(P.q_bounce + 5 * size_t(bounce_slot + k) + 4, make_float4(0.0f, 0.0f, as_f(QUEUE_NULL_ITEM), 0.0f));
+		for (int i = 0; i < n_shadow; i++) if (shadow_slot + i < P.q_shadow_capacity) __stcg(P.q_shadow + 2 * size_t(shadow_slot + i) + 1, make_float4(0.0f, 0.0f, 0.0f, as_f(QUEUE_NULL_ITEM)));
+		__threadfence();
+		for (unsigned k = 0; k < 2u; k++) if (bounce_slot + k < P.q_bounce_capacity) __stcg(P.q_bounce_ready + bounce_slot + k, P.frame_serial);
+		for (int i = 0; i < n_shadow; i++) if (shadow_slot + i < P.q_shadow_capacity) __stcg(P.q_shadow_ready + shadow_slot + i, P.frame_serial);
+		atomicAdd(&q.counters->q_fallbacks, 1u);
+		return false;
+	}
+	atomicAdd(&q.counters->q_outstanding, n_children + n_shadow);   // before anything is visible: the count never runs low
+
+	const int node = int(node_slot);
+	float4 * rec = P.q_nodes + 6 * size_t(node);
+	__stcg(rec,     make_float4(as_f(q.parent), as_f(flags | (result_is_final ? NODE_LIT : 0) | (q.which << 8)), as_f(n_children + n_shadow), as_f(hit.material_id)));
+	__stcg(rec + 1, make_float4(hit.point.x, hit.point.y, hit.point.z, distance));
+	__stcg(rec + 2, make_float4(hit.normal.x, hit.normal.y, hit.normal.z, F_r));
+	__stcg(rec + 3, make_float4(albedo_or_result.x, albedo_or_result.y, albedo_or_result.z, as_f(0)));
+	// payloads, ONE fence, then the ready words: record and items are in L2 before any consumer can see an item that names the record
+	for (int k = 0; k < 2; k++) {
+		if (has_child[k]) {
+			if (k == 0) cnt.reflection++; else cnt.refraction++;
+			write_bounce_item(P, bounce_slot + k, k == 0 ? reflected : refracted, node, k, bounces_left - 1);
+		} else {
+			__stcg(P.q_bounce + 5 * size_t(bounce_slot + k) + 4, make_float4(0.0f, 0.0f, as_f(QUEUE_NULL_ITEM), 0.0f));
+		}
+	}
+	for (int i = 0; i < n_shadow; i++) { // shadow rays (:155-198)
+		LightSample s;
+		light_sample(P, i, hit.point, s);
+		cnt.shadow++;
+		float4 * item = P.q_shadow + 2 * size_t(shadow_slot + i);
+		__stcg(item,     make_float4(hit.point.x, hit.point.y, hit.point.z, s.distance));
+		__stcg(item + 1, make_float4(s.to_light.x, s.to_light.y, s.to_light.z, as_f((node << 5) | i)));
+	}
+	__threadfence();
+	for (unsigned k = 0; k < 2u; k++) __stcg(P.q_bounce_ready + bounce_slot + k, P.frame_serial);
+	for (int i = 0; i < n_shadow; i++) __stcg(P.q_shadow_ready + shadow_slot + i, P.frame_serial);
+	return true;
+}
+
 // ------------------------------------------------------------------------- depth-first, one thread ---
 // One pending level of Raytracer::bounce's recursion (:204-397), kept in local memory. The
 // recursion is binary (reflection, then refraction) and is unrolled depth-first with the same
@@ -201,21 +383,24 @@ struct BounceFrame {
 };
 
 // bounce(ray, bounces_left), iteratively: returns the colour; distance_out = the hit distance bounce() hands to its
-// caller (Beer's law one level up). MAXB = frames reserved (>= bounces_left). first_hit: the closest hit of `ray`
-// when the caller has traced it already.
-template<bool COUNT, int MAXB, int BSTACK>
-__device__ __forceinline__ v3 shade_subtree_body(const SceneParams & P, Ray ray, int bounces_left, Counters & cnt, float & distance_out, const Candidate * first_hit) {
+// caller (Beer's law one level up). MAXB = frames reserved (>= bounces_left).
+// QUEUE: the top node of the walk is exported to the deep-pixel queue when the frame's policy says so (q.parent < 0:
+// the walk is a pixel's — queue_mode 1: its primary ray hit a transmissive material, 2: it hit anything that spawns rays;
+// q.parent >= 0: the walk is a popped item's — more than queue_inline_below bounces left); `exported` then comes back
+// true and the returned colour means nothing: the pixel is written by whoever completes the root record.
+template<bool COUNT, int MAXB, int BSTACK, bool QUEUE>
+__device__ __forceinline__ v3 shade_subtree_body(const SceneParams & P, Ray ray, int bounces_left, Counters & cnt, float & distance_out, const QueueContext * q, bool & exported) {
 	BounceFrame frames[MAXB];
 	int depth = 0;                // number of pending frames = recursion depth of the current ray
 
 	v3    returned;               // value of the bounce() call that just finished
 	float returned_distance;
+	bool  top = QUEUE;            // the next hit is the walk's top node
 
 	for (;;) {
 		// ---- bounce(ray, bounces_left): Raytracer.cpp:87-201 ---------------------------------
 		Candidate best;
-		if (first_hit) { best = *first_hit; first_hit = nullptr; }
-		else trace_closest<COUNT, BSTACK>(P, ray.origin, ray.direction, best, cnt);
+		trace_closest<COUNT, BSTACK>(P, ray.origin, ray.direction, best, cnt);
 
 		bool descend = false;
 
@@ -228,10 +413,21 @@ __device__ __forceinline__ v3 shade_subtree_body(const SceneParams & P, Ray ray,
 
 			const float4 * mp = reinterpret_cast<const float4 *>(P.materials + hit.material_id);
 			const v3 material_diffuse = get_albedo<COUNT>(P, __ldg(mp), hit, cnt);
+			const bool lit = dot(material_diffuse, material_diffuse) > 0.0f;
+
+			// QUEUE: may this node be exported? Then its shadow rays are not traced here but queued with it.
+			bool may_export = false;
+			if (QUEUE && top && bounces_left > 0) {
+				const float4 m1 = __ldg(mp + 1), m2 = __ldg(mp + 2);
+				const bool reflects = dot(V(m1), V(m1)) > 0.0f, refracts = dot(V(m2), V(m2)) > 0.0f;
+				may_export = q->parent >= 0 ? (bounces_left > P.queue_inline_below && (reflects || refracts))
+				                            : (P.queue_mode == 2 ? (reflects || refracts) : refracts);
+			}
+			const bool defer_shadows = QUEUE && may_export && lit && P.light_count > 0 && P.queue_defer_shadows;
 
 			v3 result = V(0.0f, 0.0f, 0.0f);
 
-			if (dot(material_diffuse, material_diffuse) > 0.0f) { // :143-201
+			if (lit && !defer_shadows) { // :143-201
 				v3 diffuse = V(P.ambient[0], P.ambient[1], P.ambient[2]);
 				const v3 to_camera = normalize(V(P.cam_position[0], P.cam_position[1], P.cam_position[2]) - hit.point);
 
@@ -262,6 +458,7 @@ __device__ __forceinline__ v3 shade_subtree_body(const SceneParams & P, Ray ray,
 					frame.colour_reflection = V(0.0f, 0.0f, 0.0f);
 					frame.distance = best.t;
 					frame.material_id = hit.material_id;
+					frame.F_r = 0.0f;
 					int flags = 0;
 
 					const float d_dot_n = dot(ray.direction, hit.normal);
@@ -270,8 +467,38 @@ __device__ __forceinline__ v3 shade_subtree_body(const SceneParams & P, Ray ray,
 
 					if (refraction_mask) flags |= refraction_setup(ray, hit, m1.w, d_dot_n, dDN_dx, dDN_dy, frame.refracted, frame.F_r);
 
-					if (reflection_mask) { // :249-271
-						const Ray reflected = reflection_ray(ray, hit, d_dot_n, dDN_dx, dDN_dy);
+					Ray reflected;
+					if (reflection_mask) reflected = reflection_ray(ray, hit, d_dot_n, dDN_dx, dDN_dy); // :249-271
+
+					if (QUEUE && may_export) {
+						const int node_flags = flags | (reflection_mask ? FRAME_HAS_REFLECTION : 0);
+						const int n_shadow = defer_shadows ? P.light_count : 0;
+						const bool any_child = reflection_mask || ((flags & FRAME_HAS_REFRACTION) && !(flags & FRAME_TIR));
+						if (any_child || n_shadow > 0) {
+							const bool final_result = !defer_shadows;   // the lighting above is the node's (0 when the surface is not lit)
+							if (export_node(P, *q, hit, best.t, node_flags, frame.F_r, final_result ? result : material_diffuse, final_result, reflected, frame.refracted, bounces_left, n_shadow, cnt)) {
+								exported = true;
+								distance_out = best.t;
+								return result;
+							}
+						}
+						if (defer_shadows) { // not exported after all (a pool ran out, or nothing to wait for): the lighting that was put off
+							v3 diffuse = V(P.ambient[0], P.ambient[1], P.ambient[2]);
+							const v3 to_camera = normalize(V(P.cam_position[0], P.cam_position[1], P.cam_position[2]) - hit.point);
+							for (int i = 0; i < P.light_count; i++) {
+								LightSample s;
+								light_sample(P, i, hit.point, s);
+								cnt.shadow++;
+								if (trace_any_call<BSTACK>(P, hit.point, s.to_light, s.distance, cnt)) continue;
+								diffuse = light_add(diffuse, s, hit.normal, to_camera);
+							}
+							result = lit_result(diffuse, material_diffuse);
+							frame.result = result;
+							returned = result;
+						}
+					}
+
+					if (reflection_mask) {
 						cnt.reflection++;
 						frame.flags = flags | FRAME_AFTER_REFLECTION;
 						ray = reflected;
@@ -289,6 +516,7 @@ __device__ __forceinline__ v3 shade_subtree_body(const SceneParams & P, Ray ray,
 				}
 			}
 		}
+		top = false;
 		if (descend) continue;
 
 		// ---- a bounce() call returned: unwind pending frames (:264-271, :344-396) ---------------
@@ -327,284 +555,10 @@ __device__ __forceinline__ v3 shade_subtree_body(const SceneParams & P, Ray ray,
 	distance_out = returned_distance;
 	return returned;
 }
-// inlined into the kernel that does nothing else (no queue: the code of round 1) ...
 template<bool COUNT, int MAXB, int BSTACK>
 __device__ __forceinline__ v3 shade_subtree(const SceneParams & P, const Ray & ray, int bounces_left, Counters & cnt, float & distance_out) {
-	return shade_subtree_body<COUNT, MAXB, BSTACK>(P, ray, bounces_left, cnt, distance_out, nullptr);
-}
-// ... and ONE out-of-line copy for the queue kernel, which reaches it from four places (instruction fetch had shown
-// up with two inlined copies of the traversal in round 1: DESIGN.md 4)
-template<int MAXB, int BSTACK>
-__device__ __noinline__ v3 shade_subtree_call(const SceneParams & P, const Ray & ray, int bounces_left, Counters & cnt, float & distance_out, const Candidate * first_hit) {
-	return shade_subtree_body<false, MAXB, BSTACK>(P, ray, bounces_left, cnt, distance_out, first_hit);
-}
-
-// ------------------------------------------------------------------------------ deep-pixel queue ---
-// North_star's "wavefront traversal with ray compaction", restricted to where it pays: a pixel whose primary ray hits
-// glass is not walked by one thread. Every call of bounce() in its ray tree becomes a NODE RECORD in HBM and every ray
-// an ITEM in one of two device-side queues (bounce rays: closest hit + shading; shadow rays: any hit), which all
-// persistent warps pop 32 at a time (kernels.cuh) — so a warp always holds 32 rays of ONE kind (the compaction), the
-// shadow rays leave the pixel's critical chain (which rays are spawned never depends on a shadow ray's answer), and
-// the sibling subtrees of a fan-out run side by side on whatever warps are idle. A node's value is assembled when the
-// last of its shadow rays and children has reported (a countdown in the record), by the reporting thread, with the
-// reference's sums in the reference's order: the same bits as the recursive form.
-//
-//   node record  6 x float4   {parent, flags | which << 8, pending, material id} {point, distance} {normal, F_r}
-//                             {albedo, occluded-light bits} {reflection child's colour, -} {refraction child's colour, its distance}
-//   bounce item  5 x float4   the Ray (18 floats), parent node, which | bounces_left << 1     (parent = QUEUE_NULL_ITEM: skip)
-//   shadow item  2 x float4   {origin, max distance} {direction, node << 5 | light}           (word = QUEUE_NULL_ITEM: skip)
-// An item is visible to consumers once its word in the queue's `ready` array holds the frame's serial number (written
-// after a __threadfence()). Records and items are bump-allocated per frame; when a pool is exhausted the producer
-// walks the subtree itself (shade_subtree): always correct, never blocked. Records and items are read and written
-// with .cg accesses (L2 only): another SM's L1 may hold a stale copy of the line.
-#define RT_QUEUE_MAX_LIGHTS 24
-#define QUEUE_NULL_ITEM int(0x80000000u)
-
-__device__ __forceinline__ float as_f(int v) { return __int_as_float(v); }
-__device__ __forceinline__ int   as_i(float v) { return __float_as_int(v); }
-
-// Value of a node whose shadow rays and children have all reported (the record is complete and no longer written).
-__device__ __forceinline__ v3 node_value(const SceneParams & P, const float4 * rec, float & distance_out, int & parent, int & which) {
-	const float4 r0 = __ldcg(rec), r1 = __ldcg(rec + 1), r2 = __ldcg(rec + 2), r3 = __ldcg(rec + 3);
-	parent = as_i(r0.x);
-	const int flags = as_i(r0.y) & 0xff; which = (as_i(r0.y) >> 8) & 1;
-	const int material_id = as_i(r0.w);
-	const v3 point = V(r1), normal = V(r2), material_diffuse = V(r3);
-	const unsigned occluded = unsigned(as_i(r3.w));
-	distance_out = r1.w;
-
-	v3 result = V(0.0f, 0.0f, 0.0f);
-	if (dot(material_diffuse, material_diffuse) > 0.0f) {
-		v3 diffuse = V(P.ambient[0], P.ambient[1], P.ambient[2]);
-		const v3 to_camera = normalize(V(P.cam_position[0], P.cam_position[1], P.cam_position[2]) - point);
-		for (int i = 0; i < P.light_count; i++) {
-			if ((occluded >> i) & 1u) continue;
-			LightSample s;
-			light_sample(P, i, point, s);
-			diffuse = light_add(diffuse, s, normal, to_camera);
-		}
-		result = lit_result(diffuse, material_diffuse);
-	}
-	v3 colour_reflection = V(0.0f, 0.0f, 0.0f);
-	if (flags & FRAME_HAS_REFLECTION) {
-		const float4 m1 = __ldg(reinterpret_cast<const float4 *>(P.materials + material_id) + 1);
-		colour_reflection = V(m1) * V(__ldcg(rec + 4));
-		result = result + colour_reflection;
-		if (!(flags & FRAME_HAS_REFRACTION)) return result;
-		if (flags & FRAME_TIR) return result + colour_reflection;
-	} else if (!(flags & FRAME_HAS_REFRACTION) || (flags & FRAME_TIR)) {
-		return result;
-	}
-	const float4 r5 = __ldcg(rec + 5);
-	return refraction_blend(P, material_id, flags, r2.w, result, colour_reflection, V(r5), r5.w);
-}
-
-// A child's colour (and hit distance) goes into its parent's record; whoever brings a record's countdown to zero
-// computes the node's value and carries it one level up — up to the pixel.
-__device__ __noinline__ void deliver(const SceneParams & P, const PixelOut & out, int parent, int which, v3 value, float distance) {
-	for (;;) {
-		if (parent < 0) { // the root's parent is the pixel
-			const int p = -(parent + 1);
-			write_pixel(P, out, p % P.width, p / P.width, value);
-			return;
-		}
-		float4 * rec = P.q_nodes + 6 * size_t(parent);
-		__stcg(rec + 4 + which, make_float4(value.x, value.y, value.z, distance));
-		__threadfence();
-		if (atomicSub(reinterpret_cast<int *>(rec) + 2, 1) != 1) return;
-		__threadfence();
-		value = node_value(P, rec, distance, parent, which);
-	}
-}
-__device__ __forceinline__ void deliver_shadow(const SceneParams & P, const PixelOut & out, int node, int light, bool occluded) {
-	float4 * rec = P.q_nodes + 6 * size_t(node);
-	if (occluded) atomicOr(reinterpret_cast<unsigned *>(rec) + 15, 1u << light);
-	__threadfence();
-	if (atomicSub(reinterpret_cast<int *>(rec) + 2, 1) != 1) return;
-	__threadfence();
-	float distance; int parent, which;
-	const v3 value = node_value(P, rec, distance, parent, which);
-	deliver(P, out, parent, which, value, distance);
-}
-
-// Warp-collective reservation of n slots per lane in a bump-allocated pool: one atomicAdd per warp.
-// Returns the first slot of this lane; slots at or beyond the pool's capacity do not exist (the caller falls back).
-__device__ __forceinline__ unsigned warp_reserve(unsigned * counter, unsigned n) {
-	const int lane = threadIdx.x & 31;
-	unsigned before = n;
-#pragma unroll
-	for (int o = 1; o < 32; o <<= 1) { const unsigned v = __shfl_up_sync(0xffffffffu, before, o); if (lane >= o) before += v; }
-	const unsigned total = __shfl_sync(0xffffffffu, before, 31);
-	unsigned base = 0;
-	if (lane == 0 && total) base = atomicAdd(counter, total);
-	base = __shfl_sync(0xffffffffu, base, 0);
-	return base + before - n;
-}
-
-// Warp-collective counter update: one atomicAdd per warp.
-__device__ __forceinline__ void warp_add(int * counter, int n) {
-#pragma unroll
-	for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
-	if ((threadIdx.x & 31) == 0 && n != 0) atomicAdd(counter, n);
-}
-__device__ __forceinline__ unsigned peek(const unsigned * p) { return *reinterpret_cast<const volatile unsigned *>(p); }   // a fresh value, not this SM's L1 copy
-__device__ __forceinline__ int      peek(const int * p)      { return *reinterpret_cast<const volatile int *>(p); }
-
-__device__ __forceinline__ void publish(unsigned * ready, unsigned slot, unsigned serial) { __stcg(ready + slot, serial); }   // behind a __threadfence() that follows the payload
-__device__ __forceinline__ void write_bounce_item(const SceneParams & P, unsigned slot, const Ray & r, int parent, int which, int bounces_left) {
-	float4 * item = P.q_bounce + 5 * size_t(slot);
-	__stcg(item,     make_float4(r.origin.x, r.origin.y, r.origin.z, r.direction.x));
-	__stcg(item + 1, make_float4(r.direction.y, r.direction.z, r.dO_dx.x, r.dO_dx.y));
-	__stcg(item + 2, make_float4(r.dO_dx.z, r.dO_dy.x, r.dO_dy.y, r.dO_dy.z));
-	__stcg(item + 3, make_float4(r.dD_dx.x, r.dD_dx.y, r.dD_dx.z, r.dD_dy.x));
-	__stcg(item + 4, make_float4(r.dD_dy.y, r.dD_dy.z, as_f(parent), as_f(which | (bounces_left << 1))));
-}
-__device__ __forceinline__ void read_bounce_item(const SceneParams & P, unsigned slot, Ray & r, int & parent, int & which, int & bounces_left) {
-	const float4 * item = P.q_bounce + 5 * size_t(slot);
-	const float4 a = __ldcg(item), b = __ldcg(item + 1), c = __ldcg(item + 2), d = __ldcg(item + 3), e = __ldcg(item + 4);
-	r.origin = V(a.x, a.y, a.z); r.direction = V(a.w, b.x, b.y);
-	r.dO_dx = V(b.z, b.w, c.x); r.dO_dy = V(c.y, c.z, c.w);
-	r.dD_dx = V(d.x, d.y, d.z); r.dD_dy = V(d.w, e.x, e.y);
-	parent = as_i(e.z); which = as_i(e.w) & 1; bounces_left = as_i(e.w) >> 1;
-}
-__device__ __forceinline__ void write_null_bounce_item(const SceneParams & P, unsigned slot) {
-	__stcg(P.q_bounce + 5 * size_t(slot) + 4, make_float4(0.0f, 0.0f, as_f(QUEUE_NULL_ITEM), 0.0f));
-}
-__device__ __forceinline__ void write_shadow_item(const SceneParams & P, unsigned slot, v3 origin, v3 direction, float max_distance, int word) {
-	float4 * item = P.q_shadow + 2 * size_t(slot);
-	__stcg(item,     make_float4(origin.x, origin.y, origin.z, max_distance));
-	__stcg(item + 1, make_float4(direction.x, direction.y, direction.z, as_f(word)));
-}
-
-// One call of bounce() as a work item. WARP-COLLECTIVE: all 32 lanes call it; `active` lanes carry a ray.
-// parent < 0: the ray is the primary ray of pixel -(parent + 1). The items it queues are added to the frame's count of
-// outstanding work (FrameCounters::q_outstanding) BEFORE they become visible, so the count never runs low; the caller
-// subtracts the item (or tile unit) this call finishes (kernels.cuh).
-template<int MAXB, int BSTACK>
-__device__ __forceinline__ void process_bounce(const SceneParams & P, const PixelOut & out, FrameCounters * counters, bool active, const Ray & ray, int bounces_left, int parent, int which, Counters & cnt) {
-	// ---- closest hit, hit record, albedo, which rays this node spawns -------------------------------
-	Candidate best;
-	HitRecord hit;
-	v3 material_diffuse = V(0.0f, 0.0f, 0.0f);
-	int flags = 0;
-	float F_r = 0.0f;
-	bool want_node = false;
-	Ray reflected, refracted;
-
-	best.t = 0.0f; best.instance = HIT_NONE;
-	if (active) {
-		trace_closest<false, BSTACK>(P, ray.origin, ray.direction, best, cnt);
-		if (best.instance == HIT_NONE) {
-			deliver(P, out, parent, which, sky_sample<false>(P, ray.direction, cnt), CUDART_INF_F);
-			active = false;
-		}
-	}
-	if (active) {
-		build_record(P, ray, best, hit);
-		const float4 * mp = reinterpret_cast<const float4 *>(P.materials + hit.material_id);
-		material_diffuse = get_albedo<false>(P, __ldg(mp), hit, cnt);
-
-		bool reflection_mask = false, refraction_mask = false;
-		float4 m1 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-		if (bounces_left > 0) {
-			m1 = __ldg(mp + 1);
-			const float4 m2 = __ldg(mp + 2);
-			reflection_mask = dot(V(m1), V(m1)) > 0.0f;
-			refraction_mask = dot(V(m2), V(m2)) > 0.0f;
-		}
-		// Who is queued: a primary ray that hits glass (queue_mode 1) or anything with children (queue_mode 2); every ray
-		// below a queued node down to queue_inline_below bounces left. The rest is walked depth-first right here.
-		const bool queued = parent >= 0 ? bounces_left > P.queue_inline_below
-		                                : (P.queue_mode == 2 ? (reflection_mask || refraction_mask) : refraction_mask);
-		if (!queued) {
-			float distance;
-			const v3 value = shade_subtree_call<MAXB, BSTACK>(P, ray, bounces_left, cnt, distance, &best);
-			deliver(P, out, parent, which, value, distance);
-		} else {
-			if (reflection_mask || refraction_mask) {
-				const float d_dot_n = dot(ray.direction, hit.normal);
-				const float dDN_dx = dot(ray.dD_dx, hit.normal) + dot(ray.direction, hit.dN_dx);
-				const float dDN_dy = dot(ray.dD_dy, hit.normal) + dot(ray.direction, hit.dN_dy);
-				if (refraction_mask) flags |= refraction_setup(ray, hit, m1.w, d_dot_n, dDN_dx, dDN_dy, refracted, F_r);
-				if (reflection_mask) { flags |= FRAME_HAS_REFLECTION; reflected = reflection_ray(ray, hit, d_dot_n, dDN_dx, dDN_dy); }
-			}
-			want_node = true;
-		}
-	}
-
-	// ---- node record + items: three pool reservations per warp ----------------------------------------
-	const bool lit = want_node && dot(material_diffuse, material_diffuse) > 0.0f;
-	const int n_children = !want_node ? 0 : ((flags & FRAME_HAS_REFLECTION) ? 1 : 0) + (((flags & FRAME_HAS_REFRACTION) && !(flags & FRAME_TIR)) ? 1 : 0);
-	const int n_shadow   = lit ? P.light_count : 0;
-	if (want_node && n_children + n_shadow == 0) { // nothing to wait for: result = 0 (:141), or ambient * albedo with no lights (:144,:200)
-		v3 result = V(0.0f, 0.0f, 0.0f);
-		if (lit) result = lit_result(V(P.ambient[0], P.ambient[1], P.ambient[2]), material_diffuse);
-		deliver(P, out, parent, which, result, best.t);
-		want_node = false;
-	}
-	const unsigned node_slot   = warp_reserve(&counters->q_node_reserved,   want_node ? 1u : 0u);
-	const unsigned bounce_slot = warp_reserve(&counters->q_bounce_reserved, want_node ? unsigned(n_children) : 0u);
-	const unsigned shadow_slot = warp_reserve(&counters->q_shadow_reserved, want_node ? unsigned(n_shadow) : 0u);
-	warp_add(&counters->q_outstanding, want_node ? n_children + n_shadow : 0);
-	if (!want_node) return;
-
-	if (node_slot >= P.q_node_capacity) { // no record to be had: walk the subtree here; the item slots reserved above are published empty
-		for (int k = 0; k < n_children; k++) if (bounce_slot + k < P.q_bounce_capacity) write_null_bounce_item(P, bounce_slot + k);
-		for (int i = 0; i < n_shadow; i++)   if (shadow_slot + i < P.q_shadow_capacity) write_shadow_item(P, shadow_slot + i, hit.point, hit.normal, 0.0f, QUEUE_NULL_ITEM);
-		__threadfence();
-		for (int k = 0; k < n_children; k++) if (bounce_slot + k < P.q_bounce_capacity) publish(P.q_bounce_ready, bounce_slot + k, P.frame_serial);
-		for (int i = 0; i < n_shadow; i++)   if (shadow_slot + i < P.q_shadow_capacity) publish(P.q_shadow_ready, shadow_slot + i, P.frame_serial);
-		float distance;
-		const v3 value = shade_subtree_call<MAXB, BSTACK>(P, ray, bounces_left, cnt, distance, &best);
-		deliver(P, out, parent, which, value, distance);
-		atomicAdd(&counters->q_fallbacks, 1u);
-		atomicSub(&counters->q_outstanding, n_children + n_shadow);
-		return;
-	}
-
-	const int node = int(node_slot);
-	float4 * rec = P.q_nodes + 6 * size_t(node);
-	__stcg(rec,     make_float4(as_f(parent), as_f(flags | (which << 8)), as_f(n_children + n_shadow), as_f(hit.material_id)));
-	__stcg(rec + 1, make_float4(hit.point.x, hit.point.y, hit.point.z, best.t));
-	__stcg(rec + 2, make_float4(hit.normal.x, hit.normal.y, hit.normal.z, F_r));
-	__stcg(rec + 3, make_float4(material_diffuse.x, material_diffuse.y, material_diffuse.z, as_f(0)));
-	// Payloads first — the record above, every item that has a slot — then ONE __threadfence(), then the items' ready
-	// words: record and items are in L2 before any consumer can see an item that names the record. Whatever found no
-	// slot is walked right here afterwards (its report may complete the record: the record is visible by then).
-	const bool has_child[2] = { (flags & FRAME_HAS_REFLECTION) != 0, (flags & FRAME_HAS_REFRACTION) && !(flags & FRAME_TIR) };
-	unsigned child_slot[2] = { bounce_slot, bounce_slot + (has_child[0] ? 1u : 0u) };
-	for (int k = 0; k < 2; k++) { // children (Raytracer.cpp:249-271, :316-342)
-		if (!has_child[k]) continue;
-		if (k == 0) cnt.reflection++; else cnt.refraction++;
-		if (child_slot[k] < P.q_bounce_capacity) write_bounce_item(P, child_slot[k], k == 0 ? reflected : refracted, node, k, bounces_left - 1);
-	}
-	for (int i = 0; i < n_shadow; i++) { // shadow rays (:155-198)
-		cnt.shadow++;
-		if (shadow_slot + i >= P.q_shadow_capacity) continue;
-		LightSample s;
-		light_sample(P, i, hit.point, s);
-		write_shadow_item(P, shadow_slot + i, hit.point, s.to_light, s.distance, (node << 5) | i);
-	}
-	__threadfence();
-	for (int k = 0; k < 2; k++) if (has_child[k] && child_slot[k] < P.q_bounce_capacity) publish(P.q_bounce_ready, child_slot[k], P.frame_serial);
-	for (int i = 0; i < n_shadow; i++) if (shadow_slot + i < P.q_shadow_capacity) publish(P.q_shadow_ready, shadow_slot + i, P.frame_serial);
-
-	for (int k = 0; k < 2; k++) { // a pool was exhausted: no slot, no item
-		if (!has_child[k] || child_slot[k] < P.q_bounce_capacity) continue;
-		float distance;
-		const v3 value = shade_subtree_call<MAXB, BSTACK>(P, k == 0 ? reflected : refracted, bounces_left - 1, cnt, distance, nullptr);
-		deliver(P, out, node, k, value, distance);
-		atomicAdd(&counters->q_fallbacks, 1u);
-		atomicSub(&counters->q_outstanding, 1);
-	}
-	for (int i = 0; i < n_shadow; i++) {
-		if (shadow_slot + i < P.q_shadow_capacity) continue;
-		LightSample s;
-		light_sample(P, i, hit.point, s);
-		deliver_shadow(P, out, node, i, trace_any<false, BSTACK>(P, hit.point, s.to_light, s.distance, cnt));
-		atomicAdd(&counters->q_fallbacks, 1u);
-		atomicSub(&counters->q_outstanding, 1);
-	}
+	bool exported = false;
+	return shade_subtree_body<COUNT, MAXB, BSTACK, false>(P, ray, bounces_left, cnt, distance_out, nullptr, exported);
 }
 
 } // namespace RT_NAMESPACE

@@ -82,6 +82,7 @@ struct SceneParams {
 	int width, height, bounces, mipmap_filter;
 	float max_anisotropy;
 	int traversal_naive, texture_sample_mode;   // BVH_TRAVERSAL_STRATEGY, TEXTURE_SAMPLE_MODE
+	int count_shipped_walk;                     // counting build: count the any-hit walk that ships (threaded, right child first) instead of the reference's
 	int tiles_x, tiles_y, tile_stride, tile_phase, tile_count_mine;
 	// schedule (kernels.cuh, tile_schedule_kernel): this GPU's tiles in hand-out order, and where this
 	// frame's cost per tile is accumulated for the next frame's order
@@ -100,7 +101,8 @@ struct SceneParams {
 	unsigned q_node_capacity, q_bounce_capacity, q_shadow_capacity;
 	unsigned frame_serial;       // never 0, different for every launch of a context
 	int queue_mode;              // 0 off; 1: pixels whose primary ray hits a transmissive material; 2: every pixel whose primary hit spawns rays
-	int queue_inline_below;      // a queued ray with at most this many bounces left is walked depth-first by the thread that popped it (-1: never)
+	int queue_inline_below;      // a popped ray with at most this many bounces left is walked to the end by the thread that popped it
+	int queue_defer_shadows;     // an exported node's shadow rays are queued with it (1) or traced before the export (0)
 	int blas_stack_entries;      // deepest BLAS + 1: what a push-both-pop-one traversal can hold
 };
 

@@ -258,7 +258,8 @@ __device__ __forceinline__ bool blas_intersect(const float4 * __restrict__ nodes
 // The same query on the threaded copy of the tree (threaded_nodes.h: build_threaded_nodes): records lie in
 // the order they are visited (right child first), so a hit inner node continues with the next
 // record and everything else follows the record's skip link — no stack, no push, no pop.
-__device__ __forceinline__ bool blas_shadow(const float4 * __restrict__ records, const float4 * __restrict__ hot, v3 o, v3 d, float max_distance) {
+template<bool COUNT>
+__device__ __forceinline__ bool blas_shadow(const float4 * __restrict__ records, const float4 * __restrict__ hot, v3 o, v3 d, float max_distance, Counters & cnt) {
 	const v3 inv_d = inv_direction(d);
 	const bool exact = !ray_is_regular(o, inv_d);
 	const v3 so = slab_origin(o, inv_d);
@@ -268,12 +269,14 @@ __device__ __forceinline__ bool blas_shadow(const float4 * __restrict__ records,
 		const float4 n0 = load_node(records + 2 * index), n1 = load_node(records + 2 * index + 1);
 		int next = __float_as_int(n1.z);                       // skip link
 		if (next >= 0) prefetch_record(records + 2 * next);
+		if (COUNT) cnt.nodes++;
 		if (aabb_intersect(n0, n1, so, inv_d, max_distance, exact)) {
 			const int leaf = __float_as_int(n1.w);
 			if (leaf != 0) {
 				const int first = leaf >> 6, count = leaf & 63;
 				for (int i = first; i < first + count; i++) {
 					float t, u, v;
+					if (COUNT) cnt.triangles++;
 					if (triangle_test(hot + 3 * size_t(i), o, d, max_distance, t, u, v)) return true;
 				}
 			} else {
@@ -504,8 +507,9 @@ __device__ __forceinline__ bool trace_any(const SceneParams & P, v3 o, v3 d, flo
 					}
 				}
 #endif
-				if (COUNT ? blas_intersect<COUNT>(P.nodes + 2 * size_t(inst.node_offset), hot, local_o, local_d, max_distance, blas_stack, cnt, traversal_order_mask(P, local_d))
-				          : blas_shadow(P.shadow_nodes + 2 * size_t(inst.shadow_node_offset), hot, local_o, local_d, max_distance)) return true;
+				// the counting build counts the reference's walk, or (count_traversal = 2) the walk that ships
+				if (COUNT && !P.count_shipped_walk ? blas_intersect<COUNT>(P.nodes + 2 * size_t(inst.node_offset), hot, local_o, local_d, max_distance, blas_stack, cnt, traversal_order_mask(P, local_d))
+				                                   : blas_shadow<COUNT>(P.shadow_nodes + 2 * size_t(inst.shadow_node_offset), hot, local_o, local_d, max_distance, cnt)) return true;
 			}
 		} else if (P.traversal_naive || visit_left_first(count, d)) {
 			tlas_stack[stack_size++] = left_or_first + 1;
@@ -516,6 +520,13 @@ __device__ __forceinline__ bool trace_any(const SceneParams & P, v3 o, v3 d, flo
 		}
 	}
 	return false;
+}
+
+// One out-of-line copy of the shipped any-hit query, for the places that are not hot (the deep-pixel queue's shadow
+// items and its fall-back lighting): a third inlined copy of the traversal would cost the hot loop instruction cache.
+template<int BSTACK>
+__device__ __noinline__ bool trace_any_call(const SceneParams & P, v3 o, v3 d, float max_distance, Counters & cnt) {
+	return trace_any<false, BSTACK>(P, o, d, max_distance, cnt);
 }
 
 } // namespace RT_NAMESPACE

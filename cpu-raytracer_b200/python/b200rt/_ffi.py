@@ -68,6 +68,13 @@ class Stats(C.Structure):
         return {name: getattr(self, name) for name, _ in self._fields_}
 
 
+class PeerHandle(C.Structure):          # b200rt_peer_handle (a cudaIpcMemHandle_t)
+    _fields_ = [("bytes", C.c_ubyte * 64)]
+
+
+BARRIER_BYTES = 64                      # B200RT_BARRIER_BYTES
+
+
 class Outputs(C.Structure):
     _fields_ = [
         ("frame_buffer", C.c_void_p), ("presented_rgb8", C.c_void_p), ("colour_float", C.c_void_p),
@@ -86,7 +93,7 @@ def make_config(width, height, bounces, mipmap_filter="aniso", max_anisotropy=8.
     f = FILTERS[mipmap_filter] if isinstance(mipmap_filter, str) else int(mipmap_filter)
     arithmetic = arithmetic or os.environ.get("B200RT_ARITHMETIC", "exact")     # the environment overrides the defaults (tools/, variant timing)
     deep_queue = deep_queue or os.environ.get("B200RT_DEEP_QUEUE", DEFAULT_DEEP_QUEUE)
-    return Config(width, height, bounces, f, max_anisotropy, 1 if enable_fxaa else 0, device, tile_stride, tile_phase, 1 if count_traversal else 0,
+    return Config(width, height, bounces, f, max_anisotropy, 1 if enable_fxaa else 0, device, tile_stride, tile_phase, int(count_traversal),
                   TRAVERSALS[traversal], TEXTURE_MODES[texture_mode], ARITHMETIC[arithmetic], DEEP_QUEUE[deep_queue])
 
 
@@ -134,6 +141,14 @@ def device_lib():
         lib.b200rt_upload_static.argtypes = [C.c_void_p, C.POINTER(StaticScene)]
         lib.b200rt_render_frame.argtypes = [C.c_void_p, C.POINTER(Frame), C.POINTER(Outputs)]
         lib.b200rt_render_frame_device.argtypes = [C.c_void_p, C.POINTER(Frame), C.c_uint64, C.POINTER(Stats)]
+        lib.b200rt_last_frame_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
+        lib.b200rt_peer_alloc.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(PeerHandle)]
+        lib.b200rt_peer_free.argtypes = [C.c_void_p, C.c_uint64]
+        lib.b200rt_peer_open.argtypes = [C.c_void_p, C.POINTER(PeerHandle), C.POINTER(C.c_uint64)]
+        lib.b200rt_peer_close.argtypes = [C.c_void_p, C.c_uint64]
+        lib.b200rt_peer_read.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64]
+        lib.b200rt_barrier_setup.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.c_int32, C.c_int32]
+        lib.b200rt_barrier.argtypes = [C.c_void_p]
         lib.b200rt_present_device.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_float)]
         lib.b200rt_set_band_targets.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.c_int32, C.c_int32, C.c_int32]
         lib.b200rt_present_rows_device.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_int32, C.c_int32, C.POINTER(C.c_float)]

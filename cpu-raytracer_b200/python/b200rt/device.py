@@ -122,6 +122,12 @@ class Renderer:
         self._check(self._lib.b200rt_render_frame_device(self._h, C.byref(frame), C.c_uint64(frame_buffer_ptr), C.byref(stats)))
         return stats.as_dict()
 
+    def last_frame_stats(self):
+        """Counters of the frame rendered last (waits for the stream); device_ms_render = the kernel's own globaltimer span."""
+        stats = _ffi.Stats()
+        self._check(self._lib.b200rt_last_frame_stats(self._h, C.byref(stats)))
+        return stats.as_dict()
+
     def present_device(self, frame_buffer_ptr, presented_ptr, wait=True):
         if not wait:
             self._check(self._lib.b200rt_present_device(self._h, C.c_uint64(frame_buffer_ptr), C.c_uint64(presented_ptr), None))

@@ -10,10 +10,10 @@ image (its taps reach across tile borders and wrap at the frame border).
 Every rank renders into a zero-initialised uint32 [H][W] buffer and touches only its own tiles, so
 a SUM reduction to rank 0 *is* the gather (x + 0 = x, bit for bit), with no packing kernels on
 either side. Works with any torch.distributed backend (NCCL on the GPUs, gloo in the CPU tests).
-"""
-import torch
-import torch.distributed as dist
 
+PyTorch is imported only by the pieces that wrap a torch collective or hand out a tensor view; the band exchange
+itself (PeerImages: peer memory and the device barrier of include/b200rt.h) runs through the C ABI alone.
+"""
 TILE = 32  # Window.h:32-33
 
 
@@ -36,6 +36,7 @@ def tile_rect(width, height, tile):
 
 def owner_mask(width, height, world, rank):
     """bool [H][W]: pixels owned by `rank`."""
+    import torch
     tx, ty = tile_grid(width, height)
     ids = (torch.arange(ty).unsqueeze(1) * tx + torch.arange(tx).unsqueeze(0)) % world == rank
     return ids.repeat_interleave(TILE, 0).repeat_interleave(TILE, 1)[:height, :width]
@@ -49,6 +50,7 @@ class FrameGather:
 
     def __call__(self, frame_buffer):
         """frame_buffer: int32 tensor [H][W], zero outside this rank's tiles. In place on dst."""
+        import torch.distributed as dist
         if dist.is_initialized() and dist.get_world_size(self.group) > 1:
             dist.reduce(frame_buffer, dst=self.dst, op=dist.ReduceOp.SUM, group=self.group)
         return frame_buffer
@@ -109,36 +111,88 @@ class BandExchangeGeneric:
     """The band exchange over any torch.distributed backend (gloo in the CPU tests): every rank ends up
     with the rows of its band + halo, taken from whichever rank traced them. One all_reduce(SUM) of
     images that are zero outside the sender's tiles — same trick as FrameGather; the GPU path moves
-    only the rows each rank needs (BandFrames)."""
+    only the rows each rank needs (PeerImages)."""
 
     def __init__(self, group=None):
         self.group = group
 
     def __call__(self, frame_buffer):
+        import torch.distributed as dist
         if dist.is_initialized() and dist.get_world_size(self.group) > 1:
             dist.all_reduce(frame_buffer, op=dist.ReduceOp.SUM, group=self.group)
         return frame_buffer
 
 
-class BandFrames:
-    """One full-size pre-FXAA image per rank in CUDA symmetric memory, each mapped into every rank.
+class PeerImages:
+    """Device buffers of every rank that every rank of the node has mapped (include/b200rt.h: b200rt_peer_alloc /
+    b200rt_peer_open — cudaIpc handles, NVLink peer access), plus the ranks' flag blocks for the device-side barrier
+    (b200rt_barrier_setup / b200rt_barrier). No framework is involved on the data path: the 64-byte handles are the
+    only thing the processes exchange, once, at set-up — through `exchange`, a callable that takes this rank's bytes
+    and returns every rank's (bench.py passes an all_gather over its process group, tests/test_peer_exchange.py uses
+    files; a C++ host would use a pipe).
 
-    ptrs[r] = rank r's image as seen from this process: the list b200rt_set_band_targets wants. Only
-    the rows of a rank's band (+ halo) are ever written in its image."""
+    sizes[k] = bytes of buffer k (every rank allocates the same list); ptrs[k][r] = rank r's buffer k as mapped in this
+    process — for an image, the list b200rt_set_band_targets wants."""
 
-    def __init__(self, height, width, world, rank, group=None, dtype=torch.int32, channels=None):
-        import torch.distributed._symmetric_memory as symm_mem
-        self.group = group if group is not None else dist.group.WORLD
-        shape = (height, width) if channels is None else (height, width, channels)
-        self.local = symm_mem.empty(shape, dtype=dtype, device=torch.device("cuda", torch.cuda.current_device()))
-        self.local.zero_()
-        self.handle = symm_mem.rendezvous(self.local, self.group)
-        self.ptrs = [int(self.handle.buffer_ptrs[r]) for r in range(world)]
-        self.rank = rank
+    def __init__(self, renderer, world, rank, exchange, sizes):
+        import ctypes as C
+        from . import _ffi
+        self.renderer, self.world, self.rank, self.sizes = renderer, world, rank, list(sizes)
+        self._lib, self._h = renderer._lib, renderer._h
+        mine, handles = [], []
+        for size in self.sizes + [_ffi.BARRIER_BYTES]:    # the last allocation is the barrier's flag block
+            ptr, handle = C.c_uint64(), _ffi.PeerHandle()
+            renderer._check(self._lib.b200rt_peer_alloc(self._h, size, C.byref(ptr), C.byref(handle)))
+            mine.append(ptr.value)
+            handles.append(bytes(handle.bytes))
+        self._mine = mine
+        everyone = exchange(b"".join(handles))            # [world] x (len(sizes) + 1) x 64 bytes
+        self._opened = []
+        table = []
+        for r in range(world):
+            row = []
+            for k in range(len(mine)):
+                if r == rank:
+                    row.append(mine[k])
+                    continue
+                handle = _ffi.PeerHandle.from_buffer_copy(everyone[r][64 * k:64 * (k + 1)])
+                ptr = C.c_uint64()
+                renderer._check(self._lib.b200rt_peer_open(self._h, C.byref(handle), C.byref(ptr)))
+                self._opened.append(ptr.value)
+                row.append(ptr.value)
+            table.append(row)
+        self.ptrs = [[table[r][k] for r in range(world)] for k in range(len(self.sizes))]
+        flags = (C.c_uint64 * world)(*[table[r][len(self.sizes)] for r in range(world)])
+        renderer._check(self._lib.b200rt_barrier_setup(self._h, flags, world, rank))
 
     def barrier(self):
-        """Device-side barrier of all ranks, enqueued on the current stream."""
-        self.handle.barrier()
+        """Device-side barrier of all ranks, enqueued on the renderer's stream (one tiny kernel, no host involvement)."""
+        self.renderer._check(self._lib.b200rt_barrier(self._h))
+
+    def read(self, k, dtype, shape):
+        """This rank's buffer k copied to the host (b200rt_peer_read: waits for the renderer's stream)."""
+        import numpy as np
+        out = np.zeros(shape, dtype=dtype)
+        assert out.nbytes <= self.sizes[k]
+        self.renderer._check(self._lib.b200rt_peer_read(self._h, self._mine[k], out.ctypes.data, out.nbytes))
+        return out
+
+    def tensor(self, k, shape, itemsize):
+        """This rank's buffer k as a torch tensor over the same device memory (int32 / uint8): a view, not a copy."""
+        import torch
+
+        class _Span:
+            pass
+        span = _Span()
+        span.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<i4" if itemsize == 4 else "|u1", "data": (self._mine[k], False), "version": 2}
+        return torch.as_tensor(span, device="cuda")
+
+    def close(self):
+        for p in self._opened:
+            self._lib.b200rt_peer_close(self._h, p)
+        for p in self._mine:
+            self._lib.b200rt_peer_free(self._h, p)
+        self._opened, self._mine = [], []
 
 
 class PrivateHostImage:
@@ -147,6 +201,7 @@ class PrivateHostImage:
 
     def __init__(self, shape, dtype):
         import numpy as np
+        import torch
         self.tensor = torch.empty(tuple(shape), dtype=torch.from_numpy(np.zeros(1, dtype=dtype)).dtype).pin_memory()
         self.array = self.tensor.numpy()
         self.registered = True
@@ -174,6 +229,7 @@ class SharedHostImage:
 
     def __init__(self, name, shape, dtype, create):
         import numpy as np
+        import torch
         from multiprocessing import shared_memory
         nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
         self.shm = shared_memory.SharedMemory(name=name, create=create, size=nbytes)
@@ -192,12 +248,14 @@ class SharedHostImage:
     def register(self):
         """Page-locks the mapping in this process. Call after every rank has written its own rows once:
         registration faults all pages in, and a page lives on the NUMA node of whoever touches it first."""
+        import torch
         rc = torch.cuda.cudart().cudaHostRegister(self.tensor.data_ptr(), self.nbytes, 0)
         self.registered = int(rc) == 0
         return self.registered
 
     def close(self):
         if self.registered:
+            import torch
             torch.cuda.cudart().cudaHostUnregister(self.tensor.data_ptr())
             self.registered = False
         del self.tensor, self.array

@@ -143,7 +143,9 @@ typedef struct {
 	 * row-major id t satisfies t % tile_stride == tile_phase. 1 / 0 = the whole frame.       */
 	int32_t tile_stride, tile_phase;
 	/* 1 = also count BVH nodes visited / triangles tested / texels fetched (b200rt_stats), the
-	 * run-time cousin of BVH_VISUALIZE_HEATMAP (Config.h:23). Costs registers: keep 0 when timing. */
+	 * run-time cousin of BVH_VISUALIZE_HEATMAP (Config.h:23): the work of the REFERENCE's algorithm (its visiting
+	 * order for shadow rays too). 2 = the same counters for the walk that ships (shadow rays on the threaded copy,
+	 * right child first). Costs registers: keep 0 when timing.                                    */
 	int32_t count_traversal;
 	/* BVH_TRAVERSAL_STRATEGY (Config.h:27-30, BVHNode.h:30-40): 0 = BVH_TRAVERSE_TREE_ORDERED, the shipped setting (the
 	 * child on the ray's side of the split plane first), 1 = BVH_TRAVERSE_TREE_NAIVE (always the left child first).    */
@@ -241,6 +243,11 @@ int b200rt_render_frame_device(b200rt_ctx * ctx, const b200rt_frame * frame,
 /* stats == NULL (and device_ms == NULL below): the call only ENQUEUES on the context's stream and
  * returns; the caller synchronises (or orders a collective) on b200rt_stream().              */
 
+/* Counters of the frame rendered last by any entry point (waits for the context's stream). device_ms_render is the
+ * render kernel's own %globaltimer span (first block started .. last warp done): what an asynchronous caller
+ * (stats == NULL above) reads afterwards instead of paying for timing events on the stream.        */
+int b200rt_last_frame_stats(b200rt_ctx * ctx, b200rt_stats * stats);
+
 /* FXAA + gamma over a full pre-FXAA frame that is already in device memory (after the
  * multi-GPU gather): in uint32 [height][width], out uint8 [height][width][3].              */
 int b200rt_present_device(b200rt_ctx * ctx, uint64_t frame_buffer_dev, uint64_t presented_dev, float * device_ms);
@@ -258,10 +265,37 @@ int b200rt_present_device(b200rt_ctx * ctx, uint64_t frame_buffer_dev, uint64_t 
 #define B200RT_MAX_BANDS 8
 int b200rt_set_band_targets(b200rt_ctx * ctx, const uint64_t * targets, int32_t band_count, int32_t band_rows, int32_t halo_rows);
 
+/* Peer memory and a device-side barrier, so that a host with no framework at all — the reference is a plain C++
+ * program — can run the band exchange: what the worker threads' one shared frame_buffer (Window.h:56-65,
+ * WorkerThread.cpp:53-65) becomes when the workers are GPUs in separate processes. Every process allocates its image
+ * with b200rt_peer_alloc, hands the 64-byte handle to the others by any means it likes (a pipe, a file, MPI, ...), maps
+ * theirs with b200rt_peer_open and passes the addresses to b200rt_set_band_targets. The handle is a cudaIpcMemHandle_t:
+ * one node, NVLink / PCIe peer access between the devices. Memory comes back zeroed.                               */
+typedef struct { unsigned char bytes[64]; } b200rt_peer_handle;
+int b200rt_peer_alloc(b200rt_ctx * ctx, uint64_t bytes, uint64_t * device_ptr, b200rt_peer_handle * handle);
+int b200rt_peer_free (b200rt_ctx * ctx, uint64_t device_ptr);
+int b200rt_peer_open (b200rt_ctx * ctx, const b200rt_peer_handle * handle, uint64_t * device_ptr);
+int b200rt_peer_close(b200rt_ctx * ctx, uint64_t device_ptr);
+/* Copies `bytes` of device memory (a peer buffer, an image) to the host, after the context's stream has drained.   */
+int b200rt_peer_read (b200rt_ctx * ctx, uint64_t device_ptr, void * host, uint64_t bytes);
+
+/* Barrier of `count` contexts (<= B200RT_MAX_BANDS) ON THE DEVICE: flag_blocks[r] = address, in this process, of rank
+ * r's flag block (B200RT_BARRIER_BYTES of peer memory, zeroed, never written by the host afterwards). b200rt_barrier
+ * enqueues one tiny kernel on the context's stream: it tells every peer "rank `rank` has reached barrier k" with a
+ * store into the peer's block and waits until its own block says so of everybody; stores issued by earlier kernels of
+ * this stream (the render kernel's pixels in the other GPUs' images) are visible to the peers' later kernels. All
+ * ranks must call it the same number of times. Nothing here touches the host after the call returns.            */
+#define B200RT_BARRIER_BYTES 64
+int b200rt_barrier_setup(b200rt_ctx * ctx, const uint64_t * flag_blocks, int32_t count, int32_t rank);
+int b200rt_barrier(b200rt_ctx * ctx);
+
 /* b200rt_present_device over rows [row_begin, row_end) only; frame_buffer_dev and presented_dev are
  * the bases of full-size images (presented_dev may be another GPU's, mapped here).                   */
 int b200rt_present_rows_device(b200rt_ctx * ctx, uint64_t frame_buffer_dev, uint64_t presented_dev,
                                int32_t row_begin, int32_t row_end, float * device_ms);
+
+/* (b200rt_render_frame, b200rt_submit_frame and b200rt_time_resident always render into the one image they own:
+ * band targets apply to b200rt_render_frame_device only.)                                        */
 
 /* Re-times the last frame without host<->device traffic: `repeat` launches of the render
  * (+FXAA) kernels on resident inputs, each timed with CUDA events on the context's stream;

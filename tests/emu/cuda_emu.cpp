@@ -73,7 +73,9 @@ unsigned warp_exchange(unsigned mask, unsigned value, int source_lane) {
 	const unsigned generation = w->generation;
 	if (w->arrived == mask) { w->leaving = mask; w->arrived = 0; w->generation++; }
 	else while (w->generation == generation) yield();
-	const unsigned result = source_lane < 0 ? 0u : (((mask >> source_lane) & 1u) ? w->slots[source_lane] : value);
+	unsigned result = 0u;
+	if (source_lane == -2) { for (int l = 0; l < 32; l++) if ((mask >> l) & 1u) result |= w->slots[l]; }   // ballot: OR of what the lanes deposited
+	else if (source_lane >= 0) result = ((mask >> source_lane) & 1u) ? w->slots[source_lane] : value;
 	w->leaving &= ~(1u << lane);
 	return result;
 }

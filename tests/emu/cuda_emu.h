@@ -98,6 +98,11 @@ static inline cudaError_t cudaEventRecord(cudaEvent_t e, cudaStream_t) { e->ms =
 static inline cudaError_t cudaEventSynchronize(cudaEvent_t) { return cudaSuccess; }
 static inline cudaError_t cudaEventElapsedTime(float * ms, cudaEvent_t a, cudaEvent_t b) { *ms = float(b->ms - a->ms); return cudaSuccess; }
 static inline cudaError_t cudaPointerGetAttributes(cudaPointerAttributes * a, const void * p) { a->type = emu::is_host_alloc(p) ? cudaMemoryTypeHost : cudaMemoryTypeUnregistered; return cudaSuccess; }
+struct cudaIpcMemHandle_t { char reserved[64]; };
+enum { cudaIpcMemLazyEnablePeerAccess = 1 };
+static inline cudaError_t cudaIpcGetMemHandle(cudaIpcMemHandle_t * h, void * p) { memset(h, 0, sizeof(*h)); memcpy(h, &p, sizeof(p)); return cudaSuccess; }   // one process: the handle IS the pointer
+static inline cudaError_t cudaIpcOpenMemHandle(void ** p, cudaIpcMemHandle_t h, unsigned) { memcpy(p, &h, sizeof(*p)); return cudaSuccess; }
+static inline cudaError_t cudaIpcCloseMemHandle(void *) { return cudaSuccess; }
 template<typename K> static inline cudaError_t cudaOccupancyMaxActiveBlocksPerMultiprocessor(int * n, K, int, size_t) { *n = 1; return cudaSuccess; }
 
 // ------------------------------------------------------------------------------------- device side ---
@@ -115,6 +120,7 @@ static inline int   __float_as_int(float f) { int i; memcpy(&i, &f, 4); return i
 static inline float __int_as_float(int i) { float f; memcpy(&f, &i, 4); return f; }
 static inline int   __float2int_rn(float f) { return int(lrintf(f)); }   // callers keep the argument in range (rt_math.cuh: float_to_int)
 static inline void  __threadfence() {}
+static inline void  __threadfence_system() {}
 static inline void  __syncthreads() { emu::sync_threads(); }
 static inline void  __nanosleep(unsigned) { emu::yield(); }
 static inline long long clock64() { return emu::clock(); }
@@ -123,6 +129,8 @@ using std::min; using std::max;
 
 static inline void __syncwarp(unsigned mask = 0xffffffffu) { emu::warp_exchange(mask, 0, -1); }
 static inline unsigned emu_lane() { return (threadIdx.x + threadIdx.y * blockDim.x) & 31u; }
+static inline unsigned __ballot_sync(unsigned mask, bool predicate) { return emu::warp_exchange(mask, predicate ? 1u << emu_lane() : 0u, -2); }
+static inline int __ffs(unsigned v) { return __builtin_ffs(int(v)); }
 template<typename T> static inline T __shfl_sync(unsigned mask, T v, int lane) { unsigned bits; static_assert(sizeof(T) == 4, "32-bit shuffles only"); memcpy(&bits, &v, 4); bits = emu::warp_exchange(mask, bits, lane & 31); memcpy(&v, &bits, 4); return v; }
 template<typename T> static inline T __shfl_xor_sync(unsigned mask, T v, int lane_mask) { return __shfl_sync(mask, v, int(emu_lane()) ^ lane_mask); }
 template<typename T> static inline T __shfl_up_sync(unsigned mask, T v, unsigned delta) { const int lane = int(emu_lane()); return __shfl_sync(mask, v, lane >= int(delta) ? lane - int(delta) : lane); }

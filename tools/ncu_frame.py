@@ -6,9 +6,10 @@ REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(REPO, "cpu-raytracer_b200", "python")); sys.path.insert(0, REPO)
 import bench
 from b200rt.device import Renderer
-_, scene = bench.build_scene()
+w = bench.WORKLOADS[sys.argv[1] if len(sys.argv) > 1 else "sponza1080"]
+_, scene = bench.build_scene(w)
 pack = scene.pack()
-r = Renderer(bench.WIDTH, bench.HEIGHT, bench.BOUNCES, bench.FILTER)
+r = Renderer(w["width"], w["height"], w["bounces"], w["filter"])
 r.upload_static(pack)
 for _ in range(4):
     stats = r.render(pack)["stats"]

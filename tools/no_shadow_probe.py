@@ -22,7 +22,9 @@ def build(name):
     if name == "sibenik":
         s = HostScene(standin.sibenik_standin(width=3840, height=2160)); s.update(0.0, 0); return s, 3840, 2160, 3, "aniso"
     data = os.path.join(REPO, "oracle", "_ref", "Data")
-    builder, bounces, filt, frames = {"dynamic": (scenes.dynamic, 3, "aniso", 45), "dielectrics": (scenes.dielectrics_small, 8, "ewa", 0)}[name]
+    if name == "dielectrics":
+        s = HostScene(standin.dielectrics_hall(data, width=1920, height=1080)); s.update(0.0, 0); return s, 1920, 1080, 8, "ewa"
+    builder, bounces, filt, frames = {"dynamic": (scenes.dynamic, 3, "aniso", 45)}[name]
     s = HostScene(builder(data, os.path.join(tempfile.mkdtemp(), name + ".scene"), 1920, 1080))
     for _ in range(frames + 1):
         s.update(1.0 / 60.0 if frames else 0.0, 1 if frames else 0)

@@ -18,7 +18,7 @@ from b200rt.device import Renderer  # noqa: E402
 workload = sys.argv[1] if len(sys.argv) > 1 else "sponza"
 if workload == "sponza":
     _, scene = bench.build_scene()
-    w, h, filt = bench.WIDTH, bench.HEIGHT, "tri"
+    w, h, filt = 1920, 1080, "tri"
 else:
     from b200rt import standin
     from b200rt.host import HostScene
