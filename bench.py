@@ -745,7 +745,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="sponza1080", choices=sorted(WORKLOADS))
     ap.add_argument("--arithmetic", default="exact", choices=["exact", "fast"], help="b200rt_config.arithmetic; the headline is EXACT (bit-identical to the reference)")
-    ap.add_argument("--deep-queue", dest="deep_queue", default=None, choices=["off", "glass", "all"], help="b200rt_config.deep_queue (default: the library's shipped setting)")
+    ap.add_argument("--deep-queue", dest="deep_queue", default=None, choices=["off", "glass", "all", "auto"], help="b200rt_config.deep_queue (default: the library's shipped setting)")
     ap.add_argument("--no-scale-4k", dest="no_scale_4k", action="store_true", help="N > 1: skip the configs[4] sub-record")
     args = ap.parse_args()
     if args.warmup < 3:

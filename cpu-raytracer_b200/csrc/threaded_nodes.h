@@ -49,9 +49,10 @@ static inline const char * check_tree(const b200rt_bvh_node * nodes, int node_co
 // reference's (BVHNode::should_visit_left_first: the child on the ray's side of the split axis first), which depends
 // on the ray only through the signs of its direction: eight orders, eight copies
 // (octant = x > 0 | (y > 0) << 1 | (z > 0) << 2). Records are visited in the same sequence, and tested against the
-// same running t, as by the stack traversal. A leaf of more than 63 triangles is again a chain, but the records
-// after the first carry bit 31 of `leaf`: "no box test" — the reference tests the box once per leaf, and t may
-// have shrunk below the box's entry distance in between.
+// same running t, as by the stack traversal. A leaf of more than 63 triangles is again a chain, but the reference
+// tests the box ONCE per leaf: every record of the chain links past the whole chain (a miss on the first record skips
+// it all), bit 30 of `leaf` says "hit: the leaf goes on in the next record", and the records after the first carry bit
+// 31, "no box test" (t may have shrunk below the box's entry distance in between). 2^24 triangles per BLAS here.
 static inline const char * build_threaded_nodes(const b200rt_bvh_node * nodes, int node_count, std::vector<b200rt_bvh_node> & out, int octant = -1) {
 	const size_t base = out.size();
 	const unsigned order_mask = octant < 0 ? 0u : ((octant & 4) ? 9u : 0u) | ((octant & 1) ? 2u : 0u) | ((octant & 2) ? 4u : 0u); // traverse.cuh: direction_order_mask
@@ -106,11 +107,14 @@ static inline const char * build_threaded_nodes(const b200rt_bvh_node * nodes, i
 			out[base + size_t(first_record[i])] = r;
 		} else {
 			if (n.left_or_first < 0 || n.left_or_first >= (1 << 25)) return "BLAS too large for the shadow-ray layout (2^25 triangles per BLAS)";
+			if (octant >= 0 && n.left_or_first + count > (1 << 24)) return "BLAS too large for the octant-threaded layout (2^24 triangles per BLAS)";
 			for (int k = 0, done = 0; done < count; k++, done += 63) {
 				b200rt_bvh_node r = n;
 				const int part = std::min(63, count - done);
-				r.left_or_first = done + part < count ? first_record[i] + k + 1 : after;
+				const bool more = done + part < count;
+				r.left_or_first = more && octant < 0 ? first_record[i] + k + 1 : after;
 				r.count = ((n.left_or_first + done) << 6) | part;
+				if (octant >= 0 && more)  r.count |= 0x40000000;
 				if (octant >= 0 && k > 0) r.count |= int(0x80000000u);
 				out[base + size_t(first_record[i] + k)] = r;
 			}

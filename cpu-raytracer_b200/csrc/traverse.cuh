@@ -341,10 +341,11 @@ __device__ __forceinline__ void blas_trace_threaded(const float4 * __restrict__ 
 		const float4 n0 = load_node(records + 2 * index), n1 = load_node(records + 2 * index + 1);
 		int next = __float_as_int(n1.z);                       // skip link
 		if (next >= 0) prefetch_record(records + 2 * next);
-		const int leaf = __float_as_int(n1.w);                 // bit 31: continuation of a long leaf, no box test
+		const int leaf = __float_as_int(n1.w);                 // bit 31: continuation of a long leaf, no box test; bit 30: the leaf goes on in the next record
 		if (leaf < 0 || aabb_intersect(n0, n1, so, inv_d, best.t, exact)) {
 			if (leaf != 0) {
-				const int first = (leaf & 0x7FFFFFFF) >> 6, count = leaf & 63;
+				const int first = (leaf & 0x3FFFFFFF) >> 6, count = leaf & 63;
+				if (leaf & 0x40000000) next = index + 1;
 				for (int i = first; i < first + count; i++) {
 					float t, u, v;
 					if (triangle_test(hot + 3 * size_t(i), o, d, best.t, t, u, v)) {

@@ -83,8 +83,8 @@ class Outputs(C.Structure):
 
 
 ARITHMETIC = {"exact": 0, "fast": 1}
-DEEP_QUEUE = {"off": 0, "glass": 1, "all": 2}
-DEFAULT_DEEP_QUEUE = "off"
+DEEP_QUEUE = {"off": 0, "glass": 1, "all": 2, "auto": 3}
+DEFAULT_DEEP_QUEUE = "auto"   # the context times both walks on its own first frames and keeps the faster (b200rt.h)
 
 
 def make_config(width, height, bounces, mipmap_filter="aniso", max_anisotropy=8.0, enable_fxaa=True, device=0,

@@ -160,11 +160,14 @@ typedef struct {
 	int32_t arithmetic;
 	/* Deep-pixel ray queue: 0 = every pixel's ray tree is walked depth-first by one thread;
 	 * 1 = pixels whose primary ray hits a transmissive material hand their rays (closest-hit and shadow rays alike) to
-	 * device-side queues that all persistent warps pop; 2 = every pixel whose primary hit spawns rays does.
+	 * device-side queues that all persistent warps pop; 2 = every pixel whose primary hit spawns rays does;
+	 * 3 = AUTO: the context times both (setting 0 against setting 2 with the shadow rays kept in the producing thread)
+	 * on its own first frames from the kernels' %globaltimer stamps, keeps the faster and looks again every 512 frames.
 	 * Same image bit for bit in every setting: the node values are combined in the reference's order.               */
 	int32_t deep_queue;
 } b200rt_config;
 enum { B200RT_ARITHMETIC_EXACT = 0, B200RT_ARITHMETIC_FAST = 1 };
+enum { B200RT_QUEUE_OFF = 0, B200RT_QUEUE_GLASS = 1, B200RT_QUEUE_ALL = 2, B200RT_QUEUE_AUTO = 3 };
 enum { B200RT_TEXTURE_MIPMAP = 0,   /* TEXTURE_SAMPLE_MODE_MIPMAP: mipmap_filter on mip-mapped textures, bilinear on the others */
        B200RT_TEXTURE_BILINEAR = 1, /* TEXTURE_SAMPLE_MODE_BILINEAR: Texture::sample_bilinear on level 0, Texture.cpp:156-186   */
        B200RT_TEXTURE_NEAREST = 2 };/* TEXTURE_SAMPLE_MODE_NEAREST: Texture::sample_nearest, Texture.cpp:149-154              */

@@ -16,6 +16,9 @@
 //                             PREFIX.fNNNN.rgbf  float  [H][W][3] un-quantised colour
 //                             PREFIX.fNNNN.ids   int32  [H][W][2] (instance, triangle)   ORACLE_IDS
 //                             PREFIX.fNNNN.hit   float  [H][W][4] (distance, material id, u, v)   ORACLE_IDS
+// --bridge (B200RT_BRIDGE builds, "_bridge" variants): after the CPU has traced a frame, the SAME Scene object is handed
+//   to libb200rt.so through bridge/B200Bridge.h — the binding a maintainer of the reference would add — and the GPU's
+//   frame is dumped beside the CPU's:  PREFIX.fNNNN.gpu.u32 (Window::plot format), PREFIX.fNNNN.gpu.rgb8 (after FXAA).
 #include <chrono>
 #include <string>
 #include <vector>
@@ -31,7 +34,14 @@
 
 #include "SceneFile.h"
 
+#ifdef B200RT_BRIDGE
+#define private public   // Texture, Sky, Sphere, Plane: see the head of B200Bridge.h
+#endif
 #include "Scene.h"
+#ifdef B200RT_BRIDGE
+#undef private
+#include "B200Bridge.h"
+#endif
 
 // `Raytracer::bounce` is private (Raytracer.h:16-17). The per-ray mode below has to call it with a
 // ray of its own, so the access specifier is lifted for this one header — layout and code of the
@@ -185,6 +195,7 @@ int main(int argc, char ** argv) {
 	int   width = -1, height = -1;
 	bool  quiet = false;
 	bool  per_ray = false;
+	bool  bridge = false;
 	std::vector<int> dump_frames;
 
 	for (int a = 2; a < argc; a++) {
@@ -197,6 +208,7 @@ int main(int argc, char ** argv) {
 		else if (arg == "--height") height = atoi(next());
 		else if (arg == "--quiet")  quiet = true;
 		else if (arg == "--per-ray") per_ray = true;
+		else if (arg == "--bridge")  bridge = true;
 		else if (arg == "--dump") {
 			std::string list(next());
 			size_t pos = 0;
@@ -227,7 +239,17 @@ int main(int argc, char ** argv) {
 
 	WorkerThreads::init(raytracer, window);
 
-	std::vector<double> ms_total, ms_render;
+	std::vector<double> ms_total, ms_render, ms_bridge;
+#ifdef B200RT_BRIDGE
+	B200Bridge gpu;
+	std::vector<unsigned> gpu_frame_buffer(size_t(width) * height);
+	std::vector<unsigned char> gpu_presented(size_t(width) * height * 3);
+	b200rt_stats gpu_stats;
+	memset(&gpu_stats, 0, sizeof(gpu_stats));
+	if (bridge) gpu.init(*scene, width, height);
+#else
+	if (bridge) { fprintf(stderr, "--bridge needs a _bridge build\n"); return 2; }
+#endif
 	PerformanceStats last_stats = { 0, 0, 0, 0 };
 
 	for (int frame = 0; frame < frames; frame++) {
@@ -251,6 +273,14 @@ int main(int argc, char ** argv) {
 
 		last_stats = per_ray ? g_per_ray_stats : WorkerThreads::sum_performance_stats();
 
+#ifdef B200RT_BRIDGE
+		if (bridge) {   // the same Scene, after the same Scene::update: Main.cpp:56-59 on the GPU
+			auto b0 = std::chrono::steady_clock::now();
+			gpu.render(*scene, gpu_frame_buffer.data(), gpu_presented.data(), &gpu_stats);
+			ms_bridge.push_back(std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - b0).count());
+		}
+#endif
+
 		if (!out_prefix.empty() && std::find(dump_frames.begin(), dump_frames.end(), frame) != dump_frames.end()) {
 			char tag[32]; snprintf(tag, sizeof(tag), ".f%04d", frame);
 			std::string prefix = out_prefix + tag;
@@ -260,6 +290,12 @@ int main(int argc, char ** argv) {
 			dump_primary_hits(*scene, width, height, prefix);
 #endif
 			dump_frame_inputs(*scene, prefix);
+#ifdef B200RT_BRIDGE
+			if (bridge) {
+				write_file(prefix + ".gpu.u32",  gpu_frame_buffer.data(), gpu_frame_buffer.size() * sizeof(unsigned));
+				write_file(prefix + ".gpu.rgb8", gpu_presented.data(),    gpu_presented.size());
+			}
+#endif
 		}
 	}
 
@@ -272,7 +308,16 @@ int main(int argc, char ** argv) {
 		for (size_t i = 0; i < ms_total.size(); i++) printf("%s%.4f", i ? ", " : "", ms_total[i]);
 		printf("], \"ms_render\": [");
 		for (size_t i = 0; i < ms_render.size(); i++) printf("%s%.4f", i ? ", " : "", ms_render[i]);
-		printf("]}\n");
+		printf("]");
+#ifdef B200RT_BRIDGE
+		if (bridge) {
+			printf(", \"gpu_rays\": {\"primary\": %llu, \"shadow\": %llu, \"reflection\": %llu, \"refraction\": %llu}, \"ms_bridge\": [",
+				(unsigned long long) gpu_stats.primary_rays, (unsigned long long) gpu_stats.shadow_rays, (unsigned long long) gpu_stats.reflection_rays, (unsigned long long) gpu_stats.refraction_rays);
+			for (size_t i = 0; i < ms_bridge.size(); i++) printf("%s%.4f", i ? ", " : "", ms_bridge[i]);
+			printf("]");
+		}
+#endif
+		printf("}\n");
 	}
 	fflush(stdout);
 	_Exit(0); // skip static destructors: Scene is leaked, lights were placement-new'd

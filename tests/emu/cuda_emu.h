@@ -96,6 +96,7 @@ static inline cudaError_t cudaEventCreateWithFlags(cudaEvent_t * e, unsigned) { 
 static inline cudaError_t cudaEventDestroy(cudaEvent_t e) { delete e; return cudaSuccess; }
 static inline cudaError_t cudaEventRecord(cudaEvent_t e, cudaStream_t) { e->ms = emu::now_ms(); return cudaSuccess; }
 static inline cudaError_t cudaEventSynchronize(cudaEvent_t) { return cudaSuccess; }
+static inline cudaError_t cudaEventQuery(cudaEvent_t) { return cudaSuccess; }   // launches run to completion before they return
 static inline cudaError_t cudaEventElapsedTime(float * ms, cudaEvent_t a, cudaEvent_t b) { *ms = float(b->ms - a->ms); return cudaSuccess; }
 static inline cudaError_t cudaPointerGetAttributes(cudaPointerAttributes * a, const void * p) { a->type = emu::is_host_alloc(p) ? cudaMemoryTypeHost : cudaMemoryTypeUnregistered; return cudaSuccess; }
 struct cudaIpcMemHandle_t { char reserved[64]; };

@@ -78,3 +78,21 @@ def test_emulated_fast_arithmetic_stays_inside_north_stars_tolerance(emulated):
     out = render(emulated, g, arithmetic="fast")
     assert (out["ids"] == g.ref_ids).all(-1).mean() >= 0.999
     assert psnr(unpack_rgb(out["frame_buffer"]), unpack_rgb(g.ref_frame_buffer)) >= 50.0
+
+
+@pytest.mark.timeout(600)
+def test_emulated_auto_queue_times_both_walks_and_every_frame_matches(emulated):
+    """deep_queue = AUTO: warm-up frames depth-first, then alternating timed frames, then the faster walk — same bits throughout."""
+    g = Golden("monkey_b1_aniso")
+    m = g.meta
+    r = emulated(m["width"], m["height"], m["bounces"], m["filter"], deep_queue="auto")
+    r.upload_static(g.pack)
+    queued = []
+    for _ in range(10):
+        out = r.render(g.pack, want_presented=False)
+        assert np.array_equal(out["frame_buffer"], g.ref_frame_buffer)
+        assert rays(out["stats"]) == [int(x) for x in g.ref_rays]
+        queued.append(out["stats"]["queue_nodes"] > 0)
+    r.close()
+    assert queued[:8] == [False, False, False, True, False, True, False, True]     # AutoQueue::WARM = 2, PAIRS = 3
+    assert queued[8] == queued[9]                                                   # decided: no more alternation

@@ -13,6 +13,7 @@ deterministic "is this box hit" predicate:
 """
 import ctypes as C
 import os
+import zlib
 import subprocess
 
 import numpy as np
@@ -86,7 +87,7 @@ def predicate(seed):
     """Deterministic stand-in for AABB::intersect: a function of the box bytes only, so both walks agree on it."""
     if seed is None:
         return lambda key: True
-    return lambda key: (hash((seed, key)) & 3) != 0
+    return lambda key: (zlib.crc32(key, seed) & 3) != 0        # not hash(): that one differs from process to process
 
 
 def stack_walk(nodes, hit, left_first):
@@ -109,8 +110,8 @@ def stack_walk(nodes, hit, left_first):
     return events
 
 
-def threaded_walk(records, hit):
-    """traverse.cuh: blas_shadow / blas_trace_threaded, in Python."""
+def threaded_walk(records, hit, octant_copy=False):
+    """traverse.cuh: blas_shadow / (octant_copy) blas_trace_threaded, in Python."""
     events, index, steps = [], 0, 0
     while index >= 0:
         r = records[index]
@@ -122,8 +123,10 @@ def threaded_walk(records, hit):
             ok = hit(key)
         if ok:
             if leaf != 0:
-                first, count = (leaf & 0x7FFFFFFF) >> 6, leaf & 63
+                first, count = (leaf & (0x3FFFFFFF if octant_copy else 0x7FFFFFFF)) >> 6, leaf & 63
                 events += [("tri", i) for i in range(first, first + count)]
+                if octant_copy and leaf & 0x40000000:
+                    nxt = index + 1
             else:
                 nxt = index + 1
         index = nxt
@@ -153,9 +156,9 @@ def test_octant_copies_replay_the_stack_traversal(harness):
         for octant in range(8):
             n, records = harness(nodes, octant)
             assert n > 0, name
-            for seed in (None, 1, 2):
+            for seed in (None, 1, 2, 3, 4, 5, 6):
                 want = stack_walk(nodes, predicate(seed), octant_left_first(octant))
-                got = threaded_walk(records, predicate(seed))
+                got = threaded_walk(records, predicate(seed), octant_copy=True)
                 assert got == want, (name, octant, seed)
 
 
@@ -163,7 +166,7 @@ def test_naive_order_is_octant_seven(harness):
     """BVH_TRAVERSE_TREE_NAIVE: the left child first at every node."""
     for name, nodes in trees():
         _, records = harness(nodes, 7)
-        assert threaded_walk(records, predicate(3)) == stack_walk(nodes, predicate(3), lambda count: True), name
+        assert threaded_walk(records, predicate(3), octant_copy=True) == stack_walk(nodes, predicate(3), lambda count: True), name
 
 
 def test_shadow_copy_reaches_the_same_triangles(harness):
@@ -193,10 +196,15 @@ def test_long_leaves_are_chained(harness):
     assert continued.any()
     leaf = records["count"] != 0
     assert ((records["count"][leaf] & 63) >= 1).all()
-    # a continuation record carries its leaf's box and follows the record it continues
+    # a continuation record carries its leaf's box and follows the record it continues, which says "goes on" (bit 30);
+    # every record of a chain links past the whole chain: a missed box skips all of it
     for i in np.flatnonzero(continued):
-        assert records[i - 1]["count"] != 0 and records[i - 1]["left_or_first"] == i
+        assert records[i - 1]["count"] != 0 and records[i - 1]["count"] & 0x40000000
+        assert records[i - 1]["left_or_first"] == records[i]["left_or_first"] and (records[i]["left_or_first"] == -1 or records[i]["left_or_first"] > i)
         assert box_key(records[i]) == box_key(records[i - 1])
+    _, shadow = harness(nodes, -1)                     # the any-hit copy: plain links from record to record, no flags
+    chained = [i for i in range(len(shadow) - 1) if shadow[i]["count"] != 0 and box_key(shadow[i]) == box_key(shadow[i + 1])]
+    assert chained and all(shadow[i]["left_or_first"] == i + 1 for i in chained)
 
 
 def test_broken_trees_are_refused(harness):
