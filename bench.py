@@ -235,32 +235,31 @@ def run_reference_arm(args, w):
 
 
 # ------------------------------------------------------------------------------------ GPU arm ---
-def ncu_figures(workload):
+def ncu_figures(workload, queued=False):
     """What ncu measured for the render kernel of this workload (profiles/ncu_render_kernel.json: one entry per workload,
-    each naming the capture it comes from). Instruction and byte counts of a launch do not depend on the box."""
+    each naming the capture it comes from; "<workload>/queued" = the frame went through the deep-pixel queue, i.e.
+    render_queue_kernel ran). Instruction and byte counts of a launch do not depend on the box."""
     try:
         with open(os.path.join(REPO, "profiles", "ncu_render_kernel.json")) as f:
             data = json.load(f)
     except (OSError, ValueError):
         return {}
-    entry = data.get("workloads", {}).get(workload)
-    if entry is None and data.get("workload") == workload:
-        entry = data
-    return entry or {}
+    return data.get("workloads", {}).get(workload + "/queued" if queued else workload) or {}
 
 
-def roofline_record(workload, kernel_ms, alg_bytes, rays, clocks, own_walk=None):
+def roofline_record(workload, kernel_ms, alg_bytes, rays, clocks, own_walk=None, queued=False):
     """The judged fraction is ISSUE: lane-instructions issued against what the SMs can issue (<= 1 by construction)."""
     if not kernel_ms:
         return None
-    ncu = ncu_figures(workload)
+    ncu = ncu_figures(workload, queued)
     peak_hbm, peak_source = load_peaks()
     seconds = kernel_ms * 1e-3
     sm_hz = (clocks.get("sm_mhz") or 1965.0) * 1e6
     issue_peak = 148 * 4 * 32 * sm_hz
     thread_instructions = ncu.get("thread_instructions_per_launch")
     record = {
-        "bound": "issue", "kernel": ncu.get("kernel", "render_kernel"), "kernel_ms": kernel_ms,
+        "bound": "issue", "kernel": ncu.get("kernel", "render_queue_kernel" if queued else "render_kernel"), "kernel_ms": kernel_ms,
+        "deep_pixel_queue": bool(queued),
         "achieved": None if not thread_instructions else thread_instructions / seconds / 1e12, "peak": issue_peak / 1e12, "unit": "T lane-instructions/s",
         "frac": None if not thread_instructions else thread_instructions / seconds / issue_peak,
         "peak_source": "148 SMs x 4 schedulers x 32 lanes x SM clock sampled during the timed region (%.0f MHz)" % (sm_hz / 1e6),
@@ -276,7 +275,8 @@ def roofline_record(workload, kernel_ms, alg_bytes, rays, clocks, own_walk=None)
         "hbm_peak_gbs": peak_hbm, "hbm_peak_source": peak_source,
         "hbm_frac_of_algorithmic_stream": alg_bytes / seconds / 1e9 / peak_hbm,
         "hbm_frac_of_dram_traffic": None if not ncu.get("dram_bytes_per_launch") else ncu["dram_bytes_per_launch"] / seconds / 1e9 / peak_hbm,
-        "l1_hit_pct": ncu.get("l1_hit_pct"), "l2_hit_pct": ncu.get("l2_hit_pct"),
+        "l1_hit_pct": ncu.get("l1_hit_pct"), "l2_hit_pct": ncu.get("l2_hit_pct"), "l1_throughput_pct": ncu.get("l1_throughput_pct"),
+        "local_ld_st_warp_instructions": ncu.get("local_ld_st_warp_instructions"), "global_ld_warp_instructions": ncu.get("global_ld_warp_instructions"),
         "ncu_source": ncu.get("source"),
         "shipped_walk": own_walk,
         "note": "SURVEY 8(d)'s algorithmic stream (BVH nodes + triangles, ~2 KB per ray, counted on the reference's visiting order) is served by L1 and L2 (the working set fits the 126 MB L2): "
@@ -338,7 +338,8 @@ def run_gpu_arm(args, w):
         with clocks:
             ms_render, ms_fxaa = renderer.time_resident(steps, L2_FLUSH_BYTES)
         barrier()
-        tail_ms = renderer.render(pack)["stats"]["device_ms_tail"]
+        last_stats = renderer.render(pack)["stats"]
+        tail_ms, queued = last_stats["device_ms_tail"], last_stats["queue_nodes"] > 0
         warm_render, warm_fxaa = renderer.time_resident(steps, 0)
 
         # ---- e2e: the frame loop a user writes — Scene::update on the host, then the frame through the public
@@ -396,7 +397,7 @@ def run_gpu_arm(args, w):
             scene.update(0.0, 0)
         renderer.close()
         return {"ms_render": ms_render, "ms_fxaa": ms_fxaa, "ms_step": ms_render + ms_fxaa, "warm": (warm_render, warm_fxaa), "tail_ms": tail_ms,
-                "e2e_ms": e2e_ms, "e2e_sync_ms": e2e_sync_ms, "h2d": pack.frame_bytes(), "d2h": pixels * 7, "launches": 3 * steps, "moving_camera": moving,
+                "queued": queued, "e2e_ms": e2e_ms, "e2e_sync_ms": e2e_sync_ms, "h2d": pack.frame_bytes(), "d2h": pixels * 7, "launches": 3 * steps, "moving_camera": moving,
                 "e2e_api": "Scene::update + b200rt_submit_frame/b200rt_wait_frame (two frames in flight)"}
 
     def measure_n_gpus(wl, scene, pack, steps, warmup):
@@ -490,7 +491,7 @@ def run_gpu_arm(args, w):
         dist.all_reduce(verdict, op=dist.ReduceOp.MIN)
         gather_verified = bool(verdict.item())
 
-        for _ in range(max(warmup, 3)):
+        for _ in range(max(warmup, 12)):                   # also carries deep_queue = AUTO through its comparison frames (8 + what is in flight)
             step()
         barrier()
         with clocks:
@@ -509,7 +510,8 @@ def run_gpu_arm(args, w):
                 end.record(stream)
                 torch.cuda.synchronize()
                 total += start.elapsed_time(end)
-                kernel_ms[0] += renderer.last_frame_stats()["device_ms_render"] / steps   # the render kernel's own %globaltimer span
+                last_stats = renderer.last_frame_stats()
+                kernel_ms[0] += last_stats["device_ms_render"] / steps   # the render kernel's own %globaltimer span
                 if peers is not None:
                     for k in range(3):
                         phase_ms[k] += phase_events[k].elapsed_time(phase_events[k + 1]) / steps
@@ -658,7 +660,7 @@ def run_gpu_arm(args, w):
             barrier()
             peers.close()
         renderer.close()
-        return {"ms_render": slowest_kernel_ms, "ms_fxaa": None, "ms_step": ms_step, "warm": None, "tail_ms": None,
+        return {"ms_render": slowest_kernel_ms, "ms_fxaa": None, "ms_step": ms_step, "warm": None, "tail_ms": None, "queued": last_stats["queue_nodes"] > 0,
                 "e2e_ms": e2e_ms, "e2e_sync_ms": None, "h2d": pack.frame_bytes() * world,      # every rank uploads the frame block
                 "d2h": pixels * 7 + (8 * world if peers is not None else 0),                   # whole job: the bands add up to both images (+ the arrival stamps)
                 "launches": (5 if peers is not None else 3) * steps,                           # per rank and frame: render, barrier, fxaa, barrier, tile_schedule (the NCCL path: render, tile_schedule, fxaa on rank 0)
@@ -680,7 +682,7 @@ def run_gpu_arm(args, w):
             own_walk = {"nodes_visited": s["nodes_visited"], "triangles_tested": s["triangles_tested"],
                         "reference_order": {"nodes_visited": full_stats["nodes_visited"], "triangles_tested": full_stats["triangles_tested"]},
                         "what": "shadow rays on the threaded copy, right child first (the walk that is timed) vs the reference's front-to-back order (the walk the algorithmic bytes are counted on); closest-hit rays are the same in both"}
-        roofline = roofline_record(name, m["ms_render"], algorithmic_bytes(full_stats, pixels), rays, clk, own_walk)
+        roofline = roofline_record(name, m["ms_render"], algorithmic_bytes(full_stats, pixels), rays, clk, own_walk, queued=bool(m.get("queued")))
         if roofline is not None and world > 1:
             roofline["kernel_ms_source"] = "the slowest rank's render kernel, timed by the kernel itself (%globaltimer, first block started .. last warp done); instruction and byte counts are the whole frame's (single-GPU capture), so achieved figures are per-job"
         line = {

@@ -67,8 +67,10 @@ struct b200rt_ctx {
 	// after the frame that used it, when its copy to the host (at most two frames are in flight) is long done
 	unsigned frame_number = 0;
 	// deep-pixel queue (render.cuh): pools, allocated on first use
-	DeviceBuffer q_nodes, q_bounce, q_shadow, q_bounce_ready, q_shadow_ready;
-	int queue_inline_below = 0, queue_defer_shadows = 1;
+	DeviceBuffer q_nodes, q_bounce, q_bounce_ready;
+	int queue_inline_below = 0;
+	bool queue_stalled = false;           // the queue kernel's watchdog fired once: this context renders depth-first from then on
+	bool test_stall = false;              // B200RT_TEST_QUEUE_STALL (tests): the first queued frame is marked as given up, to exercise the recovery
 	int blas_stack_entries = 1;
 	DeviceBuffer tile_cost, tile_order; // schedule of the render kernel (kernels.cuh: tile_schedule_kernel)
 	int tile_count_mine = 0;
@@ -113,7 +115,6 @@ struct b200rt_ctx {
 		int   issued = -1;          // candidate of the frame being issued if it is one of the timed ones (launch_render -> launch_schedule)
 		struct Probe { cudaEvent_t copied = nullptr; int candidate = -1; } probes[SLOTS];
 		unsigned long long * stamps = nullptr;   // pinned, SLOTS x { first_idle_ns, last_done_ns, first_start_ns }
-		int   defer_shadows = 0;    // the queued candidate keeps shadow rays in the producing thread (measured: 5.53 against 6.36 ms on configs[3])
 	} auto_queue;
 };
 
@@ -172,7 +173,7 @@ extern "C" int b200rt_create(const b200rt_config * config, b200rt_ctx ** out) {
 	ctx->kernels = &kernels_exact();
 #endif
 	if (const char * text = getenv("B200RT_QUEUE_INLINE_BELOW")) ctx->queue_inline_below = atoi(text);   // tuning knobs (tools/): see SceneParams
-	if (const char * text = getenv("B200RT_QUEUE_DEFER_SHADOWS")) ctx->queue_defer_shadows = ctx->auto_queue.defer_shadows = atoi(text) != 0;
+	if (const char * text = getenv("B200RT_TEST_QUEUE_STALL")) ctx->test_stall = atoi(text) != 0;
 
 	auto bail = [&](const char * what, cudaError_t err) { g_create_error = std::string(what) + ": " + cudaGetErrorString(err); b200rt_destroy(ctx); return -1; };
 
@@ -238,7 +239,7 @@ extern "C" void b200rt_destroy(b200rt_ctx * ctx) {
 	if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
 	for (DeviceBuffer * b : { &ctx->nodes, &ctx->shadow_nodes, &ctx->hot, &ctx->cold, &ctx->materials, &ctx->textures, &ctx->texels, &ctx->sky, &ctx->gamma,
 	                          &ctx->frame_block[0], &ctx->frame_block[1], &ctx->frame_buffer, &ctx->presented, &ctx->colour_float, &ctx->ids, &ctx->hits, &ctx->counters, &ctx->l2_scratch, &ctx->tile_cost, &ctx->tile_order,
-	                          &ctx->q_nodes, &ctx->q_bounce, &ctx->q_shadow, &ctx->q_bounce_ready, &ctx->q_shadow_ready, &ctx->wide_nodes, &ctx->hot_fast, &ctx->texels_half }) b->release();
+	                          &ctx->q_nodes, &ctx->q_bounce, &ctx->q_bounce_ready, &ctx->wide_nodes, &ctx->hot_fast, &ctx->texels_half }) b->release();
 	for (auto & slot : ctx->slots) {
 		slot.frame_buffer.release(); slot.presented.release();
 		if (slot.pinned_counters) cudaFreeHost(slot.pinned_counters);
@@ -610,21 +611,18 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 // A pool that runs out costs nothing but speed: the producer walks that subtree depth-first (FrameCounters::q_fallbacks).
 static int ensure_queue(b200rt_ctx * ctx, SceneParams & P) {
 	const size_t pixels = size_t(std::max(ctx->tile_count_mine, 1)) * 1024;
-	size_t nodes = std::min<size_t>(4 * pixels, (size_t(1) << 26) - 1), bounce = 8 * pixels, shadow = 8 * pixels;
-	if (const char * text = getenv("B200RT_QUEUE_CAPACITY")) nodes = bounce = shadow = size_t(std::max(atoi(text), 32));   // tests: small pools force the fall-back paths
+	size_t nodes = std::min<size_t>(4 * pixels, (size_t(1) << 26) - 1), bounce = 2 * nodes;   // two child slots per record
+	if (const char * text = getenv("B200RT_QUEUE_CAPACITY")) nodes = bounce = size_t(std::max(atoi(text), 32));   // tests: small pools force the fall-back paths
 	if (!ctx->q_nodes.ptr) {
 		CHECK_CUDA(ctx, ctx->q_nodes.ensure(nodes * 6 * sizeof(float4)));
 		CHECK_CUDA(ctx, ctx->q_bounce.ensure(bounce * 5 * sizeof(float4)));
-		CHECK_CUDA(ctx, ctx->q_shadow.ensure(shadow * 2 * sizeof(float4)));
 		CHECK_CUDA(ctx, ctx->q_bounce_ready.ensure(bounce * sizeof(unsigned)));
-		CHECK_CUDA(ctx, ctx->q_shadow_ready.ensure(shadow * sizeof(unsigned)));
 		// "ready" means "holds this launch's serial number": the arrays must not start with a previous owner's
 		CHECK_CUDA(ctx, cudaMemset(ctx->q_bounce_ready.ptr, 0, bounce * sizeof(unsigned)));
-		CHECK_CUDA(ctx, cudaMemset(ctx->q_shadow_ready.ptr, 0, shadow * sizeof(unsigned)));
 	}
-	P.q_nodes = static_cast<float4 *>(ctx->q_nodes.ptr); P.q_bounce = static_cast<float4 *>(ctx->q_bounce.ptr); P.q_shadow = static_cast<float4 *>(ctx->q_shadow.ptr);
-	P.q_bounce_ready = static_cast<unsigned *>(ctx->q_bounce_ready.ptr); P.q_shadow_ready = static_cast<unsigned *>(ctx->q_shadow_ready.ptr);
-	P.q_node_capacity = unsigned(nodes); P.q_bounce_capacity = unsigned(bounce); P.q_shadow_capacity = unsigned(shadow);
+	P.q_nodes = static_cast<float4 *>(ctx->q_nodes.ptr); P.q_bounce = static_cast<float4 *>(ctx->q_bounce.ptr);
+	P.q_bounce_ready = static_cast<unsigned *>(ctx->q_bounce_ready.ptr);
+	P.q_node_capacity = unsigned(nodes); P.q_bounce_capacity = unsigned(bounce);
 	return 0;
 }
 
@@ -661,12 +659,11 @@ static int launch_render(b200rt_ctx * ctx, unsigned * frame_buffer, float * colo
 	SceneParams P = ctx->params;
 	if (!banded) P.band_count = 0;
 	P.blas_stack_entries = ctx->blas_stack_entries;
-	P.queue_mode = (count || P.light_count > 24 || P.bounces == 0) ? 0 : ctx->config.deep_queue;   // RT_QUEUE_MAX_LIGHTS: a node record keeps one bit per light
-	P.queue_inline_below = ctx->queue_inline_below; P.queue_defer_shadows = ctx->queue_defer_shadows;
+	P.queue_mode = (count || P.bounces == 0 || ctx->queue_stalled) ? 0 : ctx->config.deep_queue;
+	P.queue_inline_below = ctx->queue_inline_below;
 	ctx->auto_queue.issued = -1;
 	if (P.queue_mode == B200RT_QUEUE_AUTO) {
 		P.queue_mode = auto_queue_candidate(ctx) ? B200RT_QUEUE_ALL : B200RT_QUEUE_OFF;
-		P.queue_defer_shadows = ctx->auto_queue.defer_shadows;
 	}
 	if (P.queue_mode != 0) {
 		if (ensure_queue(ctx, P)) return -1;
@@ -683,6 +680,10 @@ static int launch_render(b200rt_ctx * ctx, unsigned * frame_buffer, float * colo
 	const unsigned needed = (total_warps + 7) / 8;   // 8 warps per 256-thread block
 	if (blocks > needed) blocks = needed;
 	CHECK_CUDA(ctx, ctx->kernels->render(P, frame_buffer, colour_float, counter_block(ctx, ctx->frame_number), count ? 1 : 0, blocks, ctx->stream));
+	if (ctx->test_stall && P.queue_mode != 0) { // as if the watchdog had fired in this launch
+		ctx->test_stall = false;
+		CHECK_CUDA(ctx, cudaMemsetAsync(&counter_block(ctx, ctx->frame_number)->q_abort, 1, sizeof(unsigned), ctx->stream));
+	}
 	return 0;
 }
 
@@ -718,13 +719,23 @@ static int launch_fxaa(b200rt_ctx * ctx, const unsigned * frame_buffer, unsigned
 	return 0;
 }
 
+// The queue kernel's watchdog (kernels.cuh: RT_QUEUE_WATCHDOG_NS) gave the frame up: its image is incomplete. The
+// context renders depth-first from then on; a synchronous entry point renders the frame again, an asynchronous one
+// reports the frame as failed.
+static bool queue_stalled(b200rt_ctx * ctx, const FrameCounters & c) {
+	if (c.q_abort == 0 || ctx->queue_stalled) return false;
+	ctx->queue_stalled = true;
+	fprintf(stderr, "b200rt: the deep-pixel queue made no progress for %.1f s; this context renders depth-first from now on\n", double(RT_QUEUE_WATCHDOG_NS) * 1e-9);
+	return true;
+}
+
 static void counters_to_stats(const FrameCounters & c, b200rt_stats * stats) {
 	stats->primary_rays = c.primary; stats->shadow_rays = c.shadow; stats->reflection_rays = c.reflection; stats->refraction_rays = c.refraction;
 	stats->nodes_visited = c.nodes; stats->triangles_tested = c.triangles; stats->texels_fetched = c.texels;
 	stats->hits_accepted = c.accepted; stats->instances_entered = c.instances;
 	stats->device_ms_render = stats->device_ms_fxaa = stats->device_ms_total = 0.0f;
 	stats->device_ms_tail = (c.first_idle_ns != 0 && c.last_done_ns > ~c.first_idle_ns) ? float(double(c.last_done_ns - ~c.first_idle_ns) * 1e-6) : 0.0f;
-	stats->queue_nodes = c.q_node_reserved; stats->queue_bounce_items = c.q_bounce_reserved; stats->queue_shadow_items = c.q_shadow_reserved; stats->queue_fallbacks = c.q_fallbacks;
+	stats->queue_nodes = c.q_node_reserved; stats->queue_bounce_items = c.q_bounce_reserved; stats->queue_shadow_items = 0; stats->queue_fallbacks = c.q_fallbacks;
 }
 
 static void fill_stats(b200rt_ctx * ctx, b200rt_stats * stats) {
@@ -754,6 +765,7 @@ extern "C" int b200rt_render_frame(b200rt_ctx * ctx, const b200rt_frame * frame,
 	if (stage_frame(ctx, frame)) return -1;
 
 	unsigned * fb = static_cast<unsigned *>(ctx->frame_buffer.ptr);
+	render_again:   // (only after the queue kernel's watchdog fired: the same frame once more, depth-first)
 	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
 	if (launch_render(ctx, fb, out->colour_float ? static_cast<float *>(ctx->colour_float.ptr) : nullptr, ctx->config.count_traversal != 0)) return -1;
 	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
@@ -781,6 +793,7 @@ extern "C" int b200rt_render_frame(b200rt_ctx * ctx, const b200rt_frame * frame,
 	CHECK_CUDA(ctx, cudaEventRecord(ctx->ev[4], ctx->stream));
 	cudaError_t sync = cudaStreamSynchronize(ctx->stream);
 	if (sync != cudaSuccess) { ctx->error = std::string("render failed: ") + cudaGetErrorString(sync); return -1; }
+	if (queue_stalled(ctx, *ctx->pinned_counters)) goto render_again;
 
 	if (out->frame_buffer   && !direct_fb)  memcpy(out->frame_buffer,   pinned + off_fb,  pixels * 4);
 	if (out->presented_rgb8 && !direct_rgb) memcpy(out->presented_rgb8, pinned + off_rgb, pixels * 3);
@@ -808,6 +821,7 @@ extern "C" int b200rt_render_frame_device(b200rt_ctx * ctx, const b200rt_frame *
 	if (!stats) return 0; // asynchronous: the caller orders later work on the context's stream
 	CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->pinned_counters, counted, sizeof(FrameCounters), cudaMemcpyDeviceToHost, ctx->stream));
 	CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	if (queue_stalled(ctx, *ctx->pinned_counters)) return b200rt_render_frame_device(ctx, frame, frame_buffer_dev, stats);
 	fill_stats(ctx, stats); cudaEventElapsedTime(&stats->device_ms_total, ctx->ev[0], ctx->ev[3]);
 	return 0;
 }
@@ -820,6 +834,7 @@ extern "C" int b200rt_last_frame_stats(b200rt_ctx * ctx, b200rt_stats * stats) {
 	CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 	CHECK_CUDA(ctx, cudaMemcpy(ctx->pinned_counters, counter_block(ctx, ctx->frame_number - 1), sizeof(FrameCounters), cudaMemcpyDeviceToHost));
 	const FrameCounters & c = *ctx->pinned_counters;
+	if (queue_stalled(ctx, c)) return fail(ctx, "the deep-pixel queue stalled in the last frame: its image is incomplete; render it again (the context has switched to the depth-first walk)");
 	counters_to_stats(c, stats);
 	if (c.first_start_ns != 0 && c.last_done_ns > ~c.first_start_ns) stats->device_ms_render = float(double(c.last_done_ns - ~c.first_start_ns) * 1e-6);
 	stats->device_ms_total = stats->device_ms_render;
@@ -1025,6 +1040,7 @@ extern "C" int b200rt_wait_frame(b200rt_ctx * ctx, b200rt_stats * stats) {
 	slot.busy = false;
 	ctx->waited++;
 	if (e != cudaSuccess) { ctx->error = std::string("frame failed: ") + cudaGetErrorString(e); return -1; }
+	if (queue_stalled(ctx, *slot.pinned_counters)) return fail(ctx, "the deep-pixel queue stalled in this frame: its image is incomplete; submit it again (the context has switched to the depth-first walk)");
 	if (stats) {
 		const FrameCounters & c = *slot.pinned_counters;
 		counters_to_stats(c, stats);

@@ -104,19 +104,29 @@ __device__ __forceinline__ void warp_add(int * counter, int n) {
 }
 
 // The same frame with the deep-pixel queue (render.cuh). Every ray — a pixel's primary ray or an item popped from the
-// bounce queue — is the same depth-first walk (shade_subtree_body<QUEUE>), whose top node may be exported to the
-// queues; shadow items are any-hit queries. A warp works on ONE kind at a time, in this order of preference: bounce
-// items (the deep pixels' rays are the frame's critical path), shadow items, tile units.
+// bounce queue — is the same depth-first walk (shade_subtree_body<QUEUE>), whose top node may be exported to the queue.
+// A warp works on ONE kind at a time: bounce items first (the deep pixels' rays are the frame's critical path), then
+// tile units.
 //
 // Items are claimed by TICKET: one atomicAdd on the queue's head hands a warp the next n slots — it never fails and is
 // never retried. (The first version claimed with compare-and-swap on the head: with thousands of warps contending, one
 // wins per L2 round trip and the frame's million items went through at ~20 per microsecond — 150 ms instead of 1;
 // profiles/r02_variants_call1.jsonl, r02_variants_call2.jsonl.) A ticket may name a slot that is not published yet, or
 // never will be: a lane keeps its ticket across iterations until the slot's ready word shows this frame's serial
-// number, and meanwhile the warp takes whatever else there is; tickets die when the frame's count of outstanding work
-// (tile units + items not finished) reaches zero. Tickets are only drawn against items seen in the queue, so few are
-// ever early. A warp with no ticket that finds nothing looks three more times (2 / 4 / 8 us apart) and leaves: whoever
-// publishes an item looks at the queues again right afterwards, so nothing is orphaned, and no warp polls for long.
+// number, and meanwhile the warp takes tile units; tickets die when the frame's count of outstanding work (tile units +
+// items not finished) reaches zero. A warp with no ticket that finds nothing looks three more times (2 / 4 / 8 us
+// apart) and leaves: whoever publishes an item looks at the queue again right afterwards, so nothing is orphaned, and no
+// warp polls for long.
+//
+// Why this cannot stall. Slots are handed out in order, so the tickets in flight always cover [published .. head): an
+// item published below the head has a holder — a warp never leaves while a lane holds a ticket, and looks at its
+// tickets' ready words on every turn —, an item at or above the head is drawn by its own publisher at the latest, whose
+// next turn starts with a look at the queue. There is ONE queue: the first version of this kernel had a second one for
+// shadow rays, and a warp that held early tickets of one queue never looked at the other — with every other warp gone,
+// items of the other queue stayed unclaimed and the launch never ended (one run in a few hundred on SCENE_DYNAMIC);
+// shadow rays are traced by the thread that shades the node, which was the faster setting anyway (5.5 against 6.9 ms on
+// configs[3]). As a last line of defence a warp that has waited on its tickets for RT_QUEUE_WATCHDOG_NS raises
+// FrameCounters::q_abort, every warp leaves, and the host renders the frame again depth-first (b200rt.cu).
 template<int MAXB, int BSTACK>
 __global__ void __launch_bounds__(RT_BLOCK_THREADS, RT_MIN_BLOCKS)
 render_queue_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, float * __restrict__ colour_float, FrameCounters * counters) {
@@ -124,7 +134,7 @@ render_queue_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, f
 	const unsigned lanes_below = (1u << lane) - 1u;
 	const unsigned total_units = unsigned(P.tile_count_mine) * 32u;
 	const PixelOut out = { frame_buffer, colour_float };
-	enum { WORK_NONE = 0, WORK_UNIT = 1, WORK_BOUNCE = 2, WORK_SHADOW = 3, WORK_WAIT = 4 };
+	enum { WORK_NONE = 0, WORK_UNIT = 1, WORK_BOUNCE = 2, WORK_WAIT = 4, WORK_VOID = 5 };
 	const unsigned NO_TICKET = 0xffffffffu;
 
 	Counters cnt = { 0, 0, 0, 0, 0, 0, 0, 0 };
@@ -132,7 +142,7 @@ render_queue_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, f
 	int idle_looks = 0;
 	bool units_left = total_units > 0;   // this warp's view; once false it stays false (the cursor only grows)
 	unsigned ticket = NO_TICKET;         // this lane's claimed slot that is not published yet
-	int ticket_kind = WORK_NONE;         // warp-uniform: which queue the warp's tickets belong to
+	unsigned long long waiting_since = 0ull;   // lane 0: when the warp began to wait on tickets with nothing else to do
 
 	if (threadIdx.x == 0) atomicMax(&counters->first_start_ns, ~global_timer_ns());
 
@@ -143,20 +153,17 @@ render_queue_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, f
 		if (lane == 0) {
 			const unsigned free_lanes = 32u - unsigned(__popc(holding));
 			const unsigned hb = peek(&counters->q_bounce_head), rb = min(peek(&counters->q_bounce_reserved), P.q_bounce_capacity), ab = rb > hb ? rb - hb : 0u;
-			const unsigned hs = peek(&counters->q_shadow_head), rs = min(peek(&counters->q_shadow_reserved), P.q_shadow_capacity), as = rs > hs ? rs - hs : 0u;
-			if (holding) kind = ticket_kind;
-			else if (ab >= 32u || (ab > 0u && !units_left && as < 32u)) kind = WORK_BOUNCE;
-			else if (as >= 32u || (as > 0u && !units_left)) kind = WORK_SHADOW;
+			if (peek(&counters->q_abort) != 0u) kind = WORK_VOID;
+			else if (holding || ab >= 32u || (ab > 0u && !units_left)) kind = WORK_BOUNCE;
 			if (kind == WORK_BOUNCE && ab > 0u && free_lanes > 0u) { n = min(ab, free_lanes); first = atomicAdd(&counters->q_bounce_head, n); }
-			if (kind == WORK_SHADOW && as > 0u && free_lanes > 0u) { n = min(as, free_lanes); first = atomicAdd(&counters->q_shadow_head, n); }
 			if (kind == WORK_NONE && units_left) {
 				first = atomicAdd(&counters->next_unit, 1u);
 				if (first < total_units) kind = WORK_UNIT; else units_left = false;
 			}
-			if (kind == WORK_NONE && (units_left || ab > 0u || as > 0u || (idle_looks < 3 && peek(&counters->q_outstanding) > 0))) kind = WORK_WAIT;
+			if (kind == WORK_NONE && (units_left || ab > 0u || (idle_looks < 3 && peek(&counters->q_outstanding) > 0))) kind = WORK_WAIT;
 		}
 		kind = __shfl_sync(0xffffffffu, kind, 0); first = __shfl_sync(0xffffffffu, first, 0); n = __shfl_sync(0xffffffffu, n, 0);
-		if (kind == WORK_NONE) break;
+		if (kind == WORK_NONE || kind == WORK_VOID) break;
 		if (kind == WORK_WAIT) {
 			if (lane == 0 && idle_looks == 0) atomicMax(&counters->first_idle_ns, ~global_timer_ns());
 			__nanosleep(2000u << min(idle_looks, 2));
@@ -166,45 +173,38 @@ render_queue_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, f
 
 		// ---- items: new tickets go to the lanes that hold none; whose slot is published? --------------------
 		bool active = false;
-		if (kind == WORK_BOUNCE || kind == WORK_SHADOW) {
-			ticket_kind = kind;
+		if (kind == WORK_BOUNCE) {
 			const unsigned rank = unsigned(__popc(~holding & lanes_below));
 			if (ticket == NO_TICKET && rank < n) ticket = first + rank;
-			const unsigned capacity = kind == WORK_BOUNCE ? P.q_bounce_capacity : P.q_shadow_capacity;
-			const unsigned * ready = kind == WORK_BOUNCE ? P.q_bounce_ready : P.q_shadow_ready;
-			if (ticket != NO_TICKET && ticket >= capacity) ticket = NO_TICKET;   // beyond the pool: that item was never queued
+			if (ticket != NO_TICKET && ticket >= P.q_bounce_capacity) ticket = NO_TICKET;   // beyond the pool: that item was never queued
 			if (ticket != NO_TICKET) {
-				for (int look = 0; look < 3 && !active; look++) active = __ldcg(ready + ticket) == P.frame_serial;   // reserved a moment before it is written
+				for (int look = 0; look < 3 && !active; look++) active = __ldcg(P.q_bounce_ready + ticket) == P.frame_serial;   // reserved a moment before it is written
 				if (active) __threadfence();
 			}
 			if (__ballot_sync(0xffffffffu, active) == 0u) { // nothing published yet: the tickets wait, the warp does something else
 				kind = WORK_NONE;
 				if (lane == 0) {
-					if (peek(&counters->q_outstanding) <= 0) kind = WORK_BOUNCE;   // the frame is done: the tickets are void (handled below)
+					if (peek(&counters->q_outstanding) <= 0) kind = WORK_VOID;   // the frame is done: the tickets are void
 					else if (units_left) {
 						first = atomicAdd(&counters->next_unit, 1u);
 						if (first < total_units) kind = WORK_UNIT; else units_left = false;
 					}
+					if (kind == WORK_NONE) { // nothing but waiting: for how long already?
+						const unsigned long long now = global_timer_ns();
+						if (waiting_since == 0ull) waiting_since = now;
+						else if (now - waiting_since > RT_QUEUE_WATCHDOG_NS) { atomicOr(&counters->q_abort, 1u); kind = WORK_VOID; }
+					}
 				}
 				kind = __shfl_sync(0xffffffffu, kind, 0); first = __shfl_sync(0xffffffffu, first, 0);
-				if (kind == WORK_BOUNCE) { ticket = NO_TICKET; ticket_kind = WORK_NONE; continue; }
+				if (kind == WORK_VOID) { ticket = NO_TICKET; continue; }
 				if (kind == WORK_NONE) { __nanosleep(500); continue; }
 			}
 		}
 		idle_looks = 0;
+		waiting_since = 0ull;
 
-		int settled = 0;   // items (or the tile unit) this lane finishes: comes off the frame's outstanding work
-		if (kind == WORK_SHADOW) {
-			if (active) {
-				const float4 a = __ldcg(P.q_shadow + 2 * size_t(ticket)), b = __ldcg(P.q_shadow + 2 * size_t(ticket) + 1);
-				ticket = NO_TICKET;
-				const int word = as_i(b.w);
-				if (word != QUEUE_NULL_ITEM) {
-					deliver_shadow(P, out, word >> 5, word & 31, trace_any_call<BSTACK>(P, V(a), V(b), a.w, cnt));
-					settled = 1;
-				}
-			}
-		} else { // a walk: a pixel's (WORK_UNIT) or a popped bounce item's
+		int settled = 0;   // the item (or the tile unit) this lane finishes: comes off the frame's outstanding work
+		{ // a walk: a pixel's (WORK_UNIT) or a popped bounce item's
 			const long long unit_begin = clock64();
 			Ray ray; int bounces_left = 0, local_tile = 0;
 			QueueContext q = { counters, 0, 0 };

@@ -185,58 +185,39 @@ __device__ __forceinline__ v3 refraction_blend(const SceneParams & P, int materi
 }
 
 // ------------------------------------------------------------------------------ deep-pixel queue ---
-// North_star's "wavefront traversal with ray compaction", restricted to where it pays. A pixel whose primary ray hits
-// glass is not walked by one thread: the top node of a walk can be EXPORTED — it becomes a node record in HBM, its
-// reflection / refraction rays become items of the bounce queue and its shadow rays items of the shadow queue, which
-// all persistent warps pop (kernels.cuh): a warp holds rays of ONE kind at a time (the compaction), the shadow rays
-// leave the pixel's critical chain (which rays are spawned never depends on a shadow ray's answer), and the sibling
-// subtrees of a fan-out run side by side on whatever warps are free. Every popped ray is again a walk whose top node
-// may be exported, so a deep tree unfolds level by level. A node's value is assembled when the last of its shadow
-// rays and children has reported (a countdown in the record), by the reporting thread, with the reference's sums in
-// the reference's order: the same bits as the recursive form.
+// North_star's "wavefront traversal with ray compaction", restricted to where it pays. A deep pixel is not walked by
+// one thread: the top node of a walk can be EXPORTED — it becomes a node record in HBM and its reflection / refraction
+// rays become items of the bounce queue, which all persistent warps pop (kernels.cuh), so the sibling subtrees of a
+// fan-out run side by side on whatever warps are free. Every popped ray is again a walk whose top node may be
+// exported, so a deep tree unfolds level by level. A node's value is assembled when the last of its children has
+// reported (a countdown in the record), by the reporting thread, with the reference's sums in the reference's order:
+// the same bits as the recursive form. Shadow rays stay with the thread that shades the node (a second queue for them
+// was built and measured: slower, and two queues can starve each other — kernels.cuh).
 //
 //   node record  6 x float4   {parent, flags | which << 8, pending, material id} {point, distance} {normal, F_r}
-//                             {albedo (or the finished direct lighting: NODE_LIT), occluded-light bits}
+//                             {the node's direct lighting, -}
 //                             {reflection child's colour, -} {refraction child's colour, its distance}
 //   bounce item  5 x float4   the Ray (18 floats), parent node, which | bounces_left << 1     (parent = QUEUE_NULL_ITEM: skip)
-//   shadow item  2 x float4   {origin, max distance} {direction, node << 5 | light}           (word = QUEUE_NULL_ITEM: skip)
 // An item is visible to consumers once its word in the queue's `ready` array holds the frame's serial number (written
 // after a __threadfence()). Records and items are bump-allocated per frame; when a pool is exhausted the node is not
 // exported and its subtree is walked by the thread that holds it: always correct, never blocked. Records and items
 // are read and written with .cg accesses (L2 only): another SM's L1 may hold a stale copy of the line.
-#define RT_QUEUE_MAX_LIGHTS 24
 #define QUEUE_NULL_ITEM int(0x80000000u)
-enum { NODE_LIT = 64 };   // with the FRAME_* bits in a record's flags: the albedo slot already holds the direct lighting
 
 __device__ __forceinline__ float as_f(int v) { return __int_as_float(v); }
 __device__ __forceinline__ int   as_i(float v) { return __float_as_int(v); }
 __device__ __forceinline__ unsigned peek(const unsigned * p) { return *reinterpret_cast<const volatile unsigned *>(p); }   // a fresh value, not this SM's L1 copy
 __device__ __forceinline__ int      peek(const int * p)      { return *reinterpret_cast<const volatile int *>(p); }
 
-// Value of a node whose shadow rays and children have all reported (the record is complete and no longer written).
+// Value of a node whose children have all reported (the record is complete and no longer written).
 __device__ __forceinline__ v3 node_value(const SceneParams & P, const float4 * rec, float & distance_out, int & parent, int & which) {
 	const float4 r0 = __ldcg(rec), r1 = __ldcg(rec + 1), r2 = __ldcg(rec + 2), r3 = __ldcg(rec + 3);
 	parent = as_i(r0.x);
 	const int flags = as_i(r0.y) & 0xff; which = (as_i(r0.y) >> 8) & 1;
 	const int material_id = as_i(r0.w);
-	const v3 point = V(r1), normal = V(r2), material_diffuse = V(r3);
-	const unsigned occluded = unsigned(as_i(r3.w));
 	distance_out = r1.w;
 
-	v3 result = V(0.0f, 0.0f, 0.0f);
-	if (flags & NODE_LIT) {
-		result = material_diffuse;
-	} else if (dot(material_diffuse, material_diffuse) > 0.0f) {
-		v3 diffuse = V(P.ambient[0], P.ambient[1], P.ambient[2]);
-		const v3 to_camera = normalize(V(P.cam_position[0], P.cam_position[1], P.cam_position[2]) - point);
-		for (int i = 0; i < P.light_count; i++) {
-			if ((occluded >> i) & 1u) continue;
-			LightSample s;
-			light_sample(P, i, point, s);
-			diffuse = light_add(diffuse, s, normal, to_camera);
-		}
-		result = lit_result(diffuse, material_diffuse);
-	}
+	v3 result = V(r3);   // the direct lighting, finished by the thread that exported the node
 	v3 colour_reflection = V(0.0f, 0.0f, 0.0f);
 	if (flags & FRAME_HAS_REFLECTION) {
 		const float4 m1 = __ldg(reinterpret_cast<const float4 *>(P.materials + material_id) + 1);
@@ -268,17 +249,6 @@ __device__ __noinline__ void deliver(const SceneParams & P, const PixelOut & out
 		value = node_value(P, rec, distance, parent, which);
 	}
 }
-__device__ __forceinline__ void deliver_shadow(const SceneParams & P, const PixelOut & out, int node, int light, bool occluded) {
-	float4 * rec = P.q_nodes + 6 * size_t(node);
-	if (occluded) atomicOr(reinterpret_cast<unsigned *>(rec) + 15, 1u << light);
-	__threadfence();
-	if (atomicSub(reinterpret_cast<int *>(rec) + 2, 1) != 1) return;
-	__threadfence();
-	float distance; int parent, which;
-	const v3 value = node_value(P, rec, distance, parent, which);
-	deliver(P, out, parent, which, value, distance);
-}
-
 __device__ __forceinline__ void write_bounce_item(const SceneParams & P, unsigned slot, const Ray & r, int parent, int which, int bounces_left) {
 	float4 * item = P.q_bounce + 5 * size_t(slot);
 	__stcg(item,     make_float4(r.origin.x, r.origin.y, r.origin.z, r.direction.x));
@@ -314,37 +284,32 @@ __device__ __forceinline__ unsigned group_reserve(unsigned * counter, unsigned p
 #endif
 }
 
-// Exports the top node of a walk: record, children and (deferred) shadow rays. Returns false when a pool is exhausted
-// (nothing has been published then, and the caller goes on walking). result: the node's finished direct lighting when
-// its shadow rays were traced in line (n_shadow == 0 and lit), else the albedo.
-__device__ __forceinline__ bool export_node(const SceneParams & P, const QueueContext & q, const HitRecord & hit, float distance, int flags, float F_r, v3 albedo_or_result, bool result_is_final,
-                                            const Ray & reflected, const Ray & refracted, int bounces_left, int n_shadow, Counters & cnt) {
+// Exports the top node of a walk: record and children. Returns false when a pool is exhausted (nothing has been
+// published then, and the caller goes on walking). result: the node's finished direct lighting.
+__device__ __forceinline__ bool export_node(const SceneParams & P, const QueueContext & q, const HitRecord & hit, float distance, int flags, float F_r, v3 result,
+                                            const Ray & reflected, const Ray & refracted, int bounces_left, Counters & cnt) {
 	const bool has_child[2] = { (flags & FRAME_HAS_REFLECTION) != 0, (flags & FRAME_HAS_REFRACTION) && !(flags & FRAME_TIR) };
 	const int n_children = (has_child[0] ? 1 : 0) + (has_child[1] ? 1 : 0);
-	// every exporting lane takes one record, two bounce slots and light_count shadow slots: fixed sizes keep the
-	// reservation one atomicAdd per group; a slot that stays unused is published as a null item
+	// every exporting lane takes one record and two bounce slots: fixed sizes keep the reservation one atomicAdd per
+	// group; a slot that stays unused is published as a null item
 	const unsigned node_slot = group_reserve(&q.counters->q_node_reserved, 1u);
 	if (node_slot >= P.q_node_capacity) { atomicAdd(&q.counters->q_fallbacks, 1u); return false; }
 	const unsigned bounce_slot = group_reserve(&q.counters->q_bounce_reserved, 2u);
-	const unsigned shadow_slot = n_shadow > 0 ? group_reserve(&q.counters->q_shadow_reserved, unsigned(P.light_count)) : 0u;
-	const bool fits = bounce_slot + 2u <= P.q_bounce_capacity && (n_shadow == 0 || shadow_slot + unsigned(P.light_count) <= P.q_shadow_capacity);
-	if (!fits) { // slots inside the pool must still be published (somebody may have claimed them): as null items
+	if (bounce_slot + 2u > P.q_bounce_capacity) { // slots inside the pool must still be published (somebody may have claimed them): as null items
 		for (unsigned k = 0; k < 2u; k++) if (bounce_slot + k < P.q_bounce_capacity) __stcg(P.q_bounce + 5 * size_t(bounce_slot + k) + 4, make_float4(0.0f, 0.0f, as_f(QUEUE_NULL_ITEM), 0.0f));
-		for (int i = 0; i < n_shadow; i++) if (shadow_slot + i < P.q_shadow_capacity) __stcg(P.q_shadow + 2 * size_t(shadow_slot + i) + 1, make_float4(0.0f, 0.0f, 0.0f, as_f(QUEUE_NULL_ITEM)));
 		__threadfence();
 		for (unsigned k = 0; k < 2u; k++) if (bounce_slot + k < P.q_bounce_capacity) __stcg(P.q_bounce_ready + bounce_slot + k, P.frame_serial);
-		for (int i = 0; i < n_shadow; i++) if (shadow_slot + i < P.q_shadow_capacity) __stcg(P.q_shadow_ready + shadow_slot + i, P.frame_serial);
 		atomicAdd(&q.counters->q_fallbacks, 1u);
 		return false;
 	}
-	atomicAdd(&q.counters->q_outstanding, n_children + n_shadow);   // before anything is visible: the count never runs low
+	atomicAdd(&q.counters->q_outstanding, n_children);   // before anything is visible: the count never runs low
 
 	const int node = int(node_slot);
 	float4 * rec = P.q_nodes + 6 * size_t(node);
-	__stcg(rec,     make_float4(as_f(q.parent), as_f(flags | (result_is_final ? NODE_LIT : 0) | (q.which << 8)), as_f(n_children + n_shadow), as_f(hit.material_id)));
+	__stcg(rec,     make_float4(as_f(q.parent), as_f(flags | (q.which << 8)), as_f(n_children), as_f(hit.material_id)));
 	__stcg(rec + 1, make_float4(hit.point.x, hit.point.y, hit.point.z, distance));
 	__stcg(rec + 2, make_float4(hit.normal.x, hit.normal.y, hit.normal.z, F_r));
-	__stcg(rec + 3, make_float4(albedo_or_result.x, albedo_or_result.y, albedo_or_result.z, as_f(0)));
+	__stcg(rec + 3, make_float4(result.x, result.y, result.z, 0.0f));
 	// payloads, ONE fence, then the ready words: record and items are in L2 before any consumer can see an item that names the record
 	for (int k = 0; k < 2; k++) {
 		if (has_child[k]) {
@@ -354,17 +319,8 @@ __device__ __forceinline__ bool export_node(const SceneParams & P, const QueueCo
 			__stcg(P.q_bounce + 5 * size_t(bounce_slot + k) + 4, make_float4(0.0f, 0.0f, as_f(QUEUE_NULL_ITEM), 0.0f));
 		}
 	}
-	for (int i = 0; i < n_shadow; i++) { // shadow rays (:155-198)
-		LightSample s;
-		light_sample(P, i, hit.point, s);
-		cnt.shadow++;
-		float4 * item = P.q_shadow + 2 * size_t(shadow_slot + i);
-		__stcg(item,     make_float4(hit.point.x, hit.point.y, hit.point.z, s.distance));
-		__stcg(item + 1, make_float4(s.to_light.x, s.to_light.y, s.to_light.z, as_f((node << 5) | i)));
-	}
 	__threadfence();
 	for (unsigned k = 0; k < 2u; k++) __stcg(P.q_bounce_ready + bounce_slot + k, P.frame_serial);
-	for (int i = 0; i < n_shadow; i++) __stcg(P.q_shadow_ready + shadow_slot + i, P.frame_serial);
 	return true;
 }
 
@@ -415,7 +371,7 @@ __device__ __forceinline__ v3 shade_subtree_body(const SceneParams & P, Ray ray,
 			const v3 material_diffuse = get_albedo<COUNT>(P, __ldg(mp), hit, cnt);
 			const bool lit = dot(material_diffuse, material_diffuse) > 0.0f;
 
-			// QUEUE: may this node be exported? Then its shadow rays are not traced here but queued with it.
+			// QUEUE: may this node be exported?
 			bool may_export = false;
 			if (QUEUE && top && bounces_left > 0) {
 				const float4 m1 = __ldg(mp + 1), m2 = __ldg(mp + 2);
@@ -423,11 +379,9 @@ __device__ __forceinline__ v3 shade_subtree_body(const SceneParams & P, Ray ray,
 				may_export = q->parent >= 0 ? (bounces_left > P.queue_inline_below && (reflects || refracts))
 				                            : (P.queue_mode == 2 ? (reflects || refracts) : refracts);
 			}
-			const bool defer_shadows = QUEUE && may_export && lit && P.light_count > 0 && P.queue_defer_shadows;
-
 			v3 result = V(0.0f, 0.0f, 0.0f);
 
-			if (lit && !defer_shadows) { // :143-201
+			if (lit) { // :143-201
 				v3 diffuse = V(P.ambient[0], P.ambient[1], P.ambient[2]);
 				const v3 to_camera = normalize(V(P.cam_position[0], P.cam_position[1], P.cam_position[2]) - hit.point);
 
@@ -472,29 +426,11 @@ __device__ __forceinline__ v3 shade_subtree_body(const SceneParams & P, Ray ray,
 
 					if (QUEUE && may_export) {
 						const int node_flags = flags | (reflection_mask ? FRAME_HAS_REFLECTION : 0);
-						const int n_shadow = defer_shadows ? P.light_count : 0;
 						const bool any_child = reflection_mask || ((flags & FRAME_HAS_REFRACTION) && !(flags & FRAME_TIR));
-						if (any_child || n_shadow > 0) {
-							const bool final_result = !defer_shadows;   // the lighting above is the node's (0 when the surface is not lit)
-							if (export_node(P, *q, hit, best.t, node_flags, frame.F_r, final_result ? result : material_diffuse, final_result, reflected, frame.refracted, bounces_left, n_shadow, cnt)) {
-								exported = true;
-								distance_out = best.t;
-								return result;
-							}
-						}
-						if (defer_shadows) { // not exported after all (a pool ran out, or nothing to wait for): the lighting that was put off
-							v3 diffuse = V(P.ambient[0], P.ambient[1], P.ambient[2]);
-							const v3 to_camera = normalize(V(P.cam_position[0], P.cam_position[1], P.cam_position[2]) - hit.point);
-							for (int i = 0; i < P.light_count; i++) {
-								LightSample s;
-								light_sample(P, i, hit.point, s);
-								cnt.shadow++;
-								if (trace_any_call<BSTACK>(P, hit.point, s.to_light, s.distance, cnt)) continue;
-								diffuse = light_add(diffuse, s, hit.normal, to_camera);
-							}
-							result = lit_result(diffuse, material_diffuse);
-							frame.result = result;
-							returned = result;
+						if (any_child && export_node(P, *q, hit, best.t, node_flags, frame.F_r, result, reflected, frame.refracted, bounces_left, cnt)) {
+							exported = true;
+							distance_out = best.t;
+							return result;
 						}
 					}
 

@@ -95,16 +95,15 @@ struct SceneParams {
 	// deep-pixel queue (render.cuh): pools in HBM, bump-allocated per frame through FrameCounters::q_*
 	float4   * q_nodes;          // 6 float4 per node record
 	float4   * q_bounce;         // 5 float4 per bounce item
-	float4   * q_shadow;         // 2 float4 per shadow item
 	unsigned * q_bounce_ready;   // item i is readable once ready[i] == frame_serial
-	unsigned * q_shadow_ready;
-	unsigned q_node_capacity, q_bounce_capacity, q_shadow_capacity;
+	unsigned q_node_capacity, q_bounce_capacity;
 	unsigned frame_serial;       // never 0, different for every launch of a context
 	int queue_mode;              // 0 off; 1: pixels whose primary ray hits a transmissive material; 2: every pixel whose primary hit spawns rays
 	int queue_inline_below;      // a popped ray with at most this many bounces left is walked to the end by the thread that popped it
-	int queue_defer_shadows;     // an exported node's shadow rays are queued with it (1) or traced before the export (0)
 	int blas_stack_entries;      // deepest BLAS + 1: what a push-both-pop-one traversal can hold
 };
+
+#define RT_QUEUE_WATCHDOG_NS 2000000000ull   // kernels.cuh: render_queue_kernel gives a frame up after waiting this long on unpublished items
 
 struct FrameCounters {   // accumulated with one atomicAdd per warp
 	unsigned long long primary, shadow, reflection, refraction;
@@ -115,8 +114,8 @@ struct FrameCounters {   // accumulated with one atomicAdd per warp
 	unsigned long long first_start_ns, pad2[3];     // globaltimer when the first block started (stored as ~t)
 	// deep-pixel queue (render.cuh). Producers' cursors, consumers' heads and the count of outstanding work (tile units
 	// + items not finished) each on a 128-byte line of their own: they are hit by different warps at the same time
-	unsigned int q_node_reserved, q_bounce_reserved, q_shadow_reserved, q_fallbacks, q_pad0[28];
-	unsigned int q_bounce_head, q_shadow_head, q_pad1[30];
+	unsigned int q_node_reserved, q_bounce_reserved, q_unused0, q_fallbacks, q_pad0[28];
+	unsigned int q_bounce_head, q_abort, q_pad1[30];   // q_abort: the queue kernel's watchdog fired (kernels.cuh), the frame is incomplete
 	int q_outstanding; unsigned int q_pad2[31];
 };
 static_assert(sizeof(FrameCounters) == 512, "four 128-byte lines");

@@ -523,11 +523,4 @@ __device__ __forceinline__ bool trace_any(const SceneParams & P, v3 o, v3 d, flo
 	return false;
 }
 
-// One out-of-line copy of the shipped any-hit query, for the places that are not hot (the deep-pixel queue's shadow
-// items and its fall-back lighting): a third inlined copy of the traversal would cost the hot loop instruction cache.
-template<int BSTACK>
-__device__ __noinline__ bool trace_any_call(const SceneParams & P, v3 o, v3 d, float max_distance, Counters & cnt) {
-	return trace_any<false, BSTACK>(P, o, d, max_distance, cnt);
-}
-
 } // namespace RT_NAMESPACE

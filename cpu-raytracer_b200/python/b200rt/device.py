@@ -17,6 +17,21 @@ class DeviceError(RuntimeError):
     pass
 
 
+class _PinnedBlock:
+    """Page-locked host memory (b200rt_host_alloc) that lives as long as anything refers to it: the numpy arrays of
+    alloc_outputs() keep their block alive through their base object, so closing the renderer cannot pull it away."""
+
+    def __init__(self, lib, nbytes):
+        self._lib, self.ptr = lib, C.c_void_p()
+        if lib.b200rt_host_alloc(nbytes, C.byref(self.ptr)) != 0:
+            raise DeviceError(lib.b200rt_last_error(None).decode())
+
+    def __del__(self):
+        if self.ptr:
+            self._lib.b200rt_host_free(self.ptr)
+            self.ptr = C.c_void_p()
+
+
 class Renderer:
     def __init__(self, width, height, bounces, mipmap_filter="aniso", max_anisotropy=8.0, enable_fxaa=True, device=0,
                  tile_stride=1, tile_phase=0, count_traversal=False, traversal="ordered", texture_mode="mipmap",
@@ -29,15 +44,11 @@ class Renderer:
             raise DeviceError(self._lib.b200rt_last_error(None).decode())
         self.width, self.height = width, height
         self._keep = None
-        self._pinned = []
 
     def close(self):
         if self._h:
             self._lib.b200rt_destroy(self._h)
-            self._h = C.c_void_p()
-            for p in self._pinned:     # arrays handed out by alloc_outputs() die with the renderer
-                self._lib.b200rt_host_free(p)
-            self._pinned = []
+            self._h = C.c_void_p()       # (page-locked arrays of alloc_outputs() own their memory: _PinnedBlock)
 
     def __del__(self):
         try:
@@ -64,11 +75,9 @@ class Renderer:
         res = {}
         for name, shape, dtype in (("frame_buffer", (h, w), np.uint32), ("presented", (h, w, 3), np.uint8)):
             nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
-            p = C.c_void_p()
-            if self._lib.b200rt_host_alloc(nbytes, C.byref(p)) != 0:
-                raise DeviceError(self._lib.b200rt_last_error(None).decode())
-            self._pinned.append(p)
-            buf = (C.c_uint8 * nbytes).from_address(p.value)
+            block = _PinnedBlock(self._lib, nbytes)
+            buf = (C.c_uint8 * nbytes).from_address(block.ptr.value)
+            buf._block = block             # numpy array -> ctypes buffer -> block: freed when the last view goes
             res[name] = np.frombuffer(buf, dtype=dtype).reshape(shape)
         return res
 

@@ -159,9 +159,9 @@ typedef struct {
 	 * not bit-identical — the reference's own release build is of that kind (/fp:fast, Raytracer.vcxproj).            */
 	int32_t arithmetic;
 	/* Deep-pixel ray queue: 0 = every pixel's ray tree is walked depth-first by one thread;
-	 * 1 = pixels whose primary ray hits a transmissive material hand their rays (closest-hit and shadow rays alike) to
-	 * device-side queues that all persistent warps pop; 2 = every pixel whose primary hit spawns rays does;
-	 * 3 = AUTO: the context times both (setting 0 against setting 2 with the shadow rays kept in the producing thread)
+	 * 1 = pixels whose primary ray hits a transmissive material hand their reflection and refraction rays to a
+	 * device-side queue that all persistent warps pop; 2 = every pixel whose primary hit spawns rays does;
+	 * 3 = AUTO: the context times both (setting 0 against setting 2)
 	 * on its own first frames from the kernels' %globaltimer stamps, keeps the faster and looks again every 512 frames.
 	 * Same image bit for bit in every setting: the node values are combined in the reference's order.               */
 	int32_t deep_queue;
@@ -188,8 +188,10 @@ typedef struct {
 	float    device_ms_total;      /* uploads + kernels + downloads on the context's stream
 	                                * (= device_ms_render from b200rt_wait_frame)                         */
 	float    device_ms_tail;       /* part of device_ms_render during which some warps had already run out of work */
-	/* deep-pixel queue (config.deep_queue != 0): node records, bounce-ray and shadow-ray items of the frame, and how
-	 * many of them found their pool exhausted and were walked depth-first instead (correct either way)            */
+	/* deep-pixel queue (config.deep_queue != 0): node records and bounce-ray items of the frame, and how many nodes
+	 * found a pool exhausted and were walked depth-first instead (correct either way). queue_shadow_items is 0:
+	 * shadow rays are traced by the thread that shades the node (a second queue for them was built, measured
+	 * slower and removed; the field keeps the struct's layout)                                                     */
 	uint32_t queue_nodes, queue_bounce_items, queue_shadow_items, queue_fallbacks;
 } b200rt_stats;
 

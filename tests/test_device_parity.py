@@ -10,7 +10,7 @@ differences come from transcendentals (acosf/atan2f/expf/log2f of CUDA vs glibc,
 import numpy as np
 import pytest
 
-from conftest import psnr, unpack_rgb
+from conftest import Golden, psnr, unpack_rgb
 
 pytestmark = pytest.mark.gpu
 
@@ -170,4 +170,31 @@ def test_pipelined_animation_frames_match_the_reference():
             diff = np.abs(unpack_rgb(out["frame_buffer"]) - unpack_rgb(g.ref_frame_buffer))
             assert (diff.max(-1) > 0).mean() <= 2e-3 and diff.max() <= 8
     del outs
+    r.close()
+
+
+@pytest.mark.gpu
+def test_a_frame_the_queue_gave_up_is_rendered_again_depth_first(monkeypatch):
+    """FrameCounters::q_abort (the queue kernel's watchdog) marks a frame as incomplete: b200rt_render_frame renders it
+    again depth-first, the asynchronous entry points report it, and the context stays depth-first afterwards."""
+    from b200rt.device import DeviceError, Renderer
+    monkeypatch.setenv("B200RT_TEST_QUEUE_STALL", "1")      # the first queued frame of a context is marked as given up
+    g = Golden("dielectrics_b8_ewa")
+    m = g.meta
+    r = Renderer(m["width"], m["height"], m["bounces"], m["filter"], deep_queue="all")
+    r.upload_static(g.pack)
+    first = r.render(g.pack, want_presented=False)
+    second = r.render(g.pack, want_presented=False)
+    r.close()
+    assert np.array_equal(first["frame_buffer"], second["frame_buffer"])
+    assert first["stats"]["queue_nodes"] == 0 and second["stats"]["queue_nodes"] == 0
+    r = Renderer(m["width"], m["height"], m["bounces"], m["filter"], deep_queue="all")
+    r.upload_static(g.pack)
+    outs = r.alloc_outputs()
+    r.submit(g.pack, outs)
+    with pytest.raises(DeviceError, match="stalled"):
+        r.wait()
+    r.submit(g.pack, outs)                                   # again, as the message says
+    assert r.wait()["queue_nodes"] == 0
+    assert np.array_equal(outs["frame_buffer"], first["frame_buffer"])
     r.close()

@@ -96,3 +96,21 @@ def test_emulated_auto_queue_times_both_walks_and_every_frame_matches(emulated):
     r.close()
     assert queued[:8] == [False, False, False, True, False, True, False, True]     # AutoQueue::WARM = 2, PAIRS = 3
     assert queued[8] == queued[9]                                                   # decided: no more alternation
+
+
+@pytest.mark.timeout(300)
+def test_emulated_queue_that_gave_a_frame_up_is_rendered_again_depth_first(emulated, monkeypatch):
+    """The queue kernel's watchdog (FrameCounters::q_abort) marks a frame as incomplete: b200rt_render_frame renders it again
+    depth-first and the context stays depth-first. B200RT_TEST_QUEUE_STALL marks the first queued frame that way."""
+    monkeypatch.setenv("B200RT_TEST_QUEUE_STALL", "1")
+    g = Golden("monkey_b1_aniso")
+    m = g.meta
+    r = emulated(m["width"], m["height"], m["bounces"], m["filter"], deep_queue="all")
+    r.upload_static(g.pack)
+    first = r.render(g.pack, want_presented=False)
+    second = r.render(g.pack, want_presented=False)
+    r.close()
+    for out in (first, second):
+        assert np.array_equal(out["frame_buffer"], g.ref_frame_buffer)
+        assert out["stats"]["queue_nodes"] == 0            # the frame that counts was walked depth-first
+        assert rays(out["stats"]) == [int(x) for x in g.ref_rays]

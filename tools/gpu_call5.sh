@@ -1,5 +1,6 @@
 #!/bin/bash
 # Round 2, fifth GPU call: the whole gpu suite (full-size rows incl. stock / queue / FAST, the reference through the bridge),
+# (Historical: as run. The defer= / B200RT_QUEUE_DEFER_SHADOWS settings it names belonged to the shadow-ray queue, which was removed afterwards.)
 # queue settings side by side, the bench lines, then — only after those exited — the ncu launch list and full captures.
 cd "$(dirname "$0")/.."
 O=gpurun_out

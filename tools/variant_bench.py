@@ -2,7 +2,7 @@
 """Times kernel variants / run-time settings of libb200rt.so side by side (development tool).
 
     python tools/variant_bench.py SPEC [SPEC ...]
-    SPEC = label[,lib=path/to/libb200rt_x.so][,queue=off|glass|all|auto][,defer=0|1][,arith=exact|fast][,inline=N]
+    SPEC = label[,lib=path/to/libb200rt_x.so][,queue=off|glass|all|auto][,arith=exact|fast][,inline=N]
 
 Each SPEC runs in its own process (B200RT_LIB / B200RT_DEEP_QUEUE / B200RT_ARITHMETIC / B200RT_QUEUE_INLINE_BELOW
 select library and settings). First the golden fixtures are rendered and compared with the real reference's stored
@@ -116,8 +116,6 @@ def main():
                 env["B200RT_ARITHMETIC"] = value
             elif key == "inline":
                 env["B200RT_QUEUE_INLINE_BELOW"] = value
-            elif key == "defer":
-                env["B200RT_QUEUE_DEFER_SHADOWS"] = value
             else:
                 raise SystemExit("bad SPEC item " + item)
         try:
