@@ -5,6 +5,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -945,6 +946,65 @@ extern "C" int b200rt_barrier(b200rt_ctx * ctx) {
 	if (ctx->barrier_count == 0) return fail(ctx, "b200rt_barrier_setup has not been called");
 	CHECK_CUDA(ctx, cudaSetDevice(ctx->config.device));
 	CHECK_CUDA(ctx, ctx->kernels->barrier(ctx->barrier_blocks, ctx->barrier_count, ctx->barrier_rank, ++ctx->barrier_epoch, ctx->stream));
+	return 0;
+}
+
+// ------------------------------------------------------------- the entry point that allocates nothing ---
+// Scratch of b200rt_render_resident_noalloc: one FrameCounters block (the unit counter the persistent warps pull work
+// from, the ray counters, the kernel's time stamps) followed by the per-tile cost words the kernel adds to. File scope,
+// fixed size: every GPU that loads the library holds these 64.5 KB until the process exits. Shared by every call in
+// the process — the entry point clears it on the stream before each launch; calls that overlap on one GPU race.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[sizeof(FrameCounters) + size_t(B200RT_NOALLOC_MAX_TILES) * sizeof(unsigned)];
+
+// In host code `g_noalloc_scratch` is only a handle for the runtime, not a device address: the address is asked for
+// once per device, with that device current, and kept.
+static int noalloc_scratch_address(b200rt_ctx * ctx, unsigned char ** out) {
+	enum { MAX_DEVICES = 64 };
+	static std::mutex lock;
+	static unsigned char * address[MAX_DEVICES] = {};
+	const int device = ctx->config.device;
+	if (device < 0 || device >= MAX_DEVICES) return fail(ctx, "device ordinal beyond the no-alloc table");
+	std::lock_guard<std::mutex> guard(lock);
+	if (!address[device]) {
+		void * p = nullptr;
+		CHECK_CUDA(ctx, cudaGetSymbolAddress(&p, g_noalloc_scratch));
+		if (!p) return fail(ctx, "cudaGetSymbolAddress returned no address");
+		address[device] = static_cast<unsigned char *>(p);
+	}
+	*out = address[device];
+	return 0;
+}
+
+extern "C" int b200rt_render_resident_noalloc(b200rt_ctx * ctx, uint64_t frame_buffer_dev) {
+	if (!ctx) return -1;
+	if (!frame_buffer_dev) return fail(ctx, "null device frame buffer");
+	if (ctx->tile_count_mine > B200RT_NOALLOC_MAX_TILES)
+		return fail(ctx, "b200rt_render_resident_noalloc: this context renders " + std::to_string(ctx->tile_count_mine) + " tiles, the static scratch holds B200RT_NOALLOC_MAX_TILES = " + std::to_string(int(B200RT_NOALLOC_MAX_TILES)));
+	if (!ctx->have_frame) return fail(ctx, "no frame is resident: render one through b200rt_render_frame / b200rt_render_frame_device first");
+	const unsigned total_warps = unsigned(ctx->params.tile_count_mine) * 32u;
+	if (total_warps == 0) return 0;
+	CHECK_CUDA(ctx, cudaSetDevice(ctx->config.device));
+	unsigned char * scratch = nullptr;
+	if (noalloc_scratch_address(ctx, &scratch)) return -1;
+
+	// the scratch keeps the previous call's counts: the unit counter, the ray counters and the tile costs start at zero
+	const size_t used = sizeof(FrameCounters) + size_t(ctx->params.tile_count_mine) * sizeof(unsigned);
+	CHECK_CUDA(ctx, cudaMemsetAsync(scratch, 0, used, ctx->stream));
+
+	SceneParams P = ctx->params;
+	P.band_count = 0;                           // one target: the caller's image
+	P.blas_stack_entries = ctx->blas_stack_entries;
+	P.queue_mode = 0;                           // the depth-first walk: the queued one needs pools
+	P.tile_cost = reinterpret_cast<unsigned *>(scratch + sizeof(FrameCounters));   // the context's own cost history and tile order stay as they are
+	int & per_sm = ctx->blocks_per_sm[0][0];
+	if (per_sm == 0) {
+		CHECK_CUDA(ctx, ctx->kernels->render_occupancy(P, false, &per_sm));    // a query, no allocation
+		if (per_sm < 1) per_sm = 1;
+	}
+	unsigned blocks = unsigned(ctx->num_sms) * unsigned(per_sm);
+	const unsigned needed = (total_warps + 7) / 8;
+	if (blocks > needed) blocks = needed;
+	CHECK_CUDA(ctx, ctx->kernels->render(P, reinterpret_cast<unsigned *>(uintptr_t(frame_buffer_dev)), nullptr, reinterpret_cast<FrameCounters *>(scratch), 0, blocks, ctx->stream));
 	return 0;
 }
 

@@ -141,6 +141,7 @@ def device_lib():
         lib.b200rt_upload_static.argtypes = [C.c_void_p, C.POINTER(StaticScene)]
         lib.b200rt_render_frame.argtypes = [C.c_void_p, C.POINTER(Frame), C.POINTER(Outputs)]
         lib.b200rt_render_frame_device.argtypes = [C.c_void_p, C.POINTER(Frame), C.c_uint64, C.POINTER(Stats)]
+        lib.b200rt_render_resident_noalloc.argtypes = [C.c_void_p, C.c_uint64]
         lib.b200rt_last_frame_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
         lib.b200rt_peer_alloc.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(PeerHandle)]
         lib.b200rt_peer_free.argtypes = [C.c_void_p, C.c_uint64]

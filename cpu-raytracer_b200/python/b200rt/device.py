@@ -131,6 +131,11 @@ class Renderer:
         self._check(self._lib.b200rt_render_frame_device(self._h, C.byref(frame), C.c_uint64(frame_buffer_ptr), C.byref(stats)))
         return stats.as_dict()
 
+    def render_resident_noalloc(self, frame_buffer_ptr):
+        """The resident frame once more into a caller-owned device image, through the entry point that allocates nothing
+        (b200rt_render_resident_noalloc: scratch in a static device array). Only enqueues on the context's stream."""
+        self._check(self._lib.b200rt_render_resident_noalloc(self._h, C.c_uint64(frame_buffer_ptr)))
+
     def last_frame_stats(self):
         """Counters of the frame rendered last (waits for the stream); device_ms_render = the kernel's own globaltimer span."""
         stats = _ffi.Stats()

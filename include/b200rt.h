@@ -302,6 +302,23 @@ int b200rt_present_rows_device(b200rt_ctx * ctx, uint64_t frame_buffer_dev, uint
 /* (b200rt_render_frame, b200rt_submit_frame and b200rt_time_resident always render into the one image they own:
  * band targets apply to b200rt_render_frame_device only.)                                        */
 
+/* Renders the frame that is resident in the context (the one last handed to b200rt_render_frame,
+ * b200rt_render_frame_device or b200rt_submit_frame) once more, into the caller's device image frame_buffer_dev
+ * (uint32 [height][width], this context's tiles), WITHOUT ALLOCATING ANYTHING: no cudaMalloc, cudaFree or allocating
+ * library routine is called, so it can be used where those are forbidden (under CUDA graph capture, in a serving loop,
+ * in a harness that bans them). This entry point has no counterpart in the reference.
+ * The render kernel's scratch — its work counter, ray counters and per-tile cost words, which the
+ * other entry points keep in memory the context allocated — lives in one file-scope device array of
+ * 512 + 4 * B200RT_NOALLOC_MAX_TILES bytes (64.5 KB), held by every GPU that loads the library until the process exits.
+ * A context with more than B200RT_NOALLOC_MAX_TILES 32x32 tiles of its own (16 384: every frame up to 4096 x 4096, and
+ * a 1/N share of larger ones) is refused with an error. Every call of the process on one GPU shares that array: the
+ * call clears the part it uses on the context's stream before the launch, and calls that overlap on the GPU (two
+ * contexts, two streams) race — issue them one after another. Depth-first walk (deep_queue is ignored: the queued walk
+ * needs pools), band targets ignored, the context's tile order and counters untouched; same image, bit for bit, as the
+ * other entry points. Asynchronous: enqueues on the context's stream and returns.                                  */
+#define B200RT_NOALLOC_MAX_TILES 16384
+int b200rt_render_resident_noalloc(b200rt_ctx * ctx, uint64_t frame_buffer_dev);
+
 /* Re-times the last frame without host<->device traffic: `repeat` launches of the render
  * (+FXAA) kernels on resident inputs, each timed with CUDA events on the context's stream;
  * returns the average per-frame device times. flush_l2_bytes > 0: before every timed launch

@@ -86,6 +86,7 @@ static inline cudaError_t cudaMemcpy(void * d, const void * s, size_t n, cudaMem
 static inline cudaError_t cudaMemcpyAsync(void * d, const void * s, size_t n, cudaMemcpyKind, cudaStream_t) { if (n) memcpy(d, s, n); return cudaSuccess; }
 static inline cudaError_t cudaMemset(void * d, int v, size_t n) { memset(d, v, n); return cudaSuccess; }
 static inline cudaError_t cudaMemsetAsync(void * d, int v, size_t n, cudaStream_t) { memset(d, v, n); return cudaSuccess; }
+template<typename T> static inline cudaError_t cudaGetSymbolAddress(void ** p, T & symbol) { *p = &symbol; return cudaSuccess; }
 template<typename T> static inline cudaError_t cudaMemcpyToSymbol(T & symbol, const void * s, size_t n) { memcpy(&symbol, s, n); return cudaSuccess; }
 static inline cudaError_t cudaStreamCreateWithFlags(cudaStream_t * s, unsigned) { *s = reinterpret_cast<cudaStream_t>(malloc(8)); return cudaSuccess; }
 static inline cudaError_t cudaStreamDestroy(cudaStream_t s) { free(s); return cudaSuccess; }

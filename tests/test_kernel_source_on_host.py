@@ -99,6 +99,28 @@ def test_emulated_auto_queue_times_both_walks_and_every_frame_matches(emulated):
 
 
 @pytest.mark.timeout(300)
+def test_emulated_no_alloc_entry_point_gives_the_same_frame_twice(emulated):
+    """b200rt_render_resident_noalloc on the host build (tests/test_zz_no_alloc.py is the same test on the GPU)."""
+    import ctypes as C
+    from b200rt import _ffi
+    g = Golden("monkey_b1_aniso")
+    m = g.meta
+    lib = _ffi.device_lib()
+    r = emulated(m["width"], m["height"], m["bounces"], m["filter"])
+    r.upload_static(g.pack)
+    expected = r.render(g.pack, want_presented=False)["frame_buffer"]
+    for _ in range(2):
+        ptr, handle = C.c_uint64(), _ffi.PeerHandle()
+        r._check(lib.b200rt_peer_alloc(r._h, expected.nbytes, C.byref(ptr), C.byref(handle)))
+        r.render_resident_noalloc(ptr.value)
+        got = np.zeros_like(expected)
+        r._check(lib.b200rt_peer_read(r._h, ptr, got.ctypes.data, got.nbytes))
+        r._check(lib.b200rt_peer_free(r._h, ptr))
+        assert np.array_equal(got, expected)
+    r.close()
+
+
+@pytest.mark.timeout(300)
 def test_emulated_queue_that_gave_a_frame_up_is_rendered_again_depth_first(emulated, monkeypatch):
     """The queue kernel's watchdog (FrameCounters::q_abort) marks a frame as incomplete: b200rt_render_frame renders it again
     depth-first and the context stays depth-first. B200RT_TEST_QUEUE_STALL marks the first queued frame that way."""
