@@ -247,7 +247,7 @@ def ncu_figures(workload, queued=False):
     return data.get("workloads", {}).get(workload + "/queued" if queued else workload) or {}
 
 
-def roofline_record(workload, kernel_ms, alg_bytes, rays, clocks, own_walk=None, queued=False):
+def roofline_record(workload, kernel_ms, alg_bytes, rays, clocks, own_walk=None, queued=False, n_gpus=1):
     """The judged fraction is ISSUE: lane-instructions issued against what the SMs can issue (<= 1 by construction)."""
     if not kernel_ms:
         return None
@@ -255,14 +255,14 @@ def roofline_record(workload, kernel_ms, alg_bytes, rays, clocks, own_walk=None,
     peak_hbm, peak_source = load_peaks()
     seconds = kernel_ms * 1e-3
     sm_hz = (clocks.get("sm_mhz") or 1965.0) * 1e6
-    issue_peak = 148 * 4 * 32 * sm_hz
+    issue_peak = n_gpus * 148 * 4 * 32 * sm_hz       # the job's: every GPU issues
     thread_instructions = ncu.get("thread_instructions_per_launch")
     record = {
         "bound": "issue", "kernel": ncu.get("kernel", "render_queue_kernel" if queued else "render_kernel"), "kernel_ms": kernel_ms,
         "deep_pixel_queue": bool(queued),
         "achieved": None if not thread_instructions else thread_instructions / seconds / 1e12, "peak": issue_peak / 1e12, "unit": "T lane-instructions/s",
         "frac": None if not thread_instructions else thread_instructions / seconds / issue_peak,
-        "peak_source": "148 SMs x 4 schedulers x 32 lanes x SM clock sampled during the timed region (%.0f MHz)" % (sm_hz / 1e6),
+        "peak_source": "%s148 SMs x 4 schedulers x 32 lanes x SM clock sampled during the timed region (%.0f MHz)" % ("%d GPUs x " % n_gpus if n_gpus > 1 else "", sm_hz / 1e6),
         "thread_instructions_per_launch": thread_instructions, "threads_per_instruction": ncu.get("threads_per_instruction"), "issue_active_pct": ncu.get("issue_active_pct"),
         "stalls_per_issue": ncu.get("stalls_per_issue"),
         "traffic": ncu.get("dram_bytes_per_launch"),
@@ -272,9 +272,9 @@ def roofline_record(workload, kernel_ms, alg_bytes, rays, clocks, own_walk=None,
         "dram_gbs": None if not ncu.get("dram_bytes_per_launch") else ncu["dram_bytes_per_launch"] / seconds / 1e9,
         "l2_gbs": None if not ncu.get("l2_bytes_per_launch") else ncu["l2_bytes_per_launch"] / seconds / 1e9,
         "l1_gbs": None if not ncu.get("l1_bytes_per_launch") else ncu["l1_bytes_per_launch"] / seconds / 1e9,
-        "hbm_peak_gbs": peak_hbm, "hbm_peak_source": peak_source,
-        "hbm_frac_of_algorithmic_stream": alg_bytes / seconds / 1e9 / peak_hbm,
-        "hbm_frac_of_dram_traffic": None if not ncu.get("dram_bytes_per_launch") else ncu["dram_bytes_per_launch"] / seconds / 1e9 / peak_hbm,
+        "hbm_peak_gbs": n_gpus * peak_hbm, "hbm_peak_source": peak_source + (" x %d GPUs" % n_gpus if n_gpus > 1 else ""),
+        "hbm_frac_of_algorithmic_stream": alg_bytes / seconds / 1e9 / (n_gpus * peak_hbm),
+        "hbm_frac_of_dram_traffic": None if not ncu.get("dram_bytes_per_launch") else ncu["dram_bytes_per_launch"] / seconds / 1e9 / (n_gpus * peak_hbm),
         "l1_hit_pct": ncu.get("l1_hit_pct"), "l2_hit_pct": ncu.get("l2_hit_pct"), "l1_throughput_pct": ncu.get("l1_throughput_pct"),
         "local_ld_st_warp_instructions": ncu.get("local_ld_st_warp_instructions"), "global_ld_warp_instructions": ncu.get("global_ld_warp_instructions"),
         "ncu_source": ncu.get("source"),
@@ -682,9 +682,9 @@ def run_gpu_arm(args, w):
             own_walk = {"nodes_visited": s["nodes_visited"], "triangles_tested": s["triangles_tested"],
                         "reference_order": {"nodes_visited": full_stats["nodes_visited"], "triangles_tested": full_stats["triangles_tested"]},
                         "what": "shadow rays on the threaded copy, right child first (the walk that is timed) vs the reference's front-to-back order (the walk the algorithmic bytes are counted on); closest-hit rays are the same in both"}
-        roofline = roofline_record(name, m["ms_render"], algorithmic_bytes(full_stats, pixels), rays, clk, own_walk, queued=bool(m.get("queued")))
+        roofline = roofline_record(name, m["ms_render"], algorithmic_bytes(full_stats, pixels), rays, clk, own_walk, queued=bool(m.get("queued")), n_gpus=world)
         if roofline is not None and world > 1:
-            roofline["kernel_ms_source"] = "the slowest rank's render kernel, timed by the kernel itself (%globaltimer, first block started .. last warp done); instruction and byte counts are the whole frame's (single-GPU capture), so achieved figures are per-job"
+            roofline["kernel_ms_source"] = "the slowest rank's render kernel, timed by the kernel itself (%globaltimer, first block started .. last warp done); instruction and byte counts are the whole frame's (single-GPU capture) and the peaks are the N GPUs' together, so every figure is the job's"
         line = {
             "metric": wl["metric"], "value": rays / m["ms_step"] / 1e3, "unit": "Mrays/s", "n_gpus": world,
             "ms_per_step": m["ms_step"], "frames_per_s": 1e3 / m["ms_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,

@@ -72,7 +72,7 @@ struct b200rt_ctx {
 	int queue_inline_below = 0;
 	bool queue_stalled = false;           // the queue kernel's watchdog fired once: this context renders depth-first from then on
 	bool test_stall = false;              // B200RT_TEST_QUEUE_STALL (tests): the first queued frame is marked as given up, to exercise the recovery
-	int blas_stack_entries = 1;
+	int blas_stack_entries = 1, tlas_stack_entries = 1;
 	DeviceBuffer tile_cost, tile_order; // schedule of the render kernel (kernels.cuh: tile_schedule_kernel)
 	int tile_count_mine = 0;
 	void * pinned_out = nullptr; size_t pinned_out_bytes = 0;
@@ -486,6 +486,7 @@ static int stage_frame(b200rt_ctx * ctx, const b200rt_frame * f) {
 	int tlas_depth = 0;
 	if (const char * problem = check_tree(f->tlas_nodes, f->tlas_node_count, f->instance_count, &tlas_depth)) return fail(ctx, std::string("TLAS: ") + problem);
 	if (tlas_depth + 1 > RT_TLAS_STACK_SIZE) return fail(ctx, "TLAS deeper than the traversal stack (RT_TLAS_STACK_SIZE)");
+	ctx->tlas_stack_entries = tlas_depth + 1;
 	if ((f->sphere_count > 0 && !f->spheres) || (f->plane_count > 0 && !f->planes) || (f->light_count > 0 && !f->lights)) return fail(ctx, "a count is positive but its array is NULL");
 	for (int i = 0; i < f->sphere_count; i++) if (f->spheres[i].material_id < 0 || f->spheres[i].material_id >= material_count) return fail(ctx, "sphere material id out of range");
 	for (int i = 0; i < f->plane_count;  i++) if (f->planes[i].material_id  < 0 || f->planes[i].material_id  >= material_count) return fail(ctx, "plane material id out of range");
@@ -659,7 +660,7 @@ static int launch_render(b200rt_ctx * ctx, unsigned * frame_buffer, float * colo
 	if (total_warps == 0) return 0;
 	SceneParams P = ctx->params;
 	if (!banded) P.band_count = 0;
-	P.blas_stack_entries = ctx->blas_stack_entries;
+	P.blas_stack_entries = ctx->blas_stack_entries; P.tlas_stack_entries = ctx->tlas_stack_entries;
 	P.queue_mode = (count || P.bounces == 0 || ctx->queue_stalled) ? 0 : ctx->config.deep_queue;
 	P.queue_inline_below = ctx->queue_inline_below;
 	ctx->auto_queue.issued = -1;
@@ -993,7 +994,7 @@ extern "C" int b200rt_render_resident_noalloc(b200rt_ctx * ctx, uint64_t frame_b
 
 	SceneParams P = ctx->params;
 	P.band_count = 0;                           // one target: the caller's image
-	P.blas_stack_entries = ctx->blas_stack_entries;
+	P.blas_stack_entries = ctx->blas_stack_entries; P.tlas_stack_entries = ctx->tlas_stack_entries;
 	P.queue_mode = 0;                           // the depth-first walk: the queued one needs pools
 	P.tile_cost = reinterpret_cast<unsigned *>(scratch + sizeof(FrameCounters));   // the context's own cost history and tile order stay as they are
 	int & per_sm = ctx->blocks_per_sm[0][0];

@@ -18,7 +18,7 @@ typedef void (*RenderKernel)(const SceneParams, unsigned *, float *, FrameCounte
 // The instantiation for a frame: frames[] sized by the bounce limit (1 / 3 / 8), BLAS stack by the deepest tree (32 / 64).
 static RenderKernel pick_render(const SceneParams & P, int count) {
 	if (count) return render_kernel<true, RT_MAX_BOUNCES, 64>;
-	const bool deep = P.blas_stack_entries > 32;
+	const bool deep = P.blas_stack_entries > 32 || P.tlas_stack_entries > RT_TLAS_STACK_SMALL;
 	if (P.queue_mode != 0) {
 		if (deep) return render_queue_kernel<8, 64>;
 		return P.bounces <= 3 ? render_queue_kernel<3, 32> : render_queue_kernel<8, 32>;

@@ -284,21 +284,38 @@ __device__ __forceinline__ unsigned group_reserve(unsigned * counter, unsigned p
 #endif
 }
 
+// The same for one OR two slots per lane (two_slots): a lane with one child takes one bounce slot, so that every
+// slot of the queue carries a ray and a warp that draws 32 tickets gets 32 rays.
+__device__ __forceinline__ unsigned group_reserve_1_or_2(unsigned * counter, bool two_slots) {
+#ifdef RT_EMULATE
+	return atomicAdd(counter, two_slots ? 2u : 1u);
+#else
+	const unsigned mask = __activemask();
+	const unsigned twos = __ballot_sync(mask, two_slots);
+	const int lane = threadIdx.x & 31, leader = __ffs(mask) - 1;
+	unsigned base = 0;
+	if (lane == leader) base = atomicAdd(counter, unsigned(__popc(mask) + __popc(twos)));
+	base = __shfl_sync(mask, base, leader);
+	const unsigned below = (1u << lane) - 1u;
+	return base + unsigned(__popc(mask & below) + __popc(twos & below));
+#endif
+}
+
 // Exports the top node of a walk: record and children. Returns false when a pool is exhausted (nothing has been
 // published then, and the caller goes on walking). result: the node's finished direct lighting.
 __device__ __forceinline__ bool export_node(const SceneParams & P, const QueueContext & q, const HitRecord & hit, float distance, int flags, float F_r, v3 result,
                                             const Ray & reflected, const Ray & refracted, int bounces_left, Counters & cnt) {
 	const bool has_child[2] = { (flags & FRAME_HAS_REFLECTION) != 0, (flags & FRAME_HAS_REFRACTION) && !(flags & FRAME_TIR) };
 	const int n_children = (has_child[0] ? 1 : 0) + (has_child[1] ? 1 : 0);
-	// every exporting lane takes one record and two bounce slots: fixed sizes keep the reservation one atomicAdd per
-	// group; a slot that stays unused is published as a null item
+	// every exporting lane takes one record and one bounce slot per child, one atomicAdd per group of lanes each
 	const unsigned node_slot = group_reserve(&q.counters->q_node_reserved, 1u);
 	if (node_slot >= P.q_node_capacity) { atomicAdd(&q.counters->q_fallbacks, 1u); return false; }
-	const unsigned bounce_slot = group_reserve(&q.counters->q_bounce_reserved, 2u);
-	if (bounce_slot + 2u > P.q_bounce_capacity) { // slots inside the pool must still be published (somebody may have claimed them): as null items
-		for (unsigned k = 0; k < 2u; k++) if (bounce_slot + k < P.q_bounce_capacity) __stcg(P.q_bounce + 5 * size_t(bounce_slot + k) + 4, make_float4(0.0f, 0.0f, as_f(QUEUE_NULL_ITEM), 0.0f));
+	const unsigned slots = unsigned(n_children);
+	const unsigned bounce_slot = group_reserve_1_or_2(&q.counters->q_bounce_reserved, n_children == 2);
+	if (bounce_slot + slots > P.q_bounce_capacity) { // slots inside the pool must still be published (somebody may have claimed them): as null items
+		for (unsigned k = 0; k < slots; k++) if (bounce_slot + k < P.q_bounce_capacity) __stcg(P.q_bounce + 5 * size_t(bounce_slot + k) + 4, make_float4(0.0f, 0.0f, as_f(QUEUE_NULL_ITEM), 0.0f));
 		__threadfence();
-		for (unsigned k = 0; k < 2u; k++) if (bounce_slot + k < P.q_bounce_capacity) __stcg(P.q_bounce_ready + bounce_slot + k, P.frame_serial);
+		for (unsigned k = 0; k < slots; k++) if (bounce_slot + k < P.q_bounce_capacity) __stcg(P.q_bounce_ready + bounce_slot + k, P.frame_serial);
 		atomicAdd(&q.counters->q_fallbacks, 1u);
 		return false;
 	}
@@ -311,16 +328,14 @@ __device__ __forceinline__ bool export_node(const SceneParams & P, const QueueCo
 	__stcg(rec + 2, make_float4(hit.normal.x, hit.normal.y, hit.normal.z, F_r));
 	__stcg(rec + 3, make_float4(result.x, result.y, result.z, 0.0f));
 	// payloads, ONE fence, then the ready words: record and items are in L2 before any consumer can see an item that names the record
+	unsigned slot = bounce_slot;
 	for (int k = 0; k < 2; k++) {
-		if (has_child[k]) {
-			if (k == 0) cnt.reflection++; else cnt.refraction++;
-			write_bounce_item(P, bounce_slot + k, k == 0 ? reflected : refracted, node, k, bounces_left - 1);
-		} else {
-			__stcg(P.q_bounce + 5 * size_t(bounce_slot + k) + 4, make_float4(0.0f, 0.0f, as_f(QUEUE_NULL_ITEM), 0.0f));
-		}
+		if (!has_child[k]) continue;
+		if (k == 0) cnt.reflection++; else cnt.refraction++;
+		write_bounce_item(P, slot++, k == 0 ? reflected : refracted, node, k, bounces_left - 1);
 	}
 	__threadfence();
-	for (unsigned k = 0; k < 2u; k++) __stcg(P.q_bounce_ready + bounce_slot + k, P.frame_serial);
+	for (unsigned k = 0; k < slots; k++) __stcg(P.q_bounce_ready + bounce_slot + k, P.frame_serial);
 	return true;
 }
 

@@ -26,6 +26,7 @@ namespace rt {
 struct Affine { float4 r0, r1, r2; };
 
 #define RT_TLAS_STACK_SIZE 32   // entries of the TLAS traversal stack; b200rt.cu rejects a frame whose TLAS is deeper
+#define RT_TLAS_STACK_SMALL 8   // ... of the instantiations for shallow trees (a TLAS over up to ~100 instances): the kernels are picked per frame
 #define RT_MAX_BOUNCES 8        // NUMBER_OF_BOUNCES the kernels are instantiated up to
 
 struct DeviceInstance {
@@ -101,6 +102,7 @@ struct SceneParams {
 	int queue_mode;              // 0 off; 1: pixels whose primary ray hits a transmissive material; 2: every pixel whose primary hit spawns rays
 	int queue_inline_below;      // a popped ray with at most this many bounces left is walked to the end by the thread that popped it
 	int blas_stack_entries;      // deepest BLAS + 1: what a push-both-pop-one traversal can hold
+	int tlas_stack_entries;      // this frame's TLAS depth + 1
 };
 
 #define RT_QUEUE_WATCHDOG_NS 2000000000ull   // kernels.cuh: render_queue_kernel gives a frame up after waiting this long on unpublished items

@@ -20,8 +20,8 @@ namespace RT_NAMESPACE {
 
 // BVH_TRAVERSAL_STACK_SIZE (Config.h:25) is 64 — a capacity, not semantics: a traversal that pushes both children
 // and pops one holds at most depth + 1 entries. The host measures every tree's depth (threaded_nodes.h: check_tree)
-// and the launch picks the instantiation whose BLAS stack (BSTACK = 32 or 64 entries) is deep enough; the TLAS stack
-// is RT_TLAS_STACK_SIZE entries (rt_types.h), checked per frame. Smaller arrays = a smaller local-memory frame per
+// and the launch picks the instantiation whose stacks are deep enough: BSTACK = 32 BLAS entries with
+// RT_TLAS_STACK_SMALL TLAS entries, or 64 with RT_TLAS_STACK_SIZE (rt_types.h; the TLAS is measured per frame). Smaller arrays = a smaller local-memory frame per
 // thread (151 552 resident threads: every 4 bytes are 0.6 MB of L2 footprint).
 
 struct Ray {               // Ray.h:7-16
@@ -419,7 +419,7 @@ __device__ __forceinline__ void trace_closest(const SceneParams & P, v3 o, v3 d,
 	}
 
 	// TopLevelBVH::trace, TopLevelBVH.cpp:53-87
-	int tlas_stack[RT_TLAS_STACK_SIZE];
+	int tlas_stack[BSTACK > 32 ? RT_TLAS_STACK_SIZE : RT_TLAS_STACK_SMALL];   // the deep instantiations carry both full stacks
 	int blas_stack[BSTACK];
 
 	const v3 inv_d = inv_direction(d);
@@ -474,7 +474,7 @@ __device__ __forceinline__ bool trace_any(const SceneParams & P, v3 o, v3 d, flo
 	}
 
 	// TopLevelBVH::intersect, TopLevelBVH.cpp:89-129
-	int tlas_stack[RT_TLAS_STACK_SIZE];
+	int tlas_stack[BSTACK > 32 ? RT_TLAS_STACK_SIZE : RT_TLAS_STACK_SMALL];   // the deep instantiations carry both full stacks
 	int blas_stack[COUNT ? BSTACK : 1];   // the shipped any-hit walk is stackless (blas_shadow); only the counting build pushes
 
 	const v3 inv_d = inv_direction(d);
