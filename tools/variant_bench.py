@@ -2,7 +2,7 @@
 """Times kernel variants / run-time settings of libb200rt.so side by side (development tool).
 
     python tools/variant_bench.py SPEC [SPEC ...]
-    SPEC = label[,lib=path/to/libb200rt_x.so][,queue=off|glass|all|auto][,arith=exact|fast][,inline=N]
+    SPEC = label[,lib=path/to/libb200rt_x.so][,queue=off|glass|all|auto][,arith=exact|fast][,inline=N][,flush=0|1]
 
 Each SPEC runs in its own process (B200RT_LIB / B200RT_DEEP_QUEUE / B200RT_ARITHMETIC / B200RT_QUEUE_INLINE_BELOW
 select library and settings). First the golden fixtures are rendered and compared with the real reference's stored
@@ -86,8 +86,9 @@ def child():
                 first = r.render(pack, want_presented=False)     # the tile order settles on the measured costs
             s = first["stats"]
             rays = s["primary_rays"] + s["shadow_rays"] + s["reflection_rays"] + s["refraction_rays"]
-            r.time_resident(3, bench.L2_FLUSH_BYTES)
-            ms_render, ms_fxaa = r.time_resident(steps, bench.L2_FLUSH_BYTES)
+            flush = bench.L2_FLUSH_BYTES if os.environ.get("VARIANT_FLUSH", "1") != "0" else 0    # VARIANT_FLUSH=0: warm L2, as a frame loop leaves it
+            r.time_resident(3, flush)
+            ms_render, ms_fxaa = r.time_resident(steps, flush)
             r.close()
             key = "" if stride == 1 else "_share%d" % stride
             entry["ms_render" + key] = round(ms_render, 4)
@@ -116,6 +117,8 @@ def main():
                 env["B200RT_ARITHMETIC"] = value
             elif key == "inline":
                 env["B200RT_QUEUE_INLINE_BELOW"] = value
+            elif key == "flush":
+                env["VARIANT_FLUSH"] = value
             else:
                 raise SystemExit("bad SPEC item " + item)
         try:
