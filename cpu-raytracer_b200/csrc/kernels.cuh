@@ -160,7 +160,7 @@ render_queue_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, f
 				first = atomicAdd(&counters->next_unit, 1u);
 				if (first < total_units) kind = WORK_UNIT; else units_left = false;
 			}
-			if (kind == WORK_NONE && (units_left || ab > 0u || (idle_looks < 3 && peek(&counters->q_outstanding) > 0))) kind = WORK_WAIT;
+			if (kind == WORK_NONE && (units_left || ab > 0u || (idle_looks < P.queue_idle_looks && peek(&counters->q_outstanding) > 0))) kind = WORK_WAIT;
 		}
 		kind = __shfl_sync(0xffffffffu, kind, 0); first = __shfl_sync(0xffffffffu, first, 0); n = __shfl_sync(0xffffffffu, n, 0);
 		if (kind == WORK_NONE || kind == WORK_VOID) break;

@@ -101,6 +101,7 @@ struct SceneParams {
 	unsigned frame_serial;       // never 0, different for every launch of a context
 	int queue_mode;              // 0 off; 1: pixels whose primary ray hits a transmissive material; 2: every pixel whose primary hit spawns rays
 	int queue_inline_below;      // a popped ray with at most this many bounces left is walked to the end by the thread that popped it
+	int queue_idle_looks;        // a warp that finds neither item nor unit looks this many times more (2 / 4 / 8 / 8 ... us apart) before it leaves
 	int blas_stack_entries;      // deepest BLAS + 1: what a push-both-pop-one traversal can hold
 	int tlas_stack_entries;      // this frame's TLAS depth + 1
 };
