@@ -107,7 +107,7 @@ struct b200rt_ctx {
 	// behind the frame — no synchronisation, no timing event —, the candidate with the smaller minimum is kept, and
 	// every PERIOD frames the comparison is repeated. Both walks produce the same bits, so switching is invisible.
 	struct AutoQueue {
-		enum { WARM = 2, PAIRS = 3, SLOTS = 4, PERIOD = 512 };
+		enum { WARM = 2, PAIRS = 3, SLOTS = 4, PERIOD = 4096 };
 		int   frame = 0;            // frames since the comparison (re)started
 		int   choice = 0;           // 0 = depth-first, 1 = queued
 		bool  decided = false;

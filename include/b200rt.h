@@ -162,7 +162,7 @@ typedef struct {
 	 * 1 = pixels whose primary ray hits a transmissive material hand their reflection and refraction rays to a
 	 * device-side queue that all persistent warps pop; 2 = every pixel whose primary hit spawns rays does;
 	 * 3 = AUTO: the context times both (setting 0 against setting 2)
-	 * on its own first frames from the kernels' %globaltimer stamps, keeps the faster and looks again every 512 frames.
+	 * on its own first frames from the kernels' %globaltimer stamps, keeps the faster and looks again every 4096 frames.
 	 * Same image bit for bit in every setting: the node values are combined in the reference's order.               */
 	int32_t deep_queue;
 } b200rt_config;
