@@ -315,6 +315,7 @@ extern "C" int b200rt_upload_static(b200rt_ctx * ctx, const b200rt_static_scene 
 	for (int t = 0; t < s->texture_count; t++) {
 		const b200rt_texture & tex = s->textures[t];
 		if (tex.width <= 0 || tex.height <= 0 || tex.mip_levels < 1 || tex.mip_levels > B200RT_MAX_MIP_LEVELS || tex.texel_offset < 0) return fail(ctx, "bad texture descriptor");
+		if (tex.mipmapped && ((tex.width & (tex.width - 1)) || (tex.height & (tex.height - 1)))) return fail(ctx, "a mip-mapped texture must have power-of-two sides (Texture.cpp:50): the mip-map filters wrap coordinates by masking");
 		const int last = tex.mip_levels - 1;
 		const int64_t end = tex.texel_offset + tex.mip_offsets[last] + int64_t(std::max(tex.width >> last, 1)) * std::max(tex.height >> last, 1);
 		if (end > s->texel_count) return fail(ctx, "texture pyramid exceeds the texel pool");

@@ -269,35 +269,36 @@ __device__ __forceinline__ void read_bounce_item(const SceneParams & P, unsigned
 // What a walk needs to export its top node.
 struct QueueContext { FrameCounters * counters; int parent, which; };
 
-// Slots for the lanes that happen to stand here together (one atomicAdd for the group): `per_lane` slots each.
-// The group is whoever is converged at this point — any grouping is correct, a larger one is cheaper.
-__device__ __forceinline__ unsigned group_reserve(unsigned * counter, unsigned per_lane) {
+// One reservation for everything an export needs, for the lanes that happen to stand here together (whoever is converged
+// at this point — any grouping is correct, a larger one is cheaper): a node record per lane and a
+// bounce slot per child (one or two), taken with ONE 64-bit atomicAdd on the pair of cursors (records in the low word,
+// bounce slots in the high word), and the children added to the frame's outstanding work with one more — an export
+// used to cost two dependent atomics per group and a third per lane on one address.
+__device__ __forceinline__ void group_reserve_export(FrameCounters * counters, int n_children, unsigned & node_slot, unsigned & bounce_slot) {
+	unsigned long long * cursors = reinterpret_cast<unsigned long long *>(&counters->q_node_reserved);   // {q_node_reserved, q_bounce_reserved}
 #ifdef RT_EMULATE
-	return atomicAdd(counter, per_lane);
+	const unsigned long long old = atomicAdd(cursors, 1ull | (static_cast<unsigned long long>(n_children) << 32));
+	atomicAdd(&counters->q_outstanding, n_children);
+	node_slot = unsigned(old); bounce_slot = unsigned(old >> 32);
 #else
 	const unsigned mask = __activemask();
+	const unsigned twos = __ballot_sync(mask, n_children == 2);
 	const int lane = threadIdx.x & 31, leader = __ffs(mask) - 1;
-	unsigned base = 0;
-	if (lane == leader) base = atomicAdd(counter, per_lane * unsigned(__popc(mask)));
-	base = __shfl_sync(mask, base, leader);
-	return base + per_lane * unsigned(__popc(mask & ((1u << lane) - 1u)));
-#endif
-}
-
-// The same for one OR two slots per lane (two_slots): a lane with one child takes one bounce slot, so that every
-// slot of the queue carries a ray and a warp that draws 32 tickets gets 32 rays.
-__device__ __forceinline__ unsigned group_reserve_1_or_2(unsigned * counter, bool two_slots) {
-#ifdef RT_EMULATE
-	return atomicAdd(counter, two_slots ? 2u : 1u);
-#else
-	const unsigned mask = __activemask();
-	const unsigned twos = __ballot_sync(mask, two_slots);
-	const int lane = threadIdx.x & 31, leader = __ffs(mask) - 1;
-	unsigned base = 0;
-	if (lane == leader) base = atomicAdd(counter, unsigned(__popc(mask) + __popc(twos)));
-	base = __shfl_sync(mask, base, leader);
+	unsigned lo = 0, hi = 0;
+	if (lane == leader) {
+		const unsigned records = unsigned(__popc(mask)), children = records + unsigned(__popc(twos));
+		const unsigned long long old = atomicAdd(cursors, static_cast<unsigned long long>(records) | (static_cast<unsigned long long>(children) << 32));
+		// before anything is visible: the count never runs low. The returned value is USED, so the add has been performed
+		// at L2 before the shuffle below hands out the slots — every lane's stores (payload, fence, ready word) are issued
+		// after that; a consumer that sees an item of this group cannot bring the count to zero ahead of this add.
+		const int before = atomicAdd(&counters->q_outstanding, int(children));
+		lo = unsigned(old) + (before == int(0x80000000u) ? 1u : 0u); hi = unsigned(old >> 32);
+	}
+	lo = __shfl_sync(mask, lo, leader); hi = __shfl_sync(mask, hi, leader);
+	__syncwarp(mask);
 	const unsigned below = (1u << lane) - 1u;
-	return base + unsigned(__popc(mask & below) + __popc(twos & below));
+	node_slot = lo + unsigned(__popc(mask & below));
+	bounce_slot = hi + unsigned(__popc(mask & below) + __popc(twos & below));
 #endif
 }
 
@@ -307,19 +308,18 @@ __device__ __forceinline__ bool export_node(const SceneParams & P, const QueueCo
                                             const Ray & reflected, const Ray & refracted, int bounces_left, Counters & cnt) {
 	const bool has_child[2] = { (flags & FRAME_HAS_REFLECTION) != 0, (flags & FRAME_HAS_REFRACTION) && !(flags & FRAME_TIR) };
 	const int n_children = (has_child[0] ? 1 : 0) + (has_child[1] ? 1 : 0);
-	// every exporting lane takes one record and one bounce slot per child, one atomicAdd per group of lanes each
-	const unsigned node_slot = group_reserve(&q.counters->q_node_reserved, 1u);
-	if (node_slot >= P.q_node_capacity) { atomicAdd(&q.counters->q_fallbacks, 1u); return false; }
 	const unsigned slots = unsigned(n_children);
-	const unsigned bounce_slot = group_reserve_1_or_2(&q.counters->q_bounce_reserved, n_children == 2);
-	if (bounce_slot + slots > P.q_bounce_capacity) { // slots inside the pool must still be published (somebody may have claimed them): as null items
+	unsigned node_slot, bounce_slot;
+	group_reserve_export(q.counters, n_children, node_slot, bounce_slot);
+	if (node_slot >= P.q_node_capacity || bounce_slot + slots > P.q_bounce_capacity) {
+		// a pool is exhausted. Bounce slots inside the pool must still be published (somebody may hold a ticket for them): as null items
 		for (unsigned k = 0; k < slots; k++) if (bounce_slot + k < P.q_bounce_capacity) __stcg(P.q_bounce + 5 * size_t(bounce_slot + k) + 4, make_float4(0.0f, 0.0f, as_f(QUEUE_NULL_ITEM), 0.0f));
 		__threadfence();
 		for (unsigned k = 0; k < slots; k++) if (bounce_slot + k < P.q_bounce_capacity) __stcg(P.q_bounce_ready + bounce_slot + k, P.frame_serial);
+		atomicSub(&q.counters->q_outstanding, n_children);   // they will not become work (the walk that queued nothing still holds its own count)
 		atomicAdd(&q.counters->q_fallbacks, 1u);
 		return false;
 	}
-	atomicAdd(&q.counters->q_outstanding, n_children);   // before anything is visible: the count never runs low
 
 	const int node = int(node_slot);
 	float4 * rec = P.q_nodes + 6 * size_t(node);

@@ -111,6 +111,10 @@ __device__ __forceinline__ int positive_mod(int value, int modulus) { // Math::m
 	int r = value % modulus;
 	return r < 0 ? r + modulus : r;
 }
+// The same for a modulus that is KNOWN to be a power of two — every level of a mip-mapped texture (Texture.cpp:50): the
+// positive modulo is the low bits, for negative values too (two's complement); the same integer without the ~40
+// instructions of a division by a run-time divisor (4 % of the kernel's instructions under EWA filtering).
+__device__ __forceinline__ int positive_mod_pow2(int value, int modulus) { return value & (modulus - 1); }
 
 __device__ __forceinline__ v3 transform_position(const Affine & m, v3 p) {
 	return V(__fmaf_rn(m.r0.x, p.x, __fmaf_rn(m.r0.y, p.y, __fmaf_rn(m.r0.z, p.z, m.r0.w))),

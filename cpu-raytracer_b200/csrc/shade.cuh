@@ -182,19 +182,20 @@ __device__ __forceinline__ const Texel * texel_pool(const SceneParams & P) { ret
 
 struct TexView { const Texel * texels; int width, height, mip_levels; const int * mip_offsets; };
 
-// Texture::fetch_texel, Texture.cpp:131-147 (repeat wrap by positive modulo)
-template<bool COUNT>
+// Texture::fetch_texel, Texture.cpp:131-147 (repeat wrap by positive modulo). POW2: the caller is one of the mip-map
+// filters, which only ever see mip-mapped textures, and those have power-of-two sides (Texture.cpp:50).
+template<bool COUNT, bool POW2 = false>
 __device__ __forceinline__ v3 fetch_texel(const TexView & tex, int x, int y, int level, Counters & cnt) {
 	const int level_width  = tex.width  >> level;
 	const int level_height = tex.height >> level;
-	x = positive_mod(x, level_width);
-	y = positive_mod(y, level_height);
+	x = POW2 ? positive_mod_pow2(x, level_width)  : positive_mod(x, level_width);
+	y = POW2 ? positive_mod_pow2(y, level_height) : positive_mod(y, level_height);
 	if (COUNT) cnt.texels++;
 	return texel_rgb(tex.texels + (__ldg(tex.mip_offsets + level) + x + y * level_width));
 }
 
 // Texture::sample_bilinear, Texture.cpp:156-186
-template<bool COUNT>
+template<bool COUNT, bool POW2 = false>
 __device__ __forceinline__ v3 sample_bilinear(const TexView & tex, float s, float t, int level, Counters & cnt) {
 	const int level_width  = tex.width  >> level;
 	const int level_height = tex.height >> level;
@@ -216,10 +217,10 @@ __device__ __forceinline__ v3 sample_bilinear(const TexView & tex, float s, floa
 	const int int_s = float_to_int(s - 0.5f);
 	const int int_t = float_to_int(t - 0.5f);
 
-	const v3 c0 = fetch_texel<COUNT>(tex, int_s,     int_t,     level, cnt) * w0;
-	const v3 c1 = fetch_texel<COUNT>(tex, int_s + 1, int_t,     level, cnt) * w1;
-	const v3 c2 = fetch_texel<COUNT>(tex, int_s,     int_t + 1, level, cnt) * w2;
-	const v3 c3 = fetch_texel<COUNT>(tex, int_s + 1, int_t + 1, level, cnt) * w3;
+	const v3 c0 = fetch_texel<COUNT, POW2>(tex, int_s,     int_t,     level, cnt) * w0;
+	const v3 c1 = fetch_texel<COUNT, POW2>(tex, int_s + 1, int_t,     level, cnt) * w1;
+	const v3 c2 = fetch_texel<COUNT, POW2>(tex, int_s,     int_t + 1, level, cnt) * w2;
+	const v3 c3 = fetch_texel<COUNT, POW2>(tex, int_s + 1, int_t + 1, level, cnt) * w3;
 	return ((c0 + c1) + c2) + c3;
 }
 
@@ -231,11 +232,11 @@ __device__ v3 sample_trilinear(const TexView & tex, float s, float t, float ds_d
 	const float lambda = float(tex.mip_levels) - 1.0f + log2f(std_max(width, 1e-8f));
 	const int   level  = float_to_int(lambda - 0.5f);
 
-	if (level < 0)                   return sample_bilinear<COUNT>(tex, s, t, 0, cnt);
-	if (level >= tex.mip_levels - 1) return fetch_texel<COUNT>(tex, 0, 0, tex.mip_levels - 1, cnt);
+	if (level < 0)                   return sample_bilinear<COUNT, true>(tex, s, t, 0, cnt);
+	if (level >= tex.mip_levels - 1) return fetch_texel<COUNT, true>(tex, 0, 0, tex.mip_levels - 1, cnt);
 
 	const float f = lambda - floorf(lambda);
-	return sample_bilinear<COUNT>(tex, s, t, level, cnt) * (1.0f - f) + sample_bilinear<COUNT>(tex, s, t, level + 1, cnt) * f;
+	return sample_bilinear<COUNT, true>(tex, s, t, level, cnt) * (1.0f - f) + sample_bilinear<COUNT, true>(tex, s, t, level + 1, cnt) * f;
 }
 
 // Texture::sample_mipmap_anisotropic, Texture.cpp:207-239
@@ -253,8 +254,8 @@ __device__ v3 sample_anisotropic(const TexView & tex, float max_anisotropy, floa
 	const float lambda = float(tex.mip_levels) - 1.0f + log2f(p_max * one_over_N);
 	const int   level  = float_to_int(lambda);
 
-	if (level < 0)                   return sample_bilinear<COUNT>(tex, s, t, 0, cnt);
-	if (level >= tex.mip_levels - 1) return fetch_texel<COUNT>(tex, 0, 0, tex.mip_levels - 1, cnt);
+	if (level < 0)                   return sample_bilinear<COUNT, true>(tex, s, t, 0, cnt);
+	if (level >= tex.mip_levels - 1) return fetch_texel<COUNT, true>(tex, 0, 0, tex.mip_levels - 1, cnt);
 
 	const bool  x_major = p_x > p_y;
 	const float step_s = x_major ? ds_dx : ds_dy;
@@ -266,7 +267,7 @@ __device__ v3 sample_anisotropic(const TexView & tex, float max_anisotropy, floa
 	for (float i = 1.0f; i <= N + 0.001f; i += 1.0f) {
 		const float x = s + step_s * (i * one_over_N_plus_1 - 0.5f);
 		const float y = t + step_t * (i * one_over_N_plus_1 - 0.5f);
-		sum = sum + sample_bilinear<COUNT>(tex, x, y, level, cnt);
+		sum = sum + sample_bilinear<COUNT, true>(tex, x, y, level, cnt);
 	}
 	return sum * one_over_N;
 }
@@ -286,8 +287,8 @@ __device__ v3 sample_ewa(const TexView & tex, float max_anisotropy, float s, flo
 		major_x = tx; major_y = ty; major_length = tl;
 	}
 
-	if (minor_length < 0.00001f) return sample_bilinear<COUNT>(tex, s, t, 0, cnt);
-	if (major_length > float(tex.width)) return fetch_texel<COUNT>(tex, 0, 0, tex.mip_levels - 1, cnt);
+	if (minor_length < 0.00001f) return sample_bilinear<COUNT, true>(tex, s, t, 0, cnt);
+	if (major_length > float(tex.width)) return fetch_texel<COUNT, true>(tex, 0, 0, tex.mip_levels - 1, cnt);
 
 	if (minor_length * max_anisotropy < major_length) { // clamp the eccentricity
 		const float scale = major_length / (minor_length * max_anisotropy);
@@ -298,7 +299,7 @@ __device__ v3 sample_ewa(const TexView & tex, float max_anisotropy, float s, flo
 	const float lambda = std_max(0.0f, float(tex.mip_levels) - 1.0f + log2f(minor_length));
 	const int   level  = float_to_int(lambda);
 
-	if (level >= tex.mip_levels - 1) return fetch_texel<COUNT>(tex, 0, 0, tex.mip_levels - 1, cnt);
+	if (level >= tex.mip_levels - 1) return fetch_texel<COUNT, true>(tex, 0, 0, tex.mip_levels - 1, cnt);
 
 	const float level_width  = float(tex.width  >> level);
 	const float level_height = float(tex.height >> level);
@@ -344,7 +345,7 @@ __device__ v3 sample_ewa(const TexView & tex, float max_anisotropy, float s, flo
 				int index = float_to_int(r2 * 128.0f);
 				if (index > 127) index = 127;
 				const float weight = c_ewa_weight_table[index];
-				sum = sum + fetch_texel<COUNT>(tex, si, ti, level, cnt) * weight;
+				sum = sum + fetch_texel<COUNT, true>(tex, si, ti, level, cnt) * weight;
 				sum_weights += weight;
 			}
 		}
