@@ -155,7 +155,7 @@ typedef struct {
 	/* B200RT_ARITHMETIC_*. EXACT (0, the default): every operation in the reference's association order, a multiply-add
 	 * fused exactly where the reference calls madd / msub (SIMD_Vector3.h:53-63, Matrix4.h:39-85) — primary-hit ids, hit
 	 * distances and the 8-bit image come out as the reference's bits. FAST: a second set of kernels compiled with
-	 * contraction and a cheaper box / triangle arithmetic, inside north_star's tolerance (>= 99.9 % ids, >= 50 dB) but
+	 * -use_fast_math (contraction, approximate division / square root / exp / log) and a cheaper box / triangle arithmetic, inside north_star's tolerance (>= 99.9 % ids, >= 50 dB) but
 	 * not bit-identical — the reference's own release build is of that kind (/fp:fast, Raytracer.vcxproj).            */
 	int32_t arithmetic;
 	/* Deep-pixel ray queue: 0 = every pixel's ray tree is walked depth-first by one thread;
