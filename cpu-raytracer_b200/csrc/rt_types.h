@@ -106,7 +106,11 @@ struct SceneParams {
 	int tlas_stack_entries;      // this frame's TLAS depth + 1
 };
 
+#ifdef RT_EMULATE
+#define RT_QUEUE_WATCHDOG_NS 900000000000ull // (tests/emu: an emulated frame takes seconds of real time, and a fibre that waits is not a stall)
+#else
 #define RT_QUEUE_WATCHDOG_NS 2000000000ull   // kernels.cuh: render_queue_kernel gives a frame up after waiting this long on unpublished items
+#endif
 
 struct FrameCounters {   // accumulated with one atomicAdd per warp
 	unsigned long long primary, shadow, reflection, refraction;
