@@ -163,7 +163,11 @@ typedef struct {
 	 * device-side queue that all persistent warps pop; 2 = every pixel whose primary hit spawns rays does;
 	 * 3 = AUTO: the context times both (setting 0 against setting 2)
 	 * on its own first frames from the kernels' %globaltimer stamps, keeps the faster and looks again every 4096 frames.
-	 * Same image bit for bit in every setting: the node values are combined in the reference's order.               */
+	 * Same image bit for bit in every setting: the node values are combined in the reference's order.
+	 * Last line of defence: should the queued kernel ever wait 2 s on an item that does not appear, it gives the frame
+	 * up; b200rt_render_frame / b200rt_render_frame_device (with stats) then render the frame again depth-first,
+	 * b200rt_wait_frame / b200rt_last_frame_stats report the frame as failed (submit it again), and the context walks
+	 * depth-first from then on. Never observed with the shipped kernel (tools/queue_stress.py).                      */
 	int32_t deep_queue;
 } b200rt_config;
 enum { B200RT_ARITHMETIC_EXACT = 0, B200RT_ARITHMETIC_FAST = 1 };
