@@ -166,7 +166,7 @@ render_queue_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, f
 		if (kind == WORK_NONE || kind == WORK_VOID) break;
 		if (kind == WORK_WAIT) {
 			if (lane == 0 && idle_looks == 0) atomicMax(&counters->first_idle_ns, ~global_timer_ns());
-			__nanosleep(2000u << min(idle_looks, 2));
+			__nanosleep(2000u << min(idle_looks, P.queue_idle_shift));
 			idle_looks++;
 			continue;
 		}
@@ -217,18 +217,33 @@ render_queue_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, f
 				ticket = NO_TICKET;
 				if (q.parent == QUEUE_NULL_ITEM) active = false; else settled = 1;
 			}
+#ifdef RT_QUEUE_TRACE   // development: when was the last walk of each level picked up / finished (us since the launch began), how many
+			const int trace_level = kind == WORK_UNIT ? 9 : bounces_left;
+			if (active) {
+				const unsigned now_us = unsigned((global_timer_ns() - ~counters->first_start_ns) >> 10);
+				atomicMax(&counters->q_pad0[trace_level], now_us);
+				atomicAdd(&counters->q_pad0[18 + (trace_level > 9 ? 9 : trace_level)], 1u);
+			}
+#endif
+			bool exported = false;
 			if (active) {
 				float distance;
-				bool exported = false;
 				const v3 colour = shade_subtree_body<false, MAXB, BSTACK, true>(P, ray, bounces_left, cnt, distance, &q, exported);
+#ifdef RT_QUEUE_TRACE
+				atomicMax(&counters->q_pad1[trace_level], unsigned((global_timer_ns() - ~counters->first_start_ns) >> 10));
+#endif
 				if (!exported) {
 					if (q.parent < 0) { const int p = -(q.parent + 1); write_pixel(P, out, p % P.width, p / P.width, colour); }
 					else deliver(P, out, q.parent, q.which, colour, distance);
 				}
 			}
 			if (kind == WORK_UNIT) {
-				__syncwarp();
-				if (lane == 0) { atomicAdd(P.tile_cost + local_tile, unsigned((clock64() - unit_begin) >> 6)); settled = 1; }   // the unit itself
+				// What this tile cost, for the next frame's hand-out order. The subtrees this unit exported are walked by
+				// others, later: their time is not in this clock, and without it every tile looks cheap and the tiles whose
+				// pixels spawn the frame's longest chains are handed out anywhere — at the end, too, and the launch then
+				// waits for chains that started late. An exported pixel is booked at what a deep pixel costs depth-first.
+				const unsigned exports = unsigned(__popc(__ballot_sync(0xffffffffu, exported)));
+				if (lane == 0) { atomicAdd(P.tile_cost + local_tile, unsigned((clock64() - unit_begin) >> 6) + exports * RT_QUEUE_EXPORT_COST); settled = 1; }   // the unit itself
 			}
 		}
 		warp_add(&counters->q_outstanding, -settled);   // what a walk queued was added before it became visible (export_node)

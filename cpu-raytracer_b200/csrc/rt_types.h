@@ -101,11 +101,13 @@ struct SceneParams {
 	unsigned frame_serial;       // never 0, different for every launch of a context
 	int queue_mode;              // 0 off; 1: pixels whose primary ray hits a transmissive material; 2: every pixel whose primary hit spawns rays
 	int queue_inline_below;      // a popped ray with at most this many bounces left is walked to the end by the thread that popped it
-	int queue_idle_looks;        // a warp that finds neither item nor unit looks this many times more (2 / 4 / 8 / 8 ... us apart) before it leaves
+	int queue_idle_looks;        // a warp that finds neither item nor unit looks this many times more (2 / 4 / 8 / ... us apart) before it leaves
+	int queue_idle_shift;        // ... the pause doubles this many times at most (2: 8 us)
 	int blas_stack_entries;      // deepest BLAS + 1: what a push-both-pop-one traversal can hold
 	int tlas_stack_entries;      // this frame's TLAS depth + 1
 };
 
+#define RT_QUEUE_EXPORT_COST 300u   // tile cost (clock64 >> 6) booked per pixel whose ray tree went to the queue: ~10 us, a deep pixel's depth-first share of its unit
 #ifdef RT_EMULATE
 #define RT_QUEUE_WATCHDOG_NS 900000000000ull // (tests/emu: an emulated frame takes seconds of real time, and a fibre that waits is not a stall)
 #else

@@ -11,7 +11,7 @@ _, scene = bench.build_scene(w)
 pack = scene.pack()
 r = Renderer(w["width"], w["height"], w["bounces"], w["filter"])
 r.upload_static(pack)
-for _ in range(4):
+for _ in range(6):     # the tile order needs a few frames to settle on the measured costs
     stats = r.render(pack)["stats"]
 print(stats["device_ms_render"], stats["device_ms_fxaa"])
 r.close()
