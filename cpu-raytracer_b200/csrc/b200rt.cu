@@ -840,6 +840,7 @@ extern "C" int b200rt_last_frame_stats(b200rt_ctx * ctx, b200rt_stats * stats) {
 	CHECK_CUDA(ctx, cudaMemcpy(ctx->pinned_counters, counter_block(ctx, ctx->frame_number - 1), sizeof(FrameCounters), cudaMemcpyDeviceToHost));
 	const FrameCounters & c = *ctx->pinned_counters;
 #ifdef RT_QUEUE_TRACE
+	if (c.q_pad0[10]) fprintf(stderr, "trace items: %u warp iterations, %.1f lanes each on average; iterations with 1 / 2-3 / 4-7 / 8-15 / 16-32 lanes: %u / %u / %u / %u / %u\n", c.q_pad0[10], double(c.q_pad0[11]) / c.q_pad0[10], c.q_pad0[12], c.q_pad0[13], c.q_pad0[14], c.q_pad0[15], c.q_pad0[16]);
 	for (int level = 9; level >= 0; level--) if (c.q_pad0[18 + level]) fprintf(stderr, "trace level %d: %u walks, last picked up at %u us, last finished at %u us\n", level, c.q_pad0[18 + level], c.q_pad0[level], c.q_pad1[level]);
 #endif
 	if (queue_stalled(ctx, c)) return fail(ctx, "the deep-pixel queue stalled in the last frame: its image is incomplete; render it again (the context has switched to the depth-first walk)");

@@ -219,6 +219,10 @@ render_queue_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, f
 			}
 #ifdef RT_QUEUE_TRACE   // development: when was the last walk of each level picked up / finished (us since the launch began), how many
 			const int trace_level = kind == WORK_UNIT ? 9 : bounces_left;
+			if (kind != WORK_UNIT) { // how full are the warps that walk items? [10] iterations, [11] lanes with an item, [12..16] iterations by fill (1, 2-3, 4-7, 8-15, 16-32 lanes)
+				const unsigned lanes = unsigned(__popc(__ballot_sync(0xffffffffu, active)));
+				if (lane == 0 && lanes > 0u) { atomicAdd(&counters->q_pad0[10], 1u); atomicAdd(&counters->q_pad0[11], lanes); atomicAdd(&counters->q_pad0[12 + (lanes >= 16u ? 4 : lanes >= 8u ? 3 : lanes >= 4u ? 2 : lanes >= 2u ? 1 : 0)], 1u); }
+			}
 			if (active) {
 				const unsigned now_us = unsigned((global_timer_ns() - ~counters->first_start_ns) >> 10);
 				atomicMax(&counters->q_pad0[trace_level], now_us);

@@ -274,19 +274,20 @@ struct QueueContext { FrameCounters * counters; int parent, which; };
 // bounce slot per child (one or two), taken with ONE 64-bit atomicAdd on the pair of cursors (records in the low word,
 // bounce slots in the high word), and the children added to the frame's outstanding work with one more — an export
 // used to cost two dependent atomics per group and a third per lane on one address.
-__device__ __forceinline__ void group_reserve_export(FrameCounters * counters, int n_children, unsigned & node_slot, unsigned & bounce_slot) {
+__device__ __forceinline__ void group_reserve_export(FrameCounters * counters, const bool has_child[2], unsigned & node_slot, unsigned child_slot[2]) {
 	unsigned long long * cursors = reinterpret_cast<unsigned long long *>(&counters->q_node_reserved);   // {q_node_reserved, q_bounce_reserved}
 #ifdef RT_EMULATE
+	const int n_children = (has_child[0] ? 1 : 0) + (has_child[1] ? 1 : 0);
 	const unsigned long long old = atomicAdd(cursors, 1ull | (static_cast<unsigned long long>(n_children) << 32));
 	atomicAdd(&counters->q_outstanding, n_children);
-	node_slot = unsigned(old); bounce_slot = unsigned(old >> 32);
+	node_slot = unsigned(old); child_slot[0] = unsigned(old >> 32); child_slot[1] = child_slot[0] + (has_child[0] ? 1u : 0u);
 #else
 	const unsigned mask = __activemask();
-	const unsigned twos = __ballot_sync(mask, n_children == 2);
+	const unsigned reflecting = __ballot_sync(mask, has_child[0]), refracting = __ballot_sync(mask, has_child[1]);
 	const int lane = threadIdx.x & 31, leader = __ffs(mask) - 1;
 	unsigned lo = 0, hi = 0;
 	if (lane == leader) {
-		const unsigned records = unsigned(__popc(mask)), children = records + unsigned(__popc(twos));
+		const unsigned records = unsigned(__popc(mask)), children = unsigned(__popc(reflecting) + __popc(refracting));
 		const unsigned long long old = atomicAdd(cursors, static_cast<unsigned long long>(records) | (static_cast<unsigned long long>(children) << 32));
 		// before anything is visible: the count never runs low. The returned value is USED, so the add has been performed
 		// at L2 before the shuffle below hands out the slots — every lane's stores (payload, fence, ready word) are issued
@@ -298,7 +299,12 @@ __device__ __forceinline__ void group_reserve_export(FrameCounters * counters, i
 	__syncwarp(mask);
 	const unsigned below = (1u << lane) - 1u;
 	node_slot = lo + unsigned(__popc(mask & below));
-	bounce_slot = hi + unsigned(__popc(mask & below) + __popc(twos & below));
+	// the group's reflection rays first, then its refraction rays, each in lane order: the lanes of a group are
+	// neighbouring pixels, and whoever draws 32 consecutive tickets gets rays of one kind from one neighbourhood —
+	// a coherent warp. (Slots in arrival order — reflection, refraction, reflection, ... — made every consumer warp
+	// a mix of two ray populations; profiles/r02_queue_trace_*.txt: a level of the queue took as long as 3-5 such walks.)
+	child_slot[0] = hi + unsigned(__popc(reflecting & below));
+	child_slot[1] = hi + unsigned(__popc(reflecting) + __popc(refracting & below));
 #endif
 }
 
@@ -308,14 +314,15 @@ __device__ __forceinline__ bool export_node(const SceneParams & P, const QueueCo
                                             const Ray & reflected, const Ray & refracted, int bounces_left, Counters & cnt) {
 	const bool has_child[2] = { (flags & FRAME_HAS_REFLECTION) != 0, (flags & FRAME_HAS_REFRACTION) && !(flags & FRAME_TIR) };
 	const int n_children = (has_child[0] ? 1 : 0) + (has_child[1] ? 1 : 0);
-	const unsigned slots = unsigned(n_children);
-	unsigned node_slot, bounce_slot;
-	group_reserve_export(q.counters, n_children, node_slot, bounce_slot);
-	if (node_slot >= P.q_node_capacity || bounce_slot + slots > P.q_bounce_capacity) {
+	unsigned node_slot, child_slot[2];
+	group_reserve_export(q.counters, has_child, node_slot, child_slot);
+	const bool fits = node_slot < P.q_node_capacity && (!has_child[0] || child_slot[0] < P.q_bounce_capacity) && (!has_child[1] || child_slot[1] < P.q_bounce_capacity);
+	// (each lane checks ITS OWN slots; a lane that does not fit publishes those of its slots that lie inside the pool as null items)
+	if (!fits) {
 		// a pool is exhausted. Bounce slots inside the pool must still be published (somebody may hold a ticket for them): as null items
-		for (unsigned k = 0; k < slots; k++) if (bounce_slot + k < P.q_bounce_capacity) __stcg(P.q_bounce + 5 * size_t(bounce_slot + k) + 4, make_float4(0.0f, 0.0f, as_f(QUEUE_NULL_ITEM), 0.0f));
+		for (int k = 0; k < 2; k++) if (has_child[k] && child_slot[k] < P.q_bounce_capacity) __stcg(P.q_bounce + 5 * size_t(child_slot[k]) + 4, make_float4(0.0f, 0.0f, as_f(QUEUE_NULL_ITEM), 0.0f));
 		__threadfence();
-		for (unsigned k = 0; k < slots; k++) if (bounce_slot + k < P.q_bounce_capacity) __stcg(P.q_bounce_ready + bounce_slot + k, P.frame_serial);
+		for (int k = 0; k < 2; k++) if (has_child[k] && child_slot[k] < P.q_bounce_capacity) __stcg(P.q_bounce_ready + child_slot[k], P.frame_serial);
 		atomicSub(&q.counters->q_outstanding, n_children);   // they will not become work (the walk that queued nothing still holds its own count)
 		atomicAdd(&q.counters->q_fallbacks, 1u);
 		return false;
@@ -328,14 +335,13 @@ __device__ __forceinline__ bool export_node(const SceneParams & P, const QueueCo
 	__stcg(rec + 2, make_float4(hit.normal.x, hit.normal.y, hit.normal.z, F_r));
 	__stcg(rec + 3, make_float4(result.x, result.y, result.z, 0.0f));
 	// payloads, ONE fence, then the ready words: record and items are in L2 before any consumer can see an item that names the record
-	unsigned slot = bounce_slot;
 	for (int k = 0; k < 2; k++) {
 		if (!has_child[k]) continue;
 		if (k == 0) cnt.reflection++; else cnt.refraction++;
-		write_bounce_item(P, slot++, k == 0 ? reflected : refracted, node, k, bounces_left - 1);
+		write_bounce_item(P, child_slot[k], k == 0 ? reflected : refracted, node, k, bounces_left - 1);
 	}
 	__threadfence();
-	for (unsigned k = 0; k < slots; k++) __stcg(P.q_bounce_ready + bounce_slot + k, P.frame_serial);
+	for (int k = 0; k < 2; k++) if (has_child[k]) __stcg(P.q_bounce_ready + child_slot[k], P.frame_serial);
 	return true;
 }
 

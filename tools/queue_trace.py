@@ -13,7 +13,7 @@ scene, (w, h, bounces, filt) = variant_bench.build_scene(name)
 pack = scene.pack()
 r = Renderer(w, h, bounces, filt, tile_stride=stride, tile_phase=0, deep_queue=queue)
 r.upload_static(pack)
-for i in range(4):
+for i in range(6):
     out = r.render(pack, want_presented=False)
 print(name, "stride", stride, "queue", queue, "render ms", out["stats"]["device_ms_render"], "tail", out["stats"]["device_ms_tail"], file=sys.stderr)
 r.last_frame_stats()
