@@ -154,7 +154,7 @@ render_queue_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, f
 			const unsigned free_lanes = 32u - unsigned(__popc(holding));
 			const unsigned hb = peek(&counters->q_bounce_head), rb = min(peek(&counters->q_bounce_reserved), P.q_bounce_capacity), ab = rb > hb ? rb - hb : 0u;
 			if (peek(&counters->q_abort) != 0u) kind = WORK_VOID;
-			else if (holding || ab >= 32u || (ab > 0u && !units_left)) kind = WORK_BOUNCE;
+			else if (holding || ab >= unsigned(P.queue_item_batch) || (ab > 0u && !units_left)) kind = WORK_BOUNCE;
 			if (kind == WORK_BOUNCE && ab > 0u && free_lanes > 0u) { n = min(ab, free_lanes); first = atomicAdd(&counters->q_bounce_head, n); }
 			if (kind == WORK_NONE && units_left) {
 				first = atomicAdd(&counters->next_unit, 1u);
