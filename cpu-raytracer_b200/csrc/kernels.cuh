@@ -236,10 +236,9 @@ render_queue_kernel(const SceneParams P, unsigned * __restrict__ frame_buffer, f
 #ifdef RT_QUEUE_TRACE
 				atomicMax(&counters->q_pad1[trace_level], unsigned((global_timer_ns() - ~counters->first_start_ns) >> 10));
 #endif
-				if (!exported) {
-					if (q.parent < 0) { const int p = -(q.parent + 1); write_pixel(P, out, p % P.width, p / P.width, colour); }
-					else deliver(P, out, q.parent, q.which, colour, distance);
-				}
+				// the walk's value goes to its parent: the pixel, or the record the walk last exported (the walk went on below it)
+				if (q.parent < 0) { const int p = -(q.parent + 1); write_pixel(P, out, p % P.width, p / P.width, colour); }
+				else deliver(P, out, q.parent, q.which, colour, distance);
 			}
 			if (kind == WORK_UNIT) {
 				// What this tile cost, for the next frame's hand-out order. The subtrees this unit exported are walked by

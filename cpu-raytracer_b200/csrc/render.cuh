@@ -270,60 +270,59 @@ __device__ __forceinline__ void read_bounce_item(const SceneParams & P, unsigned
 struct QueueContext { FrameCounters * counters; int parent, which; };
 
 // One reservation for everything an export needs, for the lanes that happen to stand here together (whoever is converged
-// at this point — any grouping is correct, a larger one is cheaper): a node record per lane and a
-// bounce slot per child (one or two), taken with ONE 64-bit atomicAdd on the pair of cursors (records in the low word,
-// bounce slots in the high word), and the children added to the frame's outstanding work with one more — an export
-// used to cost two dependent atomics per group and a third per lane on one address.
-__device__ __forceinline__ void group_reserve_export(FrameCounters * counters, const bool has_child[2], unsigned & node_slot, unsigned child_slot[2]) {
+// at this point — any grouping is correct, a larger one is cheaper): a node record per lane and an item slot per lane
+// that queues a child, taken with ONE 64-bit atomicAdd on the pair of cursors (records in the low word, item slots in
+// the high word), and the queued children added to the frame's outstanding work with one more.
+__device__ __forceinline__ void group_reserve_export(FrameCounters * counters, bool queues_a_child, unsigned & node_slot, unsigned & item_slot) {
 	unsigned long long * cursors = reinterpret_cast<unsigned long long *>(&counters->q_node_reserved);   // {q_node_reserved, q_bounce_reserved}
 #ifdef RT_EMULATE
-	const int n_children = (has_child[0] ? 1 : 0) + (has_child[1] ? 1 : 0);
-	const unsigned long long old = atomicAdd(cursors, 1ull | (static_cast<unsigned long long>(n_children) << 32));
-	atomicAdd(&counters->q_outstanding, n_children);
-	node_slot = unsigned(old); child_slot[0] = unsigned(old >> 32); child_slot[1] = child_slot[0] + (has_child[0] ? 1u : 0u);
+	const unsigned long long old = atomicAdd(cursors, 1ull | (static_cast<unsigned long long>(queues_a_child ? 1 : 0) << 32));
+	if (queues_a_child) atomicAdd(&counters->q_outstanding, 1);
+	node_slot = unsigned(old); item_slot = unsigned(old >> 32);
 #else
 	const unsigned mask = __activemask();
-	const unsigned reflecting = __ballot_sync(mask, has_child[0]), refracting = __ballot_sync(mask, has_child[1]);
+	const unsigned queueing = __ballot_sync(mask, queues_a_child);
 	const int lane = threadIdx.x & 31, leader = __ffs(mask) - 1;
 	unsigned lo = 0, hi = 0;
 	if (lane == leader) {
-		const unsigned records = unsigned(__popc(mask)), children = unsigned(__popc(reflecting) + __popc(refracting));
-		const unsigned long long old = atomicAdd(cursors, static_cast<unsigned long long>(records) | (static_cast<unsigned long long>(children) << 32));
+		const unsigned records = unsigned(__popc(mask)), items = unsigned(__popc(queueing));
+		const unsigned long long old = atomicAdd(cursors, static_cast<unsigned long long>(records) | (static_cast<unsigned long long>(items) << 32));
 		// before anything is visible: the count never runs low. The returned value is USED, so the add has been performed
 		// at L2 before the shuffle below hands out the slots — every lane's stores (payload, fence, ready word) are issued
 		// after that; a consumer that sees an item of this group cannot bring the count to zero ahead of this add.
-		const int before = atomicAdd(&counters->q_outstanding, int(children));
+		const int before = atomicAdd(&counters->q_outstanding, int(items));
 		lo = unsigned(old) + (before == int(0x80000000u) ? 1u : 0u); hi = unsigned(old >> 32);
 	}
 	lo = __shfl_sync(mask, lo, leader); hi = __shfl_sync(mask, hi, leader);
 	__syncwarp(mask);
 	const unsigned below = (1u << lane) - 1u;
 	node_slot = lo + unsigned(__popc(mask & below));
-	// the group's reflection rays first, then its refraction rays, each in lane order: the lanes of a group are
-	// neighbouring pixels, and whoever draws 32 consecutive tickets gets rays of one kind from one neighbourhood —
-	// a coherent warp. (Slots in arrival order — reflection, refraction, reflection, ... — made every consumer warp
-	// a mix of two ray populations; profiles/r02_queue_trace_*.txt: a level of the queue took as long as 3-5 such walks.)
-	child_slot[0] = hi + unsigned(__popc(reflecting & below));
-	child_slot[1] = hi + unsigned(__popc(reflecting) + __popc(refracting & below));
+	// the group's items in lane order: the lanes of a group are neighbouring pixels and the items are all refraction rays,
+	// so whoever draws 32 consecutive tickets gets a coherent warp
+	item_slot = hi + unsigned(__popc(queueing & below));
 #endif
 }
 
-// Exports the top node of a walk: record and children. Returns false when a pool is exhausted (nothing has been
-// published then, and the caller goes on walking). result: the node's finished direct lighting.
+// Exports the top node of a walk as a record. The walking thread then goes on with ONE child itself, as a new walk whose
+// parent is the record, and only the OTHER child of a node that has two goes to the queue (queued_ray, queued_which): a chain of single-child nodes stays in its thread without a
+// single queue round trip, a fan-out splits off exactly one item, and the rays that stay are the coherent ones (the
+// warp's neighbouring pixels, one level down). Returns false when a pool is exhausted (nothing has been published then,
+// and the caller goes on walking depth-first). result: the node's finished direct lighting; node_out: the record.
 __device__ __forceinline__ bool export_node(const SceneParams & P, const QueueContext & q, const HitRecord & hit, float distance, int flags, float F_r, v3 result,
-                                            const Ray & reflected, const Ray & refracted, int bounces_left, Counters & cnt) {
+                                            const Ray & queued_ray, int queued_which, int bounces_left, Counters & cnt, int & node_out) {
 	const bool has_child[2] = { (flags & FRAME_HAS_REFLECTION) != 0, (flags & FRAME_HAS_REFRACTION) && !(flags & FRAME_TIR) };
 	const int n_children = (has_child[0] ? 1 : 0) + (has_child[1] ? 1 : 0);
-	unsigned node_slot, child_slot[2];
-	group_reserve_export(q.counters, has_child, node_slot, child_slot);
-	const bool fits = node_slot < P.q_node_capacity && (!has_child[0] || child_slot[0] < P.q_bounce_capacity) && (!has_child[1] || child_slot[1] < P.q_bounce_capacity);
-	// (each lane checks ITS OWN slots; a lane that does not fit publishes those of its slots that lie inside the pool as null items)
-	if (!fits) {
-		// a pool is exhausted. Bounce slots inside the pool must still be published (somebody may hold a ticket for them): as null items
-		for (int k = 0; k < 2; k++) if (has_child[k] && child_slot[k] < P.q_bounce_capacity) __stcg(P.q_bounce + 5 * size_t(child_slot[k]) + 4, make_float4(0.0f, 0.0f, as_f(QUEUE_NULL_ITEM), 0.0f));
-		__threadfence();
-		for (int k = 0; k < 2; k++) if (has_child[k] && child_slot[k] < P.q_bounce_capacity) __stcg(P.q_bounce_ready + child_slot[k], P.frame_serial);
-		atomicSub(&q.counters->q_outstanding, n_children);   // they will not become work (the walk that queued nothing still holds its own count)
+	const bool queues_a_child = n_children == 2;
+	unsigned node_slot, item_slot;
+	group_reserve_export(q.counters, queues_a_child, node_slot, item_slot);
+	if (node_slot >= P.q_node_capacity || (queues_a_child && item_slot >= P.q_bounce_capacity)) {
+		// a pool is exhausted. An item slot inside the pool must still be published (somebody may hold a ticket for it): as a null item
+		if (queues_a_child && item_slot < P.q_bounce_capacity) {
+			__stcg(P.q_bounce + 5 * size_t(item_slot) + 4, make_float4(0.0f, 0.0f, as_f(QUEUE_NULL_ITEM), 0.0f));
+			__threadfence();
+			__stcg(P.q_bounce_ready + item_slot, P.frame_serial);
+		}
+		if (queues_a_child) atomicSub(&q.counters->q_outstanding, 1);   // it will not become work (the walk that queued nothing still holds its own count)
 		atomicAdd(&q.counters->q_fallbacks, 1u);
 		return false;
 	}
@@ -334,14 +333,15 @@ __device__ __forceinline__ bool export_node(const SceneParams & P, const QueueCo
 	__stcg(rec + 1, make_float4(hit.point.x, hit.point.y, hit.point.z, distance));
 	__stcg(rec + 2, make_float4(hit.normal.x, hit.normal.y, hit.normal.z, F_r));
 	__stcg(rec + 3, make_float4(result.x, result.y, result.z, 0.0f));
-	// payloads, ONE fence, then the ready words: record and items are in L2 before any consumer can see an item that names the record
-	for (int k = 0; k < 2; k++) {
-		if (!has_child[k]) continue;
-		if (k == 0) cnt.reflection++; else cnt.refraction++;
-		write_bounce_item(P, child_slot[k], k == 0 ? reflected : refracted, node, k, bounces_left - 1);
+	if (queues_a_child) { // payload, ONE fence, then the ready word: record and item are in L2 before any consumer can see the item that names the record
+		if (queued_which == 0) cnt.reflection++; else cnt.refraction++;
+		write_bounce_item(P, item_slot, queued_ray, node, queued_which, bounces_left - 1);
+		__threadfence();
+		__stcg(P.q_bounce_ready + item_slot, P.frame_serial);
+	} else {
+		__threadfence();   // the record is in L2 before this thread's own delivery into it (or a descendant's) can complete it
 	}
-	__threadfence();
-	for (int k = 0; k < 2; k++) if (has_child[k]) __stcg(P.q_bounce_ready + child_slot[k], P.frame_serial);
+	node_out = node;
 	return true;
 }
 
@@ -366,7 +366,7 @@ struct BounceFrame {
 // q.parent >= 0: the walk is a popped item's — more than queue_inline_below bounces left); `exported` then comes back
 // true and the returned colour means nothing: the pixel is written by whoever completes the root record.
 template<bool COUNT, int MAXB, int BSTACK, bool QUEUE>
-__device__ __forceinline__ v3 shade_subtree_body(const SceneParams & P, Ray ray, int bounces_left, Counters & cnt, float & distance_out, const QueueContext * q, bool & exported) {
+__device__ __forceinline__ v3 shade_subtree_body(const SceneParams & P, Ray ray, int bounces_left, Counters & cnt, float & distance_out, QueueContext * q, bool & exported) {
 	BounceFrame frames[MAXB];
 	int depth = 0;                // number of pending frames = recursion depth of the current ray
 
@@ -448,10 +448,19 @@ __device__ __forceinline__ v3 shade_subtree_body(const SceneParams & P, Ray ray,
 					if (QUEUE && may_export) {
 						const int node_flags = flags | (reflection_mask ? FRAME_HAS_REFLECTION : 0);
 						const bool any_child = reflection_mask || ((flags & FRAME_HAS_REFRACTION) && !(flags & FRAME_TIR));
-						if (any_child && export_node(P, *q, hit, best.t, node_flags, frame.F_r, result, reflected, frame.refracted, bounces_left, cnt)) {
+						int node;
+						// of two children the thread keeps one and queues the other (P.queue_keep_refraction: which)
+						const bool refraction_child = (flags & FRAME_HAS_REFRACTION) && !(flags & FRAME_TIR);
+						const bool keep_reflection = reflection_mask && !(refraction_child && P.queue_keep_refraction);
+						if (any_child && export_node(P, *q, hit, best.t, node_flags, frame.F_r, result, keep_reflection ? frame.refracted : reflected, keep_reflection ? 1 : 0, bounces_left, cnt, node)) {
+							// the node is a record now; this thread goes on with one of its children, as a walk of its own whose
+							// value is delivered into the record (the other child, if there is one, is in the queue)
 							exported = true;
-							distance_out = best.t;
-							return result;
+							if (keep_reflection) { cnt.reflection++; ray = reflected; q->which = 0; }
+							else                 { cnt.refraction++; ray = frame.refracted; q->which = 1; }
+							q->parent = node;
+							bounces_left--;
+							continue;   // depth is still 0 and `top` still true: the next hit is a top node again
 						}
 					}
 

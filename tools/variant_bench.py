@@ -2,7 +2,7 @@
 """Times kernel variants / run-time settings of libb200rt.so side by side (development tool).
 
     python tools/variant_bench.py SPEC [SPEC ...]
-    SPEC = label[,lib=path/to/libb200rt_x.so][,queue=off|glass|all|auto][,arith=exact|fast][,inline=N][,flush=0|1][,looks=N][,shift=N][,batch=N]
+    SPEC = label[,lib=path/to/libb200rt_x.so][,queue=off|glass|all|auto][,arith=exact|fast][,inline=N][,flush=0|1][,looks=N][,shift=N][,batch=N][,keep=0|1]
 
 Each SPEC runs in its own process (B200RT_LIB / B200RT_DEEP_QUEUE / B200RT_ARITHMETIC / B200RT_QUEUE_INLINE_BELOW
 select library and settings). First the golden fixtures are rendered and compared with the real reference's stored
@@ -125,6 +125,8 @@ def main():
                 env["B200RT_QUEUE_IDLE_SHIFT"] = value
             elif key == "batch":
                 env["B200RT_QUEUE_ITEM_BATCH"] = value
+            elif key == "keep":
+                env["B200RT_QUEUE_KEEP_REFRACTION"] = value
             else:
                 raise SystemExit("bad SPEC item " + item)
         try:
