@@ -40,11 +40,11 @@ def entry(path, what):
 CAP = "ncu --set full --metrics lts__t_bytes.sum,l1tex__t_bytes.sum,smsp__thread_inst_executed.sum --clock-control none --import-source on -k regex:%s -s 3 -c 1 on python tools/ncu_frame.py %s (B200RT_DEEP_QUEUE=%s), %s"
 out = {
     "what": "ncu figures of the render kernel per bench workload; bench.py's roofline record reads the entry of the workload it times (the '/queued' entry when the frame went through the deep-pixel queue). Instruction and byte counts of a launch do not depend on the box; times under ncu are not bench values.",
-    "launch_list": "profiles/r02_launches_bench.csv (bench.py --steps 2 --warmup 3 under ncu --metrics gpu__time_duration.sum --clock-control none, tools/gpu_call14.sh: render_kernel<0,3,32> 1.068 ms avg x 28, fxaa_kernel 0.0355 ms x 31, tile_schedule_kernel 0.0051 ms x 33 -> the render kernel is 96.3 % of a frame's kernel time; the live bench of the same call measures 1.027 of 1.070 ms = 96.0 %; the 3 render_queue_kernel launches are AUTO's comparison frames, the 2 render_kernel<1,8,64> the counting launches)",
+    "launch_list": "profiles/r02_launches_bench.csv (bench.py --steps 2 --warmup 3 under ncu --metrics gpu__time_duration.sum --clock-control none, tools/gpu_call28.sh: render_kernel<0,3,32> 1.054 ms avg x 28, fxaa_kernel 0.0356 ms x 31, tile_schedule_kernel 0.0046 ms x 33 -> the render kernel is 96.3 % of a frame's kernel time; the live bench of the same call measures 1.028 of 1.072 ms = 95.9 %; the 3 render_queue_kernel launches are AUTO's comparison frames, the 2 render_kernel<1,8,64> the counting launches)",
     "workloads": {
         "sponza1080": entry("profiles/r02_ncu_full_render_sponza1080.csv", CAP % ("render_kernel", "sponza1080", "off", "tools/gpu_call14.sh")),
         "dielectrics": entry("profiles/r02_ncu_full_render_dielectrics.csv", CAP % ("render_kernel", "dielectrics", "off", "tools/gpu_call14.sh")),
-        "dielectrics/queued": entry("profiles/r02_ncu_full_render_queue_dielectrics.csv", CAP % ("render_queue_kernel", "dielectrics", "all: AUTO's queued candidate", "tools/gpu_call24.sh, -s 5")),
+        "dielectrics/queued": entry("profiles/r02_ncu_full_render_queue_dielectrics.csv", CAP % ("render_queue_kernel", "dielectrics", "all: AUTO's queued candidate", "tools/gpu_call28.sh, -s 5")),
         "sibenik4k": entry("profiles/r02_ncu_full_render_sibenik4k.csv", CAP % ("render_kernel", "sibenik4k", "off", "tools/gpu_call14.sh")),
     },
     "fxaa": entry("profiles/r02_ncu_full_fxaa_sponza1080.csv", CAP % ("fxaa_kernel", "sponza1080", "off", "tools/gpu_call14.sh")),
