@@ -69,7 +69,7 @@ struct b200rt_ctx {
 	unsigned frame_number = 0;
 	// deep-pixel queue (render.cuh): pools, allocated on first use
 	DeviceBuffer q_nodes, q_bounce, q_bounce_ready;
-	int queue_inline_below = 0, queue_idle_looks = 3, queue_idle_shift = 2, queue_item_batch = 32, queue_keep_refraction = 0;
+	int queue_inline_below = 0, queue_idle_looks = 3, queue_idle_shift = 2, queue_item_batch = 32, queue_keep_refraction = 2;
 	bool queue_stalled = false;           // the queue kernel's watchdog fired once: this context renders depth-first from then on
 	bool test_stall = false;              // B200RT_TEST_QUEUE_STALL (tests): the first queued frame is marked as given up, to exercise the recovery
 	int blas_stack_entries = 1, tlas_stack_entries = 1;
@@ -176,7 +176,7 @@ extern "C" int b200rt_create(const b200rt_config * config, b200rt_ctx ** out) {
 	if (const char * text = getenv("B200RT_QUEUE_INLINE_BELOW")) ctx->queue_inline_below = atoi(text);   // tuning knobs (tools/): see SceneParams
 	if (const char * text = getenv("B200RT_TEST_QUEUE_STALL")) ctx->test_stall = atoi(text) != 0;
 	if (const char * text = getenv("B200RT_QUEUE_IDLE_LOOKS")) ctx->queue_idle_looks = atoi(text);
-	if (const char * text = getenv("B200RT_QUEUE_KEEP_REFRACTION")) ctx->queue_keep_refraction = atoi(text) != 0;
+	if (const char * text = getenv("B200RT_QUEUE_KEEP_REFRACTION")) ctx->queue_keep_refraction = std::max(0, std::min(atoi(text), 2));
 	if (const char * text = getenv("B200RT_QUEUE_ITEM_BATCH")) ctx->queue_item_batch = std::max(1, atoi(text));
 	if (const char * text = getenv("B200RT_QUEUE_IDLE_SHIFT")) ctx->queue_idle_shift = std::max(0, std::min(atoi(text), 8));
 

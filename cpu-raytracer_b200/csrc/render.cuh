@@ -451,7 +451,10 @@ __device__ __forceinline__ v3 shade_subtree_body(const SceneParams & P, Ray ray,
 						int node;
 						// of two children the thread keeps one and queues the other (P.queue_keep_refraction: which)
 						const bool refraction_child = (flags & FRAME_HAS_REFRACTION) && !(flags & FRAME_TIR);
-						const bool keep_reflection = reflection_mask && !(refraction_child && P.queue_keep_refraction);
+						// 0: the reflection ray stays; 1: the refraction ray; 2: the ray that stays INSIDE the medium (the refraction
+						// ray on the way in, the reflection ray on the way out): the deeper subtree, as a rule
+						const bool refraction_stays = P.queue_keep_refraction == 2 ? (flags & FRAME_ENTERING) != 0 : P.queue_keep_refraction != 0;
+						const bool keep_reflection = reflection_mask && !(refraction_child && refraction_stays);
 						if (any_child && export_node(P, *q, hit, best.t, node_flags, frame.F_r, result, keep_reflection ? frame.refracted : reflected, keep_reflection ? 1 : 0, bounces_left, cnt, node)) {
 							// the node is a record now; this thread goes on with one of its children, as a walk of its own whose
 							// value is delivered into the record (the other child, if there is one, is in the queue)

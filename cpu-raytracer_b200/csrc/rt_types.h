@@ -103,7 +103,7 @@ struct SceneParams {
 	int queue_inline_below;      // a popped ray with at most this many bounces left is walked to the end by the thread that popped it
 	int queue_idle_looks;        // a warp that finds neither item nor unit looks this many times more (2 / 4 / 8 / ... us apart) before it leaves
 	int queue_idle_shift;        // ... the pause doubles this many times at most (2: 8 us)
-	int queue_keep_refraction;   // of two children the exporting thread keeps the refraction ray (1) or the reflection ray (0) and queues the other
+	int queue_keep_refraction;   // of two children the exporting thread keeps the reflection ray (0), the refraction ray (1) or the one that stays inside the medium (2) and queues the other
 	int queue_item_batch;        // while tile units are left, a warp turns to the queue only when it holds at least this many items (32: a full warp)
 	int blas_stack_entries;      // deepest BLAS + 1: what a push-both-pop-one traversal can hold
 	int tlas_stack_entries;      // this frame's TLAS depth + 1

@@ -44,7 +44,7 @@ out = {
     "workloads": {
         "sponza1080": entry("profiles/r02_ncu_full_render_sponza1080.csv", CAP % ("render_kernel", "sponza1080", "off", "tools/gpu_call14.sh")),
         "dielectrics": entry("profiles/r02_ncu_full_render_dielectrics.csv", CAP % ("render_kernel", "dielectrics", "off", "tools/gpu_call14.sh")),
-        "dielectrics/queued": entry("profiles/r02_ncu_full_render_queue_dielectrics.csv", CAP % ("render_queue_kernel", "dielectrics", "all: AUTO's queued candidate", "tools/gpu_call28.sh, -s 5")),
+        "dielectrics/queued": entry("profiles/r02_ncu_full_render_queue_dielectrics.csv", CAP % ("render_queue_kernel", "dielectrics", "all: AUTO's queued candidate", "tools/gpu_call31.sh, -s 5")),
         "sibenik4k": entry("profiles/r02_ncu_full_render_sibenik4k.csv", CAP % ("render_kernel", "sibenik4k", "off", "tools/gpu_call14.sh")),
     },
     "fxaa": entry("profiles/r02_ncu_full_fxaa_sponza1080.csv", CAP % ("fxaa_kernel", "sponza1080", "off", "tools/gpu_call14.sh")),
