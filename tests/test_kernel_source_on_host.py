@@ -136,3 +136,16 @@ def test_emulated_queue_that_gave_a_frame_up_is_rendered_again_depth_first(emula
         assert np.array_equal(out["frame_buffer"], g.ref_frame_buffer)
         assert out["stats"]["queue_nodes"] == 0            # the frame that counts was walked depth-first
         assert rays(out["stats"]) == [int(x) for x in g.ref_rays]
+
+
+@pytest.mark.timeout(600)
+@pytest.mark.parametrize("keep", ["0", "1", "2"])
+def test_emulated_queue_gives_the_same_frame_whichever_child_stays_in_the_thread(emulated, monkeypatch, keep):
+    """An exported node's thread goes on with one child and queues the other (B200RT_QUEUE_KEEP_REFRACTION: the reflection
+    ray, the refraction ray, or the one that stays inside the medium — the shipped setting): the same bits every time."""
+    monkeypatch.setenv("B200RT_QUEUE_KEEP_REFRACTION", keep)
+    g = Golden("dielectrics_b8_ewa")
+    out = render(emulated, g, deep_queue="all")
+    assert np.array_equal(out["frame_buffer"], g.ref_frame_buffer)
+    assert rays(out["stats"]) == [int(x) for x in g.ref_rays]
+    assert out["stats"]["queue_nodes"] > 0 and out["stats"]["queue_bounce_items"] > 0 and out["stats"]["queue_fallbacks"] == 0
