@@ -96,9 +96,13 @@ class ClockSampler:
 
     def __enter__(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.QUERY, "--format=csv,noheader,nounits", "-lms", "100"],
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.QUERY, "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._read, daemon=True).start()
+            deadline = time.time() + 2.0              # the timed region is tens of milliseconds: the sampler must be running before it starts
+            while not self.samples and time.time() < deadline:
+                time.sleep(0.005)
+            self.samples = []                         # what came before the region is not "during"
         except OSError:
             self.proc = None
         return self
@@ -109,7 +113,8 @@ class ClockSampler:
 
     def __exit__(self, *exc):
         if self.proc:
-            time.sleep(0.15)
+            if not self.samples:
+                time.sleep(0.05)                      # a region shorter than one sampling interval: take the sample that is on its way
             self.proc.terminate()
 
     def summary(self):
