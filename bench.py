@@ -497,6 +497,8 @@ def run_gpu_arm(args, w):
         gather_verified = bool(verdict.item())
 
         for _ in range(max(warmup, 12)):                   # also carries deep_queue = AUTO through its comparison frames (8 + what is in flight)
+            with torch.cuda.stream(stream):
+                flush.fill_(1)                             # ... under the conditions of the timed frames: L2 flushed before each
             step()
         barrier()
         with clocks:
